@@ -1,0 +1,81 @@
+// Shared definitions of the fused tcgen05 path (hidden width 512): packed-weight layout, layer programs and
+// the kernel argument blocks.  Host (fused_host.cu) and device (fused_fwd.cu, fused_bwd.cu, wgrad.cu) agree on these.
+#pragma once
+#include <cuda.h>
+#include <stdint.h>
+#include "../../include/dsdf.h"
+
+namespace dsdf {
+
+constexpr int FH = 512;              // hidden width of the fused path
+constexpr int TILE_M = 128;          // rows per CTA tile == TMEM lanes
+constexpr int A_CHUNK_BYTES = TILE_M * 128;       // [128 rows][64 bf16], SW128
+constexpr int A_BYTES = 8 * A_CHUNK_BYTES;        // 128 KB: one full 512-wide activation tile
+constexpr int HALF_N = 256;                       // accumulator half (one UMMA N)
+constexpr int STAGE_BYTES = HALF_N * 128;         // weight stage: [256 out rows][64 K] bf16, SW128 (32 KB)
+constexpr int NUM_STAGES = 3;
+constexpr int EPI_WARPS = 8;
+constexpr int CHAIN_THREADS = (EPI_WARPS + 2) * 32;   // + TMA warp + MMA warp
+constexpr int CHAIN_SMEM = A_BYTES + NUM_STAGES * STAGE_BYTES + 1024;
+constexpr int MASK_WORDS = FH / 32;               // 16 x u32 keep/relu bits per row per hidden layer
+
+// One hidden layer of a chain (forward: lin{l}; backward: dgrad of lin{l}).
+struct ChainLayer {
+  int32_t has_mma;      // 0: no tensor-core work (forward layer 0 in scene mode)
+  int32_t w_row0;       // first row of this layer's block in the packed weight tensor
+  int32_t n_halves;     // 1 or 2 accumulator halves (N = 256 each)
+  int32_t k_chunks;     // 64-wide K chunks read from the A tile
+  int32_t bias_slot;    // forward: -1 = layer bias; 0/1 = per-scene bias slot (latent folded in)
+  int32_t has_xyz;      // forward: + xyz . Wxyz (fp32, CUDA cores); backward: emit xyz-weighted column sums
+  int32_t dropout;      // dropout after this hidden layer (training)
+  int32_t out_dim;      // true width (<= 512)
+};
+
+struct FwdArgs {
+  int32_t num_hidden;                       // hidden layers (the final 512->1 layer is fused into the last epilogue)
+  int32_t n_tiles;
+  int64_t n_rows;
+  int64_t n_rows_pad;                       // rows per layer region in acts / bitmask (multiple of 128)
+  ChainLayer prog[DSDF_MAX_LAYERS];
+  const float* bias[DSDF_MAX_LAYERS];       // [512] fp32, zero padded
+  const float* wxyz[DSDF_MAX_LAYERS];       // [3][512] fp32 or null
+  const float* w_last;                      // [512] fp32 effective last-layer weight
+  const float* b_last;                      // [1]
+  const int32_t* tile_scene;                // [n_tiles] -> row of cbias
+  const float* cbias;                       // [S][2][512] per-scene biases (latent part of lin0 / skip layer + bias)
+  const float* xyz;                         // [N][3]
+  float* sdf_out;                           // [N]
+  int32_t use_tanh;
+  int32_t training;
+  uint32_t drop_thr;
+  float drop_scale;
+  uint64_t seed;
+  uint64_t row0;                            // global row id of local row 0 (dropout stream is keyed by global rows)
+  const float* gt;                          // [N] or null
+  float clamp;                              // ClampingDistance (<=0: no clamp)
+  float inv_n;                              // 1 / N_total (global batch)
+  float* dy_out;                            // [N_pad] dL/d(pre-tanh output)
+  float* tile_loss;                         // [n_tiles] sum |pred-gt| of the tile's rows
+  uint32_t* bitmask;                        // [num_hidden][N_pad][16]
+  int32_t store_acts;
+};
+
+struct BwdArgs {
+  int32_t num_hidden;
+  int32_t n_tiles;
+  int64_t n_rows;
+  int64_t n_rows_pad;
+  ChainLayer prog[DSDF_MAX_LAYERS];         // prog[l] = dgrad of lin{l}: produces dY_{l-1}; l = num_hidden-1 .. 1
+  const float* w_last;                      // [512]
+  const float* dy;                          // [N_pad]
+  const uint32_t* bitmask;                  // [num_hidden][N_pad][16]
+  float scale[DSDF_MAX_LAYERS];             // backward factor of hidden layer l where its mask bit is set
+  const float* xyz;                         // [N][3]
+  float* tile_part;                         // [n_tiles][part_stride] per-tile column sums
+  int32_t part_stride;
+  int32_t colsum_slot[DSDF_MAX_LAYERS];     // slot (x512 floats) of colsum(dY_l) in tile_part, or -1
+  int32_t xyzsum_slot[DSDF_MAX_LAYERS];     // first of 3 slots of sum_r xyz[r,d]*dY_l[r,:], or -1
+  int32_t store_dys;
+};
+
+}  // namespace dsdf

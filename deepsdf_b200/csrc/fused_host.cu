@@ -1,0 +1,308 @@
+// Host side of the fused tcgen05 path: support check, packed-weight layout, weight-norm fold + bf16 packing,
+// per-scene bias preparation (latent gather + Embedding max_norm renorm), and the C-ABI launch wrappers.
+#include "common.cuh"
+#include "fused.cuh"
+#include "fused_host.h"
+#include "host_util.h"
+
+namespace dsdf {
+
+// ---------------------------------------------------------------------------------------------- layout
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int fused_unsupported_reason(const dsdf_net_desc* d, const char** why) {
+  const int nl = d->num_linear, nh = nl - 1;
+  auto fail = [&](const char* m) { if (why) *why = m; return 1; };
+  if (nl < 3 || nl > DSDF_MAX_LAYERS) return fail("needs 2..15 hidden layers");
+  if (d->geom_dim != 3) return fail("geom_dimension must be 3");
+  if (d->xyz_in_all) return fail("xyz_in_all not supported by the fused path");
+  if (d->layernorm_mask) return fail("LayerNorm not supported by the fused path");
+  if (d->latent_dropout) return fail("latent_dropout not supported by the fused path");
+  if (d->latent_size < 1 || d->latent_size > 256) return fail("latent_size must be 1..256");
+  if (d->out_dim[nl - 1] != 1) return fail("last layer must have one output");
+  if (d->latent_in_mask & 1u) return fail("latent_in=[0] not supported");
+  if (d->latent_in_mask >> nh) return fail("latent_in on the last layer not supported");
+  int n_lat = 0;
+  for (int l = 1; l < nh; ++l) n_lat += (d->latent_in_mask >> l) & 1;
+  if (n_lat > 1) return fail("at most one latent_in layer");
+  const int LD = d->latent_size + d->geom_dim;
+  if (d->in_dim[0] != LD) return fail("first layer must take [latent, xyz]");
+  for (int l = 0; l < nh; ++l) {
+    const bool next_lat = (d->latent_in_mask >> (l + 1)) & 1;
+    if (d->out_dim[l] != (next_lat ? FH - LD : FH)) return fail("hidden width must be 512");
+    if (l > 0 && d->in_dim[l] != FH) return fail("hidden width must be 512");
+  }
+  if (d->in_dim[nl - 1] != FH) return fail("hidden width must be 512");
+  if (why) *why = "";
+  return 0;
+}
+
+int fused_layout(const dsdf_net_desc* d, FusedLayout* lo) {
+  const char* why = nullptr;
+  if (fused_unsupported_reason(d, &why)) return set_error("fused path unsupported: %s", why);
+  memset(lo, 0, sizeof(*lo));
+  const int nl = d->num_linear, nh = nl - 1;
+  const int L = d->latent_size, LD = L + d->geom_dim;
+  lo->num_hidden = nh;
+  lo->lat_layer = -1;
+  int rows_f = 0, rows_b = 0;
+  for (int l = 0; l < nh; ++l) {
+    const bool lat = (d->latent_in_mask >> l) & 1;
+    if (lat) lo->lat_layer = l;
+    lo->xw[l] = (l == 0) ? 0 : (lat ? d->in_dim[l] - LD : d->in_dim[l]);
+    lo->lat_col0[l] = (l == 0) ? 0 : (lat ? lo->xw[l] : -1);
+    lo->xyz_col0[l] = (l == 0) ? L : (lat ? lo->xw[l] + L : -1);
+    lo->fwd_row0[l] = rows_f;
+    lo->fwd_halves[l] = (d->out_dim[l] + HALF_N - 1) / HALF_N;
+    lo->fwd_kchunks[l] = (lo->xw[l] + 63) / 64;
+    if (l > 0) rows_f += lo->fwd_halves[l] * HALF_N;
+    lo->bwd_row0[l] = rows_b;
+    lo->bwd_halves[l] = (lo->xw[l] + HALF_N - 1) / HALF_N;
+    lo->bwd_kchunks[l] = (d->out_dim[l] + 63) / 64;
+    if (l > 0) rows_b += lo->bwd_halves[l] * HALF_N;
+  }
+  lo->fwd_rows = rows_f;
+  lo->bwd_rows = rows_b;
+  size_t off = 0;
+  lo->off_wp = off;      off = align_up(off + size_t(rows_f) * FH * 2, 1024);
+  lo->off_wpt = off;     off = align_up(off + size_t(rows_b) * FH * 2, 1024);
+  lo->off_bias = off;    off = align_up(off + size_t(nh) * FH * 4, 256);
+  lo->off_wxyz = off;    off = align_up(off + size_t(2) * 3 * FH * 4, 256);        // slot 0: lin0, slot 1: skip layer
+  lo->off_wlatT = off;   off = align_up(off + size_t(2) * L * FH * 4, 256);        // [slot][k][512]
+  lo->off_wlast = off;   off = align_up(off + size_t(FH) * 4, 256);
+  for (int l = 0; l < nl; ++l) {
+    lo->off_weff[l] = off;  off = align_up(off + size_t(d->out_dim[l]) * d->in_dim[l] * 4, 256);
+    lo->off_invn[l] = off;  off = align_up(off + size_t(d->out_dim[l]) * 4, 256);
+  }
+  lo->total_bytes = off;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- fold + pack
+struct PackArgs {
+  dsdf_net_desc desc;
+  dsdf_params params;
+  FusedLayout lo;
+  uint8_t* pack;
+};
+
+// grid: (max out rows, num_linear); block 128.  One block folds one output row of one layer.
+__global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
+  const int l = blockIdx.y, o = blockIdx.x;
+  const dsdf_net_desc& d = a.desc;
+  if (o >= d.out_dim[l]) return;
+  const int in = d.in_dim[l];
+  const int nh = a.lo.num_hidden;
+  const float* vrow = a.params.v[l] + size_t(o) * in;
+  __shared__ float red[4];
+  __shared__ float s_scale;
+  float ss = 0.f;
+  for (int k = threadIdx.x; k < in; k += blockDim.x) { float t = vrow[k]; ss += t * t; }
+  for (int off = 16; off > 0; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float tot = (red[0] + red[1]) + (red[2] + red[3]);
+    float invn = 1.0f, scale = 1.0f;
+    if (a.params.g[l] != nullptr) { invn = 1.0f / sqrtf(tot); scale = a.params.g[l][o] * invn; }
+    s_scale = scale;
+    reinterpret_cast<float*>(a.pack + a.lo.off_invn[l])[o] = invn;
+    if (l < nh) reinterpret_cast<float*>(a.pack + a.lo.off_bias)[l * FH + o] = a.params.b[l][o];
+  }
+  __syncthreads();
+  const float scale = s_scale;
+  float* weff = reinterpret_cast<float*>(a.pack + a.lo.off_weff[l]) + size_t(o) * in;
+  __nv_bfloat16* wp = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wp);
+  __nv_bfloat16* wpt = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wpt);
+  float* wxyz = reinterpret_cast<float*>(a.pack + a.lo.off_wxyz);
+  float* wlatT = reinterpret_cast<float*>(a.pack + a.lo.off_wlatT);
+  float* wlast = reinterpret_cast<float*>(a.pack + a.lo.off_wlast);
+  const int L = d.latent_size;
+  for (int k = threadIdx.x; k < in; k += blockDim.x) {
+    const float w = vrow[k] * scale;
+    weff[k] = w;
+    if (l == nh) { wlast[k] = w; continue; }
+    const int xw = a.lo.xw[l];
+    if (k < xw) {
+      if (l > 0) {
+        wp[size_t(a.lo.fwd_row0[l] + o) * FH + k] = __float2bfloat16_rn(w);
+        wpt[size_t(a.lo.bwd_row0[l] + k) * FH + o] = __float2bfloat16_rn(w);
+      }
+    } else if (a.lo.lat_col0[l] >= 0 && k < a.lo.lat_col0[l] + L) {
+      const int slot = (l == 0) ? 0 : 1;
+      wlatT[(size_t(slot) * L + (k - a.lo.lat_col0[l])) * FH + o] = w;
+    } else if (a.lo.xyz_col0[l] >= 0 && k >= a.lo.xyz_col0[l]) {
+      const int slot = (l == 0) ? 0 : 1;
+      wxyz[(size_t(slot) * 3 + (k - a.lo.xyz_col0[l])) * FH + o] = w;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- scene prepare
+// Embedding(max_norm) lookup side effect: rows of the batch with ||z|| > max_norm are rescaled in place
+// (train_deep_sdf.py:385,509).  One warp per scene.
+__global__ void latent_renorm_kernel(float* table, const int64_t* scene_ids, int S, int L, float max_norm) {
+  const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (s >= S) return;
+  const int lane = threadIdx.x & 31;
+  // a scene listed twice must be renormalised once: only its first occurrence acts
+  const int64_t id = scene_ids[s];
+  for (int t = 0; t < s; ++t) if (scene_ids[t] == id) return;
+  float* row = table + size_t(id) * L;
+  float ss = 0.f;
+  for (int k = lane; k < L; k += 32) ss += row[k] * row[k];
+  for (int off = 16; off > 0; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+  const float nrm = sqrtf(ss);
+  if (nrm > max_norm) {
+    const float sc = max_norm / (nrm + 1e-7f);
+    for (int k = lane; k < L; k += 32) row[k] *= sc;
+  }
+}
+
+// cbias[s][slot][o] = bias_l[o] + sum_k Weff_l[o, lat_col0 + k] * z[scene_ids[s]][k]; grid (S, 2), block 512
+__global__ void scene_bias_kernel(const float* __restrict__ table, const int64_t* __restrict__ scene_ids, int L,
+                                  const float* __restrict__ wlatT, const float* __restrict__ bias, int lat_layer,
+                                  float* __restrict__ cbias) {
+  const int s = blockIdx.x, slot = blockIdx.y, o = threadIdx.x;
+  extern __shared__ float z[];
+  const float* row = table + size_t(scene_ids[s]) * L;
+  for (int k = threadIdx.x; k < L; k += blockDim.x) z[k] = row[k];
+  __syncthreads();
+  float acc = 0.f;
+  if (slot == 0 || lat_layer > 0) {
+    const int l = (slot == 0) ? 0 : lat_layer;
+    acc = bias[l * FH + o];
+    const float* w = wlatT + size_t(slot) * L * FH + o;
+    for (int k = 0; k < L; ++k) acc += w[size_t(k) * FH] * z[k];
+  }
+  cbias[(size_t(s) * 2 + slot) * FH + o] = acc;
+}
+
+static void fill_programs(const dsdf_net_desc* d, const FusedLayout& lo, ChainLayer* fwd, ChainLayer* bwd) {
+  for (int l = 0; l < lo.num_hidden; ++l) {
+    ChainLayer& F = fwd[l];
+    F.has_mma = (l > 0);
+    F.w_row0 = lo.fwd_row0[l];
+    F.n_halves = lo.fwd_halves[l];
+    F.k_chunks = lo.fwd_kchunks[l];
+    F.bias_slot = (l == 0) ? 0 : (l == lo.lat_layer ? 1 : -1);
+    F.has_xyz = (l == 0 || l == lo.lat_layer);
+    F.dropout = (d->dropout_mask >> l) & 1;
+    F.out_dim = d->out_dim[l];
+    ChainLayer& B = bwd[l];
+    B.has_mma = (l > 0);
+    B.w_row0 = lo.bwd_row0[l];
+    B.n_halves = lo.bwd_halves[l];
+    B.k_chunks = lo.bwd_kchunks[l];
+    B.bias_slot = -1;
+    B.has_xyz = (l == 0 || l == lo.lat_layer);
+    B.dropout = F.dropout;
+    B.out_dim = d->out_dim[l];
+  }
+}
+
+int launch_fused_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, const FwdArgs& args, int grid, cudaStream_t stream);
+
+}  // namespace dsdf
+
+using namespace dsdf;
+
+extern "C" int dsdf_fused_supported(const dsdf_net_desc* desc) { return fused_unsupported_reason(desc, nullptr) == 0; }
+
+extern "C" size_t dsdf_pack_bytes(const dsdf_net_desc* desc) {
+  FusedLayout lo;
+  if (fused_layout(desc, &lo)) return 0;
+  return lo.total_bytes;
+}
+
+extern "C" int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, void* stream) {
+  if (int e = require_sm100()) return e;
+  PackArgs a;
+  a.desc = *desc;
+  a.params = *params;
+  if (int e = fused_layout(desc, &a.lo)) return e;
+  a.pack = static_cast<uint8_t*>(pack);
+  DSDF_REQUIRE((reinterpret_cast<uintptr_t>(pack) & 1023) == 0, "pack buffer must be 1024-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // zero the padded regions (bf16 blocks, bias, wxyz, wlatT, wlast)
+  DSDF_CHECK_CUDA(cudaMemsetAsync(pack, 0, a.lo.off_weff[0], st));
+  int max_out = 0;
+  for (int l = 0; l < desc->num_linear; ++l) max_out = desc->out_dim[l] > max_out ? desc->out_dim[l] : max_out;
+  pack_weights_kernel<<<dim3(max_out, desc->num_linear), 128, 0, st>>>(a);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, float* lat_table, const int64_t* scene_ids,
+                                  int32_t n_scenes, float max_norm, float* cbias, void* stream) {
+  if (int e = require_sm100()) return e;
+  FusedLayout lo;
+  if (int e = fused_layout(desc, &lo)) return e;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int L = desc->latent_size;
+  if (max_norm > 0.f) {
+    latent_renorm_kernel<<<(n_scenes + 3) / 4, 128, 0, st>>>(lat_table, scene_ids, n_scenes, L, max_norm);
+    DSDF_CHECK_CUDA(cudaGetLastError());
+  }
+  const uint8_t* p = static_cast<const uint8_t*>(pack);
+  scene_bias_kernel<<<dim3(n_scenes, 2), FH, L * sizeof(float), st>>>(
+      lat_table, scene_ids, L, reinterpret_cast<const float*>(p + lo.off_wlatT),
+      reinterpret_cast<const float*>(p + lo.off_bias), lo.lat_layer, cbias);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const float* cbias,
+                                  const int32_t* tile_scene, const float* xyz, int64_t n_rows, float* sdf_out,
+                                  const dsdf_train_io* tr, void* stream) {
+  if (int e = require_sm100()) return e;
+  FusedLayout lo;
+  if (int e = fused_layout(desc, &lo)) return e;
+  DSDF_REQUIRE(n_rows > 0, "n_rows must be positive");
+  const uint8_t* p = static_cast<const uint8_t*>(pack);
+  FwdArgs a;
+  memset(&a, 0, sizeof(a));
+  ChainLayer bwd_unused[DSDF_MAX_LAYERS];
+  fill_programs(desc, lo, a.prog, bwd_unused);
+  a.num_hidden = lo.num_hidden;
+  a.n_rows = n_rows;
+  a.n_tiles = int((n_rows + TILE_M - 1) / TILE_M);
+  a.n_rows_pad = int64_t(a.n_tiles) * TILE_M;
+  for (int l = 0; l < lo.num_hidden; ++l) {
+    a.bias[l] = reinterpret_cast<const float*>(p + lo.off_bias) + size_t(l) * FH;
+    a.wxyz[l] = (l == 0) ? reinterpret_cast<const float*>(p + lo.off_wxyz)
+                         : (l == lo.lat_layer ? reinterpret_cast<const float*>(p + lo.off_wxyz) + 3 * FH : nullptr);
+  }
+  a.w_last = reinterpret_cast<const float*>(p + lo.off_wlast);
+  a.b_last = tr && tr->b_last ? tr->b_last : nullptr;
+  DSDF_REQUIRE(a.b_last != nullptr, "b_last (bias of the last layer) must be given");
+  a.tile_scene = tile_scene;
+  a.cbias = cbias;
+  a.xyz = xyz;
+  a.sdf_out = sdf_out;
+  a.use_tanh = desc->use_tanh;
+  a.training = tr->training;
+  a.drop_thr = dropout_threshold(desc->dropout_prob);
+  a.drop_scale = 1.0f / (1.0f - float(a.drop_thr) / 256.0f);
+  a.seed = tr->seed;
+  a.row0 = tr->row0;
+  a.gt = tr->gt;
+  a.clamp = tr->clamp;
+  a.inv_n = tr->inv_n;
+  a.dy_out = tr->dy_out;
+  a.tile_loss = tr->tile_loss;
+  a.bitmask = tr->bitmask;
+  a.store_acts = (tr->acts != nullptr);
+  if (a.training) {
+    DSDF_REQUIRE(tr->n_rows_pad == a.n_rows_pad, "n_rows_pad must be n_rows rounded up to 128");
+    if (a.gt) DSDF_REQUIRE(a.dy_out && a.tile_loss, "training with gt needs dy_out and tile_loss");
+  }
+  CUtensorMap tmW, tmActs;
+  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wp, FH, lo.fwd_rows, FH * 2, 64, HALF_N)) return e;
+  const void* acts_ptr = tr->acts ? tr->acts : static_cast<const void*>(p + lo.off_wp);   // dummy map when unused
+  const uint64_t acts_rows = tr->acts ? uint64_t(lo.num_hidden) * a.n_rows_pad : uint64_t(lo.fwd_rows);
+  if (int e = make_tmap_bf16_2d(&tmActs, acts_ptr, FH, acts_rows, FH * 2, 64, TILE_M)) return e;
+  int grid = sm_count();
+  if (grid > a.n_tiles) grid = a.n_tiles;
+  return launch_fused_forward(tmW, tmActs, a, grid, static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,32 @@
+// Packed-weight layout of the fused path (offsets into the caller-provided pack buffer).
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+#include "../../include/dsdf.h"
+
+namespace dsdf {
+
+struct FusedLayout {
+  int32_t num_hidden;
+  int32_t lat_layer;                     // index of the latent_in layer, or -1
+  int32_t xw[DSDF_MAX_LAYERS];           // width of the hidden-activation part of layer l's input (0 for layer 0)
+  int32_t lat_col0[DSDF_MAX_LAYERS];     // first latent column of layer l's input, or -1
+  int32_t xyz_col0[DSDF_MAX_LAYERS];     // first xyz column of layer l's input, or -1
+  int32_t fwd_row0[DSDF_MAX_LAYERS], fwd_halves[DSDF_MAX_LAYERS], fwd_kchunks[DSDF_MAX_LAYERS];
+  int32_t bwd_row0[DSDF_MAX_LAYERS], bwd_halves[DSDF_MAX_LAYERS], bwd_kchunks[DSDF_MAX_LAYERS];
+  int32_t fwd_rows, bwd_rows;
+  size_t off_wp;                         // bf16 [fwd_rows][512]   forward B operand  (rows = out features, K = in)
+  size_t off_wpt;                        // bf16 [bwd_rows][512]   dgrad B operand    (rows = in features,  K = out)
+  size_t off_bias;                       // f32  [num_hidden][512]
+  size_t off_wxyz;                       // f32  [2][3][512]       xyz columns of lin0 / skip layer
+  size_t off_wlatT;                      // f32  [2][L][512]       latent columns of lin0 / skip layer, transposed
+  size_t off_wlast;                      // f32  [512]             effective last-layer weight
+  size_t off_weff[DSDF_MAX_LAYERS];      // f32  [out][in]         effective (folded) weights, reference layout
+  size_t off_invn[DSDF_MAX_LAYERS];      // f32  [out]             1/||v|| per row (1 for plain layers)
+  size_t total_bytes;
+};
+
+int fused_unsupported_reason(const dsdf_net_desc* d, const char** why);
+int fused_layout(const dsdf_net_desc* d, FusedLayout* lo);
+
+}  // namespace dsdf

@@ -1,0 +1,144 @@
+// tcgen05 / TMA bring-up micro-tests.  One CTA computes C[128 x N] = A * B^T on the tensor cores with the operand
+// layouts the fused kernels rely on, so that every descriptor convention is checked against a PyTorch matmul before
+// the big kernels depend on it:
+//   mode bit0: A is MN-major (stored [K rows][128 M] in global)  - wgrad's dY^T operand
+//   mode bit1: B is MN-major (stored [K rows][N]   in global)    - wgrad's X^T operand
+//   mode bit2: A tile is written to shared memory by threads with sw128_offset() instead of TMA (the epilogue's path)
+//   mode bit3: additionally TMA-store the A tile back to global (activation / dY stash path)
+// Descriptor LBO/SBO are runtime arguments so the host can sweep conventions without rebuilding.
+#include "common.cuh"
+#include "host_util.h"
+#include "../../include/dsdf.h"
+
+namespace dsdf {
+
+struct SelftestArgs {
+  int K, N, mode;
+  uint32_t a_lbo, a_sbo, b_lbo, b_sbo;
+  const __nv_bfloat16* a_raw;   // for manual writes: K-major [128][K]
+  float* C;                     // [128][N]
+};
+
+constexpr int ST_THREADS = 192;   // warps 0-3 epilogue (TMEM lane quadrants), warp 4 TMA, warp 5 MMA/alloc
+
+__global__ void __launch_bounds__(ST_THREADS, 1)
+umma_selftest_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const __grid_constant__ CUtensorMap tmStore, SelftestArgs args) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int K = args.K, N = args.N;
+  const bool a_mn = args.mode & 1, b_mn = args.mode & 2, manual_a = args.mode & 4, do_store = args.mode & 8;
+  uint8_t* sA = smem;                         // up to 64 KB
+  uint8_t* sB = smem + 65536;                 // up to 128 KB
+  __shared__ uint64_t bar_full, bar_done;
+  __shared__ uint32_t tmem_base_slot;
+  const int warp = threadIdx.x >> 5;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&bar_full, 1);
+    mbar_init(&bar_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 5) tmem_alloc<256>(&tmem_base_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  // ---- stage operands
+  uint32_t a_bytes = 128u * K * 2u, b_bytes = uint32_t(N) * K * 2u;
+  if (manual_a) {
+    // K-major A written by threads: chunk kc = [128 rows][64 cols]
+    for (int idx = threadIdx.x; idx < 128 * K; idx += blockDim.x) {
+      int r = idx / K, c = idx % K;
+      uint32_t off = (c >> 6) * (128u * 128u) + sw128_offset(r, c & 63);
+      *reinterpret_cast<__nv_bfloat16*>(sA + off) = args.a_raw[idx];
+    }
+    fence_proxy_async_smem();
+  }
+  __syncthreads();
+  if (warp == 4 && elect_one()) {
+    uint32_t tx = b_bytes + (manual_a ? 0u : a_bytes);
+    mbar_arrive_expect_tx(&bar_full, tx);
+    if (!manual_a) {
+      if (!a_mn) {
+        for (int kc = 0; kc < K / 64; ++kc) tma_load_2d(sA + kc * 16384, &tmA, &bar_full, kc * 64, 0);   // box {64, 128}
+      } else {
+        for (int mg = 0; mg < 2; ++mg) tma_load_2d(sA + mg * (K * 128), &tmA, &bar_full, mg * 64, 0);    // box {64, K}
+      }
+    }
+    if (!b_mn) {
+      for (int kc = 0; kc < K / 64; ++kc) tma_load_2d(sB + kc * (N * 128), &tmB, &bar_full, kc * 64, 0);   // box {64, N}
+    } else {
+      for (int ng = 0; ng < N / 64; ++ng) tma_load_2d(sB + ng * (K * 128), &tmB, &bar_full, ng * 64, 0);   // box {64, K}
+    }
+  }
+  if (warp == 5) {
+    mbar_wait(&bar_full, 0);
+    tc_fence_after();
+    if (elect_one()) {
+      const uint32_t idesc = umma_idesc_bf16(128, N, a_mn ? 1 : 0, b_mn ? 1 : 0);
+      const uint64_t a_hi = umma_desc_hi_sw128(args.a_lbo, args.a_sbo);
+      const uint64_t b_hi = umma_desc_hi_sw128(args.b_lbo, args.b_sbo);
+      for (int ks = 0; ks < K / 16; ++ks) {
+        uint32_t a_off = a_mn ? ks * 2048u : (ks >> 2) * 16384u + (ks & 3) * 32u;
+        uint32_t b_off = b_mn ? ks * 2048u : (ks >> 2) * (uint32_t(N) * 128u) + (ks & 3) * 32u;
+        umma_bf16_ss(tmem_base, umma_desc(smem_u32(sA) + a_off, a_hi), umma_desc(smem_u32(sB) + b_off, b_hi), idesc,
+                     ks > 0 ? 1u : 0u);
+      }
+      umma_commit(&bar_done);
+    }
+    __syncwarp();
+  }
+  if (warp < 4) {
+    mbar_wait(&bar_done, 0);
+    tc_fence_after();
+    const int row = warp * 32 + lane_id();
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem_base + (uint32_t(warp * 32) << 16) + c0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) args.C[size_t(row) * N + c0 + j] = __uint_as_float(v[j]);
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (do_store && !a_mn && threadIdx.x == 0) {
+    // write the (swizzled) A tile back through a SWIZZLE_128B tensor map: must land un-swizzled in global
+    for (int kc = 0; kc < K / 64; ++kc) tma_store_2d(&tmStore, sA + kc * 16384, kc * 64, 0);
+    tma_store_commit();
+    tma_store_wait_all0();
+  }
+  __syncthreads();
+  if (warp == 5) tmem_dealloc<256>(tmem_base);
+}
+
+}  // namespace dsdf
+
+extern "C" int dsdf_selftest_umma(int mode, const void* A, const void* B, float* C, void* A_store_out, int K, int N,
+                                  unsigned a_lbo, unsigned a_sbo, unsigned b_lbo, unsigned b_sbo, void* stream) {
+  using namespace dsdf;
+  if (int e = require_sm100()) return e;
+  DSDF_REQUIRE(K % 64 == 0 && K >= 64 && K <= 256, "selftest: K must be 64..256, multiple of 64");
+  DSDF_REQUIRE(N % 64 == 0 && N >= 64 && N <= 256, "selftest: N must be 64..256, multiple of 64");
+  const bool a_mn = mode & 1, b_mn = mode & 2;
+  CUtensorMap tmA, tmB, tmS;
+  int e;
+  if (!a_mn) e = make_tmap_bf16_2d(&tmA, A, K, 128, uint64_t(K) * 2, 64, 128);
+  else       e = make_tmap_bf16_2d(&tmA, A, 128, K, 128 * 2, 64, K);
+  if (e) return e;
+  if (!b_mn) e = make_tmap_bf16_2d(&tmB, B, K, N, uint64_t(K) * 2, 64, N);
+  else       e = make_tmap_bf16_2d(&tmB, B, N, K, uint64_t(N) * 2, 64, K);
+  if (e) return e;
+  const void* store_ptr = A_store_out ? A_store_out : A;
+  e = make_tmap_bf16_2d(&tmS, store_ptr, K, 128, uint64_t(K) * 2, 64, 128);
+  if (e) return e;
+  if ((mode & 8) && !A_store_out) return set_error("selftest: store mode needs an output buffer");
+  SelftestArgs args{K, N, mode, a_lbo, a_sbo, b_lbo, b_sbo, reinterpret_cast<const __nv_bfloat16*>(A), C};
+  const size_t smem = 65536 + 131072 + 1024;
+  DSDF_CHECK_CUDA(cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  umma_selftest_kernel<<<1, ST_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB, tmS, args);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

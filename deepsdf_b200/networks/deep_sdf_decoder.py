@@ -1,0 +1,213 @@
+"""Drop-in ``Decoder`` for ``deep_sdf.networks.deep_sdf_decoder.Decoder``.
+
+Same constructor keywords, same parameter / ``state_dict`` names (``lin{l}.bias``,
+``lin{l}.parametrizations.weight.original0|1`` or ``lin{l}.weight``, ``bn{l}.*``), same
+attributes (``geom_dimension``, ``num_layers``, ``latent_in`` ...), same ``forward(input[N, L+D])
+-> [N, 1]`` contract, honours ``train()/eval()``, differentiable w.r.t. its input and its
+parameters, survives ``torch.nn.DataParallel`` on one device.  Reference:
+deep_sdf/networks/deep_sdf_decoder.py:9-111.
+
+The compute is NOT PyTorch: ``forward``/``backward`` call the C-ABI library
+(``include/dsdf.h``) - hand-written sm_100a kernels.  There is no CPU path and no fallback.
+
+Additional (fused, scene-mode) entry points used by the build's own trainer / grid evaluator:
+``decode_scenes`` (see ``deepsdf_b200.engine``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional
+
+import torch
+import torch.nn as nn
+
+from .. import _lib as L
+from ..spec import NetSpec
+
+_WS_SINGLE_PASS_LIMIT = 6 << 30     # keep one workspace alive for backward below this size
+_CHUNK_ROWS = 1 << 17
+
+
+class Decoder(nn.Module):
+    def __init__(
+        self,
+        latent_size,
+        dims,
+        geom_dimension,
+        dropout=None,
+        dropout_prob=0.0,
+        norm_layers=(),
+        latent_in=(),
+        weight_norm=False,
+        xyz_in_all=None,
+        use_tanh=False,
+        latent_dropout=False,
+    ):
+        super().__init__()
+        self.spec = NetSpec(latent_size, list(dims), geom_dimension, dropout, dropout_prob, norm_layers, latent_in,
+                            weight_norm, xyz_in_all, use_tanh, latent_dropout)
+        s = self.spec
+        # public attributes the reference sets (deep_sdf_decoder.py:31-40, 66-72)
+        self.num_layers = s.num_layers
+        self.geom_dimension = geom_dimension
+        self.norm_layers = norm_layers
+        self.latent_in = latent_in
+        self.latent_dropout = latent_dropout
+        self.xyz_in_all = xyz_in_all
+        self.weight_norm = weight_norm
+        self.use_tanh = use_tanh
+        self.dropout_prob = dropout_prob
+        self.dropout = dropout
+        self.latent_size = latent_size
+        # parameter containers with the reference's names; they only hold tensors, their forward() is never used
+        for layer in range(s.num_linear):
+            lin = nn.Linear(s.in_dims[layer], s.out_dims[layer])
+            if s.is_weight_normed(layer):
+                lin = nn.utils.parametrizations.weight_norm(lin)
+            setattr(self, "lin" + str(layer), lin)
+            if s.has_layernorm(layer):
+                setattr(self, "bn" + str(layer), nn.LayerNorm(s.out_dims[layer]))
+        self._desc = s.desc()
+
+    # ------------------------------------------------------------------ parameter plumbing
+    def layer_tensors(self, layer: int):
+        """(v_or_weight, g_or_None, bias, ln_w, ln_b) of one layer, as the live Parameters."""
+        lin = getattr(self, "lin" + str(layer))
+        if self.spec.is_weight_normed(layer):
+            g = lin.parametrizations.weight.original0
+            v = lin.parametrizations.weight.original1
+        else:
+            g, v = None, lin.weight
+        ln_w = ln_b = None
+        if self.spec.has_layernorm(layer):
+            bn = getattr(self, "bn" + str(layer))
+            ln_w, ln_b = bn.weight, bn.bias
+        return v, g, lin.bias, ln_w, ln_b
+
+    def flat_param_list(self) -> List[torch.Tensor]:
+        out = []
+        for layer in range(self.spec.num_linear):
+            out.extend(t for t in self.layer_tensors(layer) if t is not None)
+        return out
+
+    def c_params(self, tensors: Optional[List[torch.Tensor]] = None) -> L.Params:
+        """Fill the C struct from the live parameters (or from a same-order tensor list)."""
+        P = L.Params()
+        it = iter(tensors) if tensors is not None else None
+        for layer in range(self.spec.num_linear):
+            live = self.layer_tensors(layer)
+            vals = []
+            for t in live:
+                if t is None:
+                    vals.append(None)
+                else:
+                    vals.append(next(it) if it is not None else t)
+            v, g, b, ln_w, ln_b = vals
+            for name, t in (("v", v), ("g", g), ("b", b), ("ln_w", ln_w), ("ln_b", ln_b)):
+                if t is not None:
+                    if t.dtype != torch.float32 or not t.is_contiguous():
+                        raise L.DsdfError("decoder parameters must be contiguous fp32")
+                    getattr(P, name)[layer] = t.data_ptr()
+        return P
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, input):
+        if input.dim() != 2 or input.shape[1] != self.spec.full_dims[0]:
+            raise RuntimeError(
+                f"Decoder expects input [N, {self.spec.full_dims[0]}] (latent ++ xyz), got {tuple(input.shape)}")
+        L.require_cuda(input, *self.flat_param_list())
+        seed = 0
+        if self.training:
+            # one Philox key per call, drawn from torch's CPU generator -> torch.manual_seed makes runs repeatable
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        params = self.flat_param_list()
+        return _DecoderFn.apply(self, input, bool(self.training), seed, *params)
+
+
+class _DecoderFn(torch.autograd.Function):
+    """Generic-path autograd node.  forward/backward are C-ABI calls; for ``create_graph=True`` (the double-backward
+    trick behind ``torch.autograd.functional.jvp``, deep_sdf/mesh.py:405-422) backward returns ``grad_out * G`` with the
+    per-row input gradient G from the kernel, which is differentiable w.r.t. ``grad_out``."""
+
+    @staticmethod
+    def forward(ctx, module: Decoder, inp: torch.Tensor, training: bool, seed: int, *params):
+        lib = L.lib()
+        desc = module._desc
+        x = inp.detach().contiguous().float()
+        N = x.shape[0]
+        out = torch.empty(N, 1, device=x.device, dtype=torch.float32)
+        ctx.module, ctx.training, ctx.seed = module, training, seed
+        ctx.n_params = len(params)
+        ctx.saved_ws = None
+        if N == 0:
+            ctx.save_for_backward(x, *params)
+            return out
+        P = module.c_params([p.detach() for p in params])
+        with torch.cuda.device(x.device):
+            st = L.stream_ptr(x.device)
+            need_grad = any(ctx.needs_input_grad)
+            chunk = N
+            if lib.dsdf_generic_workspace_bytes(C.byref(desc), N) > _WS_SINGLE_PASS_LIMIT:
+                chunk = _CHUNK_ROWS
+            ctx.chunk = chunk
+            for r0 in range(0, N, chunk):
+                n = min(chunk, N - r0)
+                nbytes = lib.dsdf_generic_workspace_bytes(C.byref(desc), n)
+                ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+                L.check(lib.dsdf_generic_forward(C.byref(desc), C.byref(P), x[r0:r0 + n].data_ptr(), n, int(training), seed, r0,
+                                                 out[r0:r0 + n].data_ptr(), ws.data_ptr(), nbytes, st))
+                if need_grad and chunk == N:
+                    ctx.saved_ws = ws
+        ctx.save_for_backward(x, *params)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        x, *params = ctx.saved_tensors
+        module: Decoder = ctx.module
+        lib = L.lib()
+        desc = module._desc
+        N = x.shape[0]
+        need_in = ctx.needs_input_grad[1]
+        need_p = any(ctx.needs_input_grad[4:])
+        none4 = (None, None, None, None)
+        if N == 0:
+            return none4[:1] + ((torch.zeros_like(x) if need_in else None),) + (None, None) + tuple(
+                torch.zeros_like(p) if n else None for p, n in zip(params, ctx.needs_input_grad[4:]))
+        double = torch.is_grad_enabled() and grad_out.requires_grad
+        P = module.c_params([p.detach() for p in params])
+        go = (torch.ones(N, 1, device=x.device) if double else grad_out.detach()).contiguous().float()
+        gin = torch.empty_like(x) if (need_in or double) else None
+        pgrads = [torch.empty_like(p) for p in params] if (need_p and not double) else None
+        PG = None
+        if pgrads is not None:
+            PG = L.ParamGrads()
+            it = iter(pgrads)
+            for layer in range(module.spec.num_linear):
+                live = module.layer_tensors(layer)
+                for name, t in zip(("v", "g", "b", "ln_w", "ln_b"), live):
+                    if t is not None:
+                        getattr(PG, name)[layer] = next(it).data_ptr()
+        with torch.cuda.device(x.device):
+            st = L.stream_ptr(x.device)
+            chunk = ctx.chunk
+            for ci, r0 in enumerate(range(0, N, chunk)):
+                n = min(chunk, N - r0)
+                nbytes = lib.dsdf_generic_workspace_bytes(C.byref(desc), n)
+                if ctx.saved_ws is not None:
+                    ws = ctx.saved_ws
+                else:   # recompute this chunk's forward (same Philox key and row ids -> same dropout masks)
+                    ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+                    scratch = torch.empty(n, 1, device=x.device)
+                    L.check(lib.dsdf_generic_forward(C.byref(desc), C.byref(P), x[r0:r0 + n].data_ptr(), n, int(ctx.training),
+                                                     ctx.seed, r0, scratch.data_ptr(), ws.data_ptr(), nbytes, st))
+                L.check(lib.dsdf_generic_backward(
+                    C.byref(desc), C.byref(P), x[r0:r0 + n].data_ptr(), n, int(ctx.training), ctx.seed, r0,
+                    go[r0:r0 + n].data_ptr(), gin[r0:r0 + n].data_ptr() if gin is not None else None,
+                    C.byref(PG) if PG is not None else None, int(ci > 0), ws.data_ptr(), nbytes, st))
+        if double:
+            # first-order exact; differentiable w.r.t. grad_out (rows are independent scalars)
+            return (None, grad_out * gin, None, None) + tuple(None for _ in params)
+        grads_p = tuple(g if n else None for g, n in zip(pgrads, ctx.needs_input_grad[4:])) if pgrads is not None else tuple(
+            None for _ in params)
+        return (None, gin if need_in else None, None, None) + grads_p

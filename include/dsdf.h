@@ -1,0 +1,137 @@
+/* deepsdf_b200 C ABI  (libdsdf_b200.so)
+ *
+ * Drop-in boundary for the DeepSDF auto-decoder hot path of mkofler96/DeepSDF.  Every entry point takes plain
+ * pointers and sizes only (CUDA *device* pointers owned by the caller unless stated otherwise), an explicit
+ * cudaStream_t passed as void*, and returns 0 on success or a non-zero code; dsdf_last_error() then holds a
+ * thread-local message.  The library never allocates device memory behind the caller's back: every scratch
+ * buffer is a caller-provided workspace whose size a *_bytes() query returns.  sm_100a only - any other device
+ * is an error, there is no CPU or other-GPU fallback.
+ *
+ * What each group replaces in the reference (paths relative to the reference root):
+ *   net desc / params        Decoder.__init__                  deep_sdf/networks/deep_sdf_decoder.py:10-73
+ *   dsdf_generic_forward     Decoder.forward                   deep_sdf/networks/deep_sdf_decoder.py:76-111
+ *   dsdf_generic_backward    autograd of the above             train_deep_sdf.py:533, deep_sdf/mesh.py:405-422
+ *   dsdf_pack_weights        torch._weight_norm per call       deep_sdf/networks/deep_sdf_decoder.py:50-55
+ *   dsdf_scene_prepare       lat_vecs(indices) + max_norm      train_deep_sdf.py:385,509
+ *   dsdf_fused_forward       decoder(input) (+clamp, L1)       train_deep_sdf.py:511-519 ; deep_sdf/utils.py:54-65
+ *   dsdf_fused_dgrad/wgrad   chunk_loss.backward()             train_deep_sdf.py:533
+ *   dsdf_fused_finish        weight_norm backward, latent grad, code regulariser   train_deep_sdf.py:523-533
+ *   dsdf_adam                optimizer_all.step()              train_deep_sdf.py:400-411,545
+ *   dsdf_grid_points         create_mesh sample grid           deep_sdf/mesh.py:37-53
+ */
+#ifndef DSDF_B200_H
+#define DSDF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DSDF_MAX_LAYERS 16
+#define DSDF_ABI_VERSION 1
+
+/* Network description == the reference's NetworkSpecs after Decoder.__init__ resolved the layer sizes. */
+typedef struct dsdf_net_desc {
+  int32_t latent_size;                 /* L  (CodeLength) */
+  int32_t geom_dim;                    /* D  (geom_dimension) */
+  int32_t num_linear;                  /* number of nn.Linear layers = len(dims)+1 */
+  int32_t in_dim[DSDF_MAX_LAYERS];     /* lin{l}.in_features  */
+  int32_t out_dim[DSDF_MAX_LAYERS];    /* lin{l}.out_features */
+  uint32_t weight_norm_mask;           /* bit l: lin{l} is weight-normed (g,v) */
+  uint32_t layernorm_mask;             /* bit l: bn{l} LayerNorm applied after lin{l} (hidden layers only) */
+  uint32_t dropout_mask;               /* bit l: F.dropout after hidden layer l */
+  uint32_t latent_in_mask;             /* bit l: x = cat([x, input]) before lin{l} */
+  int32_t xyz_in_all;                  /* x = cat([x, xyz]) before every lin{l}, l != 0, not in latent_in */
+  int32_t use_tanh;                    /* extra tanh on the last layer (the final self.th tanh is always applied) */
+  int32_t latent_dropout;              /* F.dropout(latent, 0.2) on the first-layer copy of the latent */
+  float dropout_prob;
+} dsdf_net_desc;
+
+/* Parameter pointers in the reference's own layout (fp32, row-major [out,in]); g == NULL for plain layers. */
+typedef struct dsdf_params {
+  const float* v[DSDF_MAX_LAYERS];     /* lin{l}.weight  or  lin{l}.parametrizations.weight.original1 */
+  const float* g[DSDF_MAX_LAYERS];     /* lin{l}.parametrizations.weight.original0 [out]  or NULL */
+  const float* b[DSDF_MAX_LAYERS];     /* lin{l}.bias */
+  const float* ln_w[DSDF_MAX_LAYERS];  /* bn{l}.weight or NULL */
+  const float* ln_b[DSDF_MAX_LAYERS];  /* bn{l}.bias   or NULL */
+} dsdf_params;
+
+typedef struct dsdf_param_grads {      /* same shapes as dsdf_params; written (not accumulated) unless stated */
+  float* v[DSDF_MAX_LAYERS];
+  float* g[DSDF_MAX_LAYERS];
+  float* b[DSDF_MAX_LAYERS];
+  float* ln_w[DSDF_MAX_LAYERS];
+  float* ln_b[DSDF_MAX_LAYERS];
+} dsdf_param_grads;
+
+int dsdf_abi_version(void);
+const char* dsdf_last_error(void);
+/* 0 if the current CUDA device is sm_100; error otherwise (used by the Python side to fail loudly). */
+int dsdf_check_device(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Dropout: Philox4x32-10, counter (row, layer, col/16), key seed; keep iff byte >= round(p*256).
+ * Writes the {0,1} keep mask of one hidden layer as uint8 [n_rows, width] (tests / oracle hand-over). */
+int dsdf_dropout_mask(uint64_t seed, uint32_t layer, uint64_t row0, int64_t n_rows, int32_t width, float p,
+                      uint8_t* mask_out, void* stream);
+/* effective drop probability round(p*256)/256 actually applied (host function) */
+float dsdf_dropout_effective_p(float p);
+
+/* ------------------------------------------------------------------------------------------------
+ * Generic path: any NetworkSpecs (small nets, LayerNorm, xyz_in_all, geom_dim != 3).  fp32 CUDA-core kernels.
+ * forward:  input [N, L+D] fp32 -> out [N] fp32.  `save` != 0 keeps what backward needs inside `workspace`.
+ * backward: grad_out [N]; grad_input [N, L+D] or NULL; pgrads or NULL.  accumulate != 0 adds into pgrads. */
+size_t dsdf_generic_workspace_bytes(const dsdf_net_desc* desc, int64_t n_rows);
+int dsdf_generic_forward(const dsdf_net_desc* desc, const dsdf_params* params, const float* input, int64_t n_rows,
+                         int32_t training, uint64_t seed, uint64_t row0, float* out, void* workspace,
+                         size_t workspace_bytes, void* stream);
+int dsdf_generic_backward(const dsdf_net_desc* desc, const dsdf_params* params, const float* input, int64_t n_rows,
+                          int32_t training, uint64_t seed, uint64_t row0, const float* grad_out, float* grad_input,
+                          const dsdf_param_grads* pgrads, int32_t accumulate, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Fused tcgen05 path (hidden width 512, weight-norm or plain layers, one latent_in layer, geom_dim 3).
+ *
+ * Scene mode: every 128-row tile of points belongs to ONE scene, so the latent columns of lin0 and of the
+ * latent_in layer collapse into a per-scene bias vector (dsdf_scene_prepare) and are never materialised per row.
+ *   pack       caller buffer of dsdf_pack_bytes(), 1024-byte aligned; rebuilt by dsdf_pack_weights whenever the
+ *              parameters change (fold g*v/||v||, bf16 pack of W and W^T, fp32 side tables).
+ *   cbias      [n_scenes][2][512] fp32, written by dsdf_scene_prepare
+ *   tile_scene [ceil(n_rows/128)] int32: row of cbias each tile uses
+ */
+typedef struct dsdf_train_io {
+  const float* b_last;     /* device pointer to the last layer's bias [1] (always required) */
+  int32_t training;        /* 1: dropout on, masks/activations/loss outputs below are honoured */
+  uint64_t seed;           /* Philox key */
+  uint64_t row0;           /* global row id of local row 0 (dropout stream is keyed by global row) */
+  const float* gt;         /* [n_rows] ground-truth SDF or NULL */
+  float clamp;             /* ClampingDistance; <= 0 disables clamping */
+  float inv_n;             /* 1 / (global batch rows): loss normaliser, train_deep_sdf.py:519 */
+  float* dy_out;           /* [n_rows_pad] dL/d(pre-tanh output) */
+  float* tile_loss;        /* [n_tiles] sum |pred - gt| per tile (not yet divided by N) */
+  uint32_t* bitmask;       /* [num_hidden][n_rows_pad][16] relu*dropout keep bits, or NULL */
+  void* acts;              /* bf16 [num_hidden][n_rows_pad][512] post-activation stash for wgrad, or NULL */
+  int64_t n_rows_pad;      /* n_rows rounded up to a multiple of 128 */
+} dsdf_train_io;
+
+int dsdf_fused_supported(const dsdf_net_desc* desc);
+size_t dsdf_pack_bytes(const dsdf_net_desc* desc);
+int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, void* stream);
+/* nn.Embedding(max_norm) renorm of the listed rows (in place, max_norm <= 0: off) + per-scene bias vectors. */
+int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, float* lat_table, const int64_t* scene_ids,
+                       int32_t n_scenes, float max_norm, float* cbias, void* stream);
+int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const float* cbias, const int32_t* tile_scene,
+                       const float* xyz, int64_t n_rows, float* sdf_out, const dsdf_train_io* io, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * tcgen05 bring-up self test (see csrc/selftest.cu). */
+int dsdf_selftest_umma(int mode, const void* A, const void* B, float* C, void* A_store_out, int K, int N,
+                       unsigned a_lbo, unsigned a_sbo, unsigned b_lbo, unsigned b_sbo, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSDF_B200_H */
