@@ -78,4 +78,21 @@ struct BwdArgs {
   int32_t store_dys;
 };
 
+constexpr int WG_MAX_SLABS = 64;
+struct WgradSlab {
+  int32_t dy_layer;     // region of the dY stash (hidden layer index l)
+  int32_t x_layer;      // region of the activation stash (= l-1: the input of lin{l})
+  int32_t m0;           // first output feature of the 128-row slab
+  int32_t n;            // input features covered (256 or 512)
+  int32_t splits;       // row-range splits (CTAs) of this slab
+  int32_t first_cta;
+  int64_t part_offset;  // float offset of this slab's partials [splits][128][n]
+};
+struct WgradArgs {
+  int32_t n_slabs;
+  int64_t n_rows_pad;
+  float* partials;
+  WgradSlab slab[WG_MAX_SLABS];
+};
+
 }  // namespace dsdf

@@ -283,7 +283,7 @@ extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, c
   a.use_tanh = desc->use_tanh;
   a.training = tr->training;
   a.drop_thr = dropout_threshold(desc->dropout_prob);
-  a.drop_scale = 1.0f / (1.0f - float(a.drop_thr) / 256.0f);
+  a.drop_scale = 1.0f / (1.0f - desc->dropout_prob);   // F.dropout scaling with the nominal p
   a.seed = tr->seed;
   a.row0 = tr->row0;
   a.gt = tr->gt;

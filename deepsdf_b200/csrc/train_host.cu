@@ -1,0 +1,219 @@
+// C-ABI wrappers of the fused training step: buffer sizing, dgrad chain, wgrad, finish (reductions + weight-norm
+// backward + latent gradient + loss) and Adam.
+#include "train_kernels.cuh"
+#include "host_util.h"
+
+namespace dsdf {
+
+int launch_fused_dgrad(const CUtensorMap& tmW, const CUtensorMap& tmDys, const BwdArgs& args, int grid, cudaStream_t stream);
+int launch_wgrad(const CUtensorMap& tmDys, const CUtensorMap& tmActs, const WgradArgs& args, int grid, cudaStream_t stream);
+int launch_wgrad_last(const void* x_last, const float* dy, int64_t n_rows_pad, float* part, int n_blocks, cudaStream_t stream);
+
+namespace {
+
+constexpr int kPlanCtas = 148;        // the split plan is fixed (not device dependent) so results are reproducible
+constexpr int kLastBlocks = 148;
+
+struct WgradPlan {
+  int n_slabs;
+  int n_ctas;
+  WgradSlab slab[WG_MAX_SLABS];
+  int32_t slab_of[DSDF_MAX_LAYERS][4];
+  size_t total_floats;
+};
+
+int build_plan(const dsdf_net_desc* d, const FusedLayout& lo, WgradPlan* p) {
+  memset(p, 0, sizeof(*p));
+  for (int l = 0; l < DSDF_MAX_LAYERS; ++l) for (int m = 0; m < 4; ++m) p->slab_of[l][m] = -1;
+  // cost units: a 512-wide slab = 2, a 256-wide slab = 1
+  int units = 0, n = 0;
+  for (int l = 1; l < lo.num_hidden; ++l) {
+    const int mblocks = (d->out_dim[l] + 127) / 128;
+    for (int mb = 0; mb < mblocks; ++mb) {
+      if (n >= WG_MAX_SLABS) return set_error("too many wgrad slabs");
+      WgradSlab& s = p->slab[n];
+      s.dy_layer = l; s.x_layer = l - 1; s.m0 = mb * 128; s.n = lo.bwd_halves[l] * HALF_N;
+      units += s.n / 256;
+      p->slab_of[l][mb] = n++;
+    }
+  }
+  p->n_slabs = n;
+  int per_unit = units > 0 ? kPlanCtas / units : 1;
+  if (per_unit < 1) per_unit = 1;
+  int cta = 0; size_t off = 0;
+  for (int i = 0; i < n; ++i) {
+    WgradSlab& s = p->slab[i];
+    s.splits = per_unit * (s.n / 256);
+    s.first_cta = cta; cta += s.splits;
+    s.part_offset = int64_t(off);
+    off += size_t(s.splits) * 128 * s.n;
+  }
+  p->n_ctas = cta;
+  p->total_floats = off;
+  return 0;
+}
+
+inline int n_slots(const FusedLayout& lo) { return lo.num_hidden + 6; }
+
+}  // namespace
+}  // namespace dsdf
+
+using namespace dsdf;
+
+// sizes[]: 0 acts, 1 dys, 2 bitmask, 3 dy, 4 tile_loss, 5 tile_part, 6 wg_part, 7 last_part, 8 scene_sums (+scene_reg), 9 cbias
+extern "C" int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, int32_t n_scenes, size_t* sizes) {
+  FusedLayout lo;
+  if (int e = fused_layout(desc, &lo)) return e;
+  WgradPlan plan;
+  if (int e = build_plan(desc, lo, &plan)) return e;
+  const int64_t n_tiles = (n_rows + TILE_M - 1) / TILE_M, n_pad = n_tiles * TILE_M;
+  const size_t nh = lo.num_hidden;
+  sizes[0] = nh * n_pad * FH * 2;
+  sizes[1] = nh * n_pad * FH * 2;
+  sizes[2] = nh * n_pad * MASK_WORDS * 4;
+  sizes[3] = size_t(n_pad) * 4;
+  sizes[4] = size_t(n_tiles) * 4;
+  sizes[5] = size_t(n_tiles) * n_slots(lo) * FH * 4;
+  sizes[6] = plan.total_floats * 4;
+  sizes[7] = size_t(kLastBlocks) * (FH + 1) * 4;
+  sizes[8] = (size_t(n_scenes) * n_slots(lo) * FH + size_t(n_scenes)) * 4;
+  sizes[9] = size_t(n_scenes) * 2 * FH * 4;
+  return 0;
+}
+
+extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, const dsdf_train_bufs* bufs, const float* xyz,
+                                int64_t n_rows, int32_t training, void* stream) {
+  if (int e = require_sm100()) return e;
+  FusedLayout lo;
+  if (int e = fused_layout(desc, &lo)) return e;
+  DSDF_REQUIRE(n_rows > 0 && n_rows % TILE_M == 0, "fused training needs n_rows to be a positive multiple of 128");
+  const uint8_t* p = static_cast<const uint8_t*>(pack);
+  BwdArgs a;
+  memset(&a, 0, sizeof(a));
+  ChainLayer fwd_unused[DSDF_MAX_LAYERS];
+  {
+    // same program builder as the forward (fused_host.cu keeps it static); rebuild the backward half here
+    for (int l = 0; l < lo.num_hidden; ++l) {
+      ChainLayer& B = a.prog[l];
+      B.has_mma = (l > 0); B.w_row0 = lo.bwd_row0[l]; B.n_halves = lo.bwd_halves[l]; B.k_chunks = lo.bwd_kchunks[l];
+      B.bias_slot = -1; B.has_xyz = (l == 0 || l == lo.lat_layer); B.dropout = (desc->dropout_mask >> l) & 1;
+      B.out_dim = desc->out_dim[l];
+    }
+    (void)fwd_unused;
+  }
+  a.num_hidden = lo.num_hidden;
+  a.n_rows = n_rows;
+  a.n_tiles = int(n_rows / TILE_M);
+  a.n_rows_pad = n_rows;
+  a.w_last = reinterpret_cast<const float*>(p + lo.off_wlast);
+  a.dy = bufs->dy;
+  a.bitmask = bufs->bitmask;
+  const float sc = 1.0f / (1.0f - desc->dropout_prob);
+  for (int l = 0; l < lo.num_hidden; ++l) {
+    a.scale[l] = (training && ((desc->dropout_mask >> l) & 1)) ? sc : 1.0f;
+    a.colsum_slot[l] = l;
+    a.xyzsum_slot[l] = (l == 0) ? lo.num_hidden : (l == lo.lat_layer ? lo.num_hidden + 3 : -1);
+  }
+  a.xyz = xyz;
+  a.tile_part = bufs->tile_part;
+  a.part_stride = n_slots(lo) * FH;
+  a.store_dys = 1;
+  CUtensorMap tmW, tmDys;
+  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wpt, FH, lo.bwd_rows, FH * 2, 64, HALF_N)) return e;
+  if (int e = make_tmap_bf16_2d(&tmDys, bufs->dys, FH, uint64_t(lo.num_hidden) * n_rows, FH * 2, 64, TILE_M)) return e;
+  int grid = sm_count();
+  if (grid > a.n_tiles) grid = a.n_tiles;
+  return launch_fused_dgrad(tmW, tmDys, a, grid, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs* bufs, int64_t n_rows, void* stream) {
+  if (int e = require_sm100()) return e;
+  FusedLayout lo;
+  if (int e = fused_layout(desc, &lo)) return e;
+  DSDF_REQUIRE(n_rows > 0 && n_rows % TILE_M == 0, "fused training needs n_rows to be a positive multiple of 128");
+  WgradPlan plan;
+  if (int e = build_plan(desc, lo, &plan)) return e;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  WgradArgs a;
+  memset(&a, 0, sizeof(a));
+  a.n_slabs = plan.n_slabs;
+  a.n_rows_pad = n_rows;
+  a.partials = bufs->wg_part;
+  memcpy(a.slab, plan.slab, sizeof(plan.slab));
+  CUtensorMap tmDys, tmActs;
+  const uint64_t rows = uint64_t(lo.num_hidden) * n_rows;
+  if (int e = make_tmap_bf16_2d(&tmDys, bufs->dys, FH, rows, FH * 2, 64, 32)) return e;
+  if (int e = make_tmap_bf16_2d(&tmActs, bufs->acts, FH, rows, FH * 2, 64, 32)) return e;
+  if (int e = launch_wgrad(tmDys, tmActs, a, plan.n_ctas, st)) return e;
+  const uint8_t* x_last = static_cast<const uint8_t*>(bufs->acts) + size_t(lo.num_hidden - 1) * n_rows * FH * 2;
+  return launch_wgrad_last(x_last, bufs->dy, n_rows, bufs->last_part, kLastBlocks, st);
+}
+
+extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
+                                 const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows,
+                                 const float* lat_table, const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total,
+                                 float reg_lambda_eff, float inv_n, const dsdf_param_grads* pgrads, float* lat_grad,
+                                 float* loss_out, void* stream) {
+  if (int e = require_sm100()) return e;
+  FinishArgs a;
+  memset(&a, 0, sizeof(a));
+  if (int e = fused_layout(desc, &a.lo)) return e;
+  WgradPlan plan;
+  if (int e = build_plan(desc, a.lo, &plan)) return e;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  a.desc = *desc;
+  a.params = *params;
+  a.grads = *pgrads;
+  a.pack = static_cast<const uint8_t*>(pack);
+  a.tile_part = bufs->tile_part;
+  a.tile_scene = tile_scene;
+  a.n_tiles = int(n_rows / TILE_M);
+  a.n_slots = n_slots(a.lo);
+  a.n_scenes = n_scenes;
+  a.scene_sums = bufs->scene_sums;
+  a.scene_reg = bufs->scene_sums + size_t(n_scenes) * a.n_slots * FH;
+  a.wg_part = bufs->wg_part;
+  memcpy(a.slab_of, plan.slab_of, sizeof(plan.slab_of));
+  memcpy(a.slab, plan.slab, sizeof(plan.slab));
+  a.last_part = bufs->last_part;
+  a.n_last_blocks = kLastBlocks;
+  a.lat_table = lat_table;
+  a.scene_ids = scene_ids;
+  a.lat_grad = lat_grad;
+  a.reg_scale = reg_lambda_eff * inv_n;
+  a.inv_n = inv_n;
+  a.tile_loss = bufs->tile_loss;
+  a.loss_out = loss_out;
+  a.xyz_slot0 = a.lo.num_hidden;
+  for (int l = 0; l < desc->num_linear; ++l) {
+    DSDF_REQUIRE(pgrads->v[l] && pgrads->b[l], "missing gradient pointers");
+    if ((desc->weight_norm_mask >> l) & 1) DSDF_REQUIRE(pgrads->g[l] && params->g[l], "missing g pointers");
+  }
+  scene_sums_kernel<<<dim3(n_scenes, a.n_slots), FH, 0, st>>>(a.tile_part, tile_scene, a.n_tiles, a.n_slots, a.scene_sums);
+  if (lat_grad) {
+    DSDF_CHECK_CUDA(cudaMemsetAsync(lat_grad, 0, size_t(n_scenes_total) * desc->latent_size * sizeof(float), st));
+    latent_grad_kernel<<<n_scenes, 256, 0, st>>>(a);
+  }
+  int max_out = 0;
+  for (int l = 0; l < desc->num_linear; ++l) max_out = desc->out_dim[l] > max_out ? desc->out_dim[l] : max_out;
+  assemble_grads_kernel<<<dim3(max_out, desc->num_linear), 128, 0, st>>>(a);
+  if (loss_out) {
+    DSDF_REQUIRE(lat_grad || reg_lambda_eff == 0.f, "loss with regulariser needs the latent-grad pass");
+    loss_kernel<<<1, 256, 0, st>>>(a);
+  }
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dsdf_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
+                         int32_t step, float grad_scale, void* stream) {
+  if (int e = require_sm100()) return e;
+  if (n <= 0) return 0;
+  DSDF_REQUIRE(step >= 1, "Adam step counter starts at 1");
+  const float bc1 = float(1.0 - pow(double(beta1), double(step)));
+  const float bc2 = float(1.0 - pow(double(beta2), double(step)));
+  adam_kernel<<<unsigned((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1,
+                                                                                       sqrtf(bc2), grad_scale);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

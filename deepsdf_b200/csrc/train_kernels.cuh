@@ -1,0 +1,174 @@
+// Small fp32 kernels that close the fused training step: deterministic reductions of the per-tile / per-split partials,
+// assembly of the effective-weight gradient, weight-norm backward, latent-code gradient (+ code regulariser), loss, Adam.
+// Replaces train_deep_sdf.py:519-533 (loss assembly, regulariser) and :545 (optimizer_all.step()).
+#pragma once
+#include "common.cuh"
+#include "fused.cuh"
+#include "fused_host.h"
+
+namespace dsdf {
+
+struct FinishArgs {
+  dsdf_net_desc desc;
+  FusedLayout lo;
+  dsdf_params params;
+  dsdf_param_grads grads;
+  const uint8_t* pack;
+  const float* tile_part;       // [n_tiles][n_slots][512]
+  const int32_t* tile_scene;    // [n_tiles]
+  int32_t n_tiles, n_slots, n_scenes;
+  float* scene_sums;            // [S][n_slots][512]
+  float* scene_reg;             // [S] rows_s * ||z_s|| (written by latent_grad_kernel)
+  const float* wg_part;         // wgrad partials
+  int32_t slab_of[DSDF_MAX_LAYERS][4];     // slab index of (layer, m-block) or -1
+  WgradSlab slab[WG_MAX_SLABS];
+  const float* last_part;       // [n_last_blocks][513]
+  int32_t n_last_blocks;
+  const float* lat_table;       // [S_total][L]
+  const int64_t* scene_ids;     // [S]
+  float* lat_grad;              // [S_total][L] dense
+  float reg_scale;              // lambda * min(1, epoch/100) * inv_n   (0: no regulariser)
+  float inv_n;
+  const float* tile_loss;       // [n_tiles]
+  float* loss_out;              // [2]: total loss, data term
+  int32_t xyz_slot0;            // first xyz-sum slot of lin0 (3 slots), skip layer follows (+3)
+};
+
+// scene_sums[s][slot][c] = sum over the tiles of scene s (ascending tile order) of tile_part[tile][slot][c]
+__global__ void __launch_bounds__(FH) scene_sums_kernel(const float* __restrict__ tile_part, const int32_t* __restrict__ tile_scene,
+                                                        int n_tiles, int n_slots, float* __restrict__ scene_sums) {
+  const int s = blockIdx.x, slot = blockIdx.y, c = threadIdx.x;
+  float acc = 0.f;
+  for (int t = 0; t < n_tiles; ++t)
+    if (__ldg(tile_scene + t) == s) acc += __ldg(tile_part + (size_t(t) * n_slots + slot) * FH + c);
+  scene_sums[(size_t(s) * n_slots + slot) * FH + c] = acc;
+}
+
+// One block per (output row o, layer l): assemble dW_eff[o, :], then weight-norm backward (or plain copy) and bias grad.
+__global__ void __launch_bounds__(128) assemble_grads_kernel(const __grid_constant__ FinishArgs a) {
+  const int l = blockIdx.y, o = blockIdx.x;
+  const dsdf_net_desc& d = a.desc;
+  if (o >= d.out_dim[l]) return;
+  const int in = d.in_dim[l], nh = a.lo.num_hidden, L = d.latent_size, S = a.n_scenes;
+  __shared__ float s_dw[FH + 8];
+  __shared__ float red[4];
+  __shared__ float s_dg;
+  const float* v = a.params.v[l] + size_t(o) * in;
+  float dot = 0.f;
+  for (int k = threadIdx.x; k < in; k += blockDim.x) {
+    float g = 0.f;
+    if (l == nh) {
+      for (int b = 0; b < a.n_last_blocks; ++b) g += a.last_part[size_t(b) * (FH + 1) + k];
+    } else if (k < a.lo.xw[l]) {
+      const WgradSlab& sl = a.slab[a.slab_of[l][o >> 7]];
+      const float* p = a.wg_part + sl.part_offset + size_t(o & 127) * sl.n + k;
+      for (int sp = 0; sp < sl.splits; ++sp) g += p[size_t(sp) * 128 * sl.n];
+    } else if (a.lo.lat_col0[l] >= 0 && k < a.lo.lat_col0[l] + L) {
+      const int kk = k - a.lo.lat_col0[l];
+      for (int s = 0; s < S; ++s)
+        g += a.scene_sums[(size_t(s) * a.n_slots + l) * FH + o] * a.lat_table[size_t(a.scene_ids[s]) * L + kk];
+    } else {
+      const int dd = k - a.lo.xyz_col0[l];
+      const int slot = a.xyz_slot0 + (l == 0 ? 0 : 3) + dd;
+      for (int s = 0; s < S; ++s) g += a.scene_sums[(size_t(s) * a.n_slots + slot) * FH + o];
+    }
+    s_dw[k] = g;
+    dot += g * v[k];
+  }
+  for (int off = 16; off > 0; off >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, off);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = dot;
+  __syncthreads();
+  const bool wn = (d.weight_norm_mask >> l) & 1;
+  const float invn = reinterpret_cast<const float*>(a.pack + a.lo.off_invn[l])[o];
+  if (threadIdx.x == 0) {
+    const float dg = ((red[0] + red[1]) + (red[2] + red[3])) * invn;
+    s_dg = dg;
+    if (wn) a.grads.g[l][o] = dg;
+    float db = 0.f;
+    if (l == nh) { for (int b = 0; b < a.n_last_blocks; ++b) db += a.last_part[size_t(b) * (FH + 1) + FH]; }
+    else { for (int s = 0; s < S; ++s) db += a.scene_sums[(size_t(s) * a.n_slots + l) * FH + o]; }
+    a.grads.b[l][o] = db;
+  }
+  __syncthreads();
+  float* dv = a.grads.v[l] + size_t(o) * in;
+  if (wn) {
+    const float gi = a.params.g[l][o] * invn, dg = s_dg;
+    for (int k = threadIdx.x; k < in; k += blockDim.x) dv[k] = gi * (s_dw[k] - v[k] * invn * dg);
+  } else {
+    for (int k = threadIdx.x; k < in; k += blockDim.x) dv[k] = s_dw[k];
+  }
+}
+
+// lat_grad[scene_ids[s]][k] = colsum_s(dY_0) . W0[:, k] + colsum_s(dY_skip) . Wskip[:, xw+k] + reg * rows_s * z/||z||
+// grid S, block 256 (8 warps; warp w handles k = w, w+8, ...; lanes stride the 512 outputs -> coalesced wlatT reads)
+__global__ void __launch_bounds__(256) latent_grad_kernel(const __grid_constant__ FinishArgs a) {
+  const int s = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int L = a.desc.latent_size;
+  const float* wlatT = reinterpret_cast<const float*>(a.pack + a.lo.off_wlatT);
+  const float* ss0 = a.scene_sums + (size_t(s) * a.n_slots + 0) * FH;
+  const float* ss1 = a.lo.lat_layer > 0 ? a.scene_sums + (size_t(s) * a.n_slots + a.lo.lat_layer) * FH : nullptr;
+  const float* z = a.lat_table + size_t(a.scene_ids[s]) * L;
+  __shared__ float s_norm;
+  __shared__ int s_rows;
+  if (warp == 0) {
+    float q = 0.f;
+    for (int k = lane; k < L; k += 32) q += z[k] * z[k];
+    for (int off = 16; off > 0; off >>= 1) q += __shfl_xor_sync(0xffffffffu, q, off);
+    int cnt = 0;
+    for (int t = lane; t < a.n_tiles; t += 32) cnt += (a.tile_scene[t] == s);
+    for (int off = 16; off > 0; off >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+    if (lane == 0) { s_norm = sqrtf(q); s_rows = cnt * TILE_M; a.scene_reg[s] = sqrtf(q) * float(cnt * TILE_M); }
+  }
+  __syncthreads();
+  for (int k = warp; k < L; k += 8) {
+    float acc = 0.f;
+    for (int o = lane; o < FH; o += 32) {
+      acc += ss0[o] * wlatT[size_t(k) * FH + o];
+      if (ss1) acc += ss1[o] * wlatT[(size_t(L) + k) * FH + o];
+    }
+    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    if (lane == 0) {
+      if (a.reg_scale != 0.f && s_norm > 0.f) acc += a.reg_scale * float(s_rows) * z[k] / s_norm;
+      a.lat_grad[size_t(a.scene_ids[s]) * L + k] = acc;
+    }
+  }
+}
+
+// loss_out[0] = inv_n * sum(tile_loss) + reg ; loss_out[1] = data term.  Single block, fixed summation order.
+__global__ void __launch_bounds__(256) loss_kernel(const __grid_constant__ FinishArgs a) {
+  __shared__ float red[256];
+  float acc = 0.f;
+  for (int t = threadIdx.x; t < a.n_tiles; t += 256) acc += a.tile_loss[t];
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const float data = red[0] * a.inv_n;
+    float reg = 0.f;
+    if (a.reg_scale != 0.f) {
+      for (int s = 0; s < a.n_scenes; ++s) reg += a.scene_reg[s];
+      reg *= a.reg_scale;
+    }
+    a.loss_out[0] = data + reg;
+    a.loss_out[1] = data;
+  }
+}
+
+// torch.optim.Adam (no weight decay, no amsgrad), one flat tensor.  step >= 1.
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n,
+                            float lr, float beta1, float beta2, float eps, float bc1, float bc2_sqrt, float grad_scale) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float gi = g[i] * grad_scale;
+  const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+  const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+  m[i] = mi;
+  v[i] = vi;
+  const float denom = sqrtf(vi) / bc2_sqrt + eps;
+  p[i] -= (lr / bc1) * (mi / denom);
+}
+
+}  // namespace dsdf

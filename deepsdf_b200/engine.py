@@ -1,0 +1,192 @@
+"""Host-side driver of the fused (tcgen05) scene-mode path.
+
+``FusedEngine`` wraps a drop-in ``Decoder`` whose NetworkSpecs the fused kernels support (8x512 class) and exposes
+the calls the build's trainer / grid evaluator / latent optimiser use:
+
+  * ``repack()``                      fold weight-norm + bf16 pack (once per parameter update)
+  * ``decode_scenes(...)``            SDF of points grouped in 128-row scene-aligned tiles (eval or train mode)
+  * ``loss_and_grads(...)``           one training step's loss and gradients (train_deep_sdf.py:483-533)
+
+All compute is in the C-ABI library; this file only allocates tensors and sequences the calls on the current stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from . import _lib as L
+from .networks.deep_sdf_decoder import Decoder
+
+TILE = 128
+
+
+class TrainBufs(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("acts", "dys", "bitmask", "dy", "tile_loss", "tile_part", "wg_part", "last_part",
+                                           "scene_sums")]
+
+
+def _declare_train(lib) -> None:
+    if getattr(lib, "_dsdf_train_declared", False):
+        return
+    vp, i32, i64, f32, sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
+    P = C.POINTER
+    lib.dsdf_train_buf_sizes.restype = C.c_int
+    lib.dsdf_train_buf_sizes.argtypes = [P(L.NetDesc), i64, i32, P(sz)]
+    lib.dsdf_fused_dgrad.restype = C.c_int
+    lib.dsdf_fused_dgrad.argtypes = [P(L.NetDesc), vp, P(TrainBufs), vp, i64, i32, vp]
+    lib.dsdf_fused_wgrad.restype = C.c_int
+    lib.dsdf_fused_wgrad.argtypes = [P(L.NetDesc), P(TrainBufs), i64, vp]
+    lib.dsdf_fused_finish.restype = C.c_int
+    lib.dsdf_fused_finish.argtypes = [P(L.NetDesc), vp, P(L.Params), P(TrainBufs), vp, i64, vp, vp, i32, i64, f32, f32,
+                                      P(L.ParamGrads), vp, vp, vp]
+    lib.dsdf_adam.restype = C.c_int
+    lib.dsdf_adam.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp]
+    lib._dsdf_train_declared = True
+
+
+class FusedEngine:
+    def __init__(self, decoder: Decoder):
+        self.lib = L.lib()
+        _declare_train(self.lib)
+        self.decoder = decoder
+        self.spec = decoder.spec
+        self.desc = decoder._desc
+        if self.lib.dsdf_fused_supported(C.byref(self.desc)) != 1:
+            raise L.DsdfError("this NetworkSpecs is not supported by the fused tcgen05 path (needs 8x512-class dims); "
+                              "use Decoder.forward (generic path)")
+        p0 = next(decoder.parameters())
+        L.require_cuda(p0)
+        self.device = p0.device
+        with torch.cuda.device(self.device):
+            L.check(self.lib.dsdf_check_device())
+        nbytes = self.lib.dsdf_pack_bytes(C.byref(self.desc))
+        raw = torch.zeros(nbytes + 1024, dtype=torch.uint8, device=self.device)
+        off = (-raw.data_ptr()) % 1024
+        self._pack_raw = raw
+        self.pack = raw[off:off + nbytes]
+        self.num_hidden = self.spec.num_linear - 1
+        self._bufs_key = None
+        self._bufs: Dict[str, torch.Tensor] = {}
+        self.repack()
+
+    # ------------------------------------------------------------------ weights
+    def _st(self) -> int:
+        return L.stream_ptr(self.device)
+
+    def repack(self) -> None:
+        """Fold g*v/||v|| and rebuild the bf16 operand packs from the decoder's *current* parameters."""
+        self._P = self.decoder.c_params()
+        with torch.cuda.device(self.device):
+            L.check(self.lib.dsdf_pack_weights(C.byref(self.desc), C.byref(self._P), self.pack.data_ptr(), self._st()))
+
+    def _b_last(self) -> torch.Tensor:
+        return getattr(self.decoder, "lin" + str(self.spec.num_linear - 1)).bias
+
+    # ------------------------------------------------------------------ scenes
+    def scene_bias(self, lat_table: torch.Tensor, scene_ids: torch.Tensor, max_norm: Optional[float] = None,
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Per-scene bias vectors [S, 2, 512]; applies nn.Embedding(max_norm) renorm to the listed rows in place."""
+        L.require_cuda(lat_table, scene_ids)
+        assert lat_table.dtype == torch.float32 and lat_table.is_contiguous() and lat_table.shape[1] == self.spec.latent_size
+        assert scene_ids.dtype == torch.int64 and scene_ids.is_contiguous()
+        S = scene_ids.numel()
+        cb = out if out is not None else torch.empty(S, 2, 512, device=self.device)
+        with torch.cuda.device(self.device):
+            L.check(self.lib.dsdf_scene_prepare(C.byref(self.desc), self.pack.data_ptr(), lat_table.data_ptr(),
+                                                scene_ids.data_ptr(), S, float(max_norm or 0.0), cb.data_ptr(), self._st()))
+        return cb
+
+    def decode_scenes(self, cbias: torch.Tensor, tile_scene: torch.Tensor, xyz: torch.Tensor,
+                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Eval-mode SDF [N] of xyz [N,3]; rows [128*t, 128*t+128) use scene row ``tile_scene[t]`` of ``cbias``."""
+        L.require_cuda(cbias, tile_scene, xyz)
+        N = xyz.shape[0]
+        assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.shape[1] == 3
+        assert tile_scene.dtype == torch.int32 and tile_scene.numel() == (N + TILE - 1) // TILE
+        sdf = out if out is not None else torch.empty(N, device=self.device)
+        io = L.TrainIO()
+        io.b_last = self._b_last().data_ptr()
+        io.training = 0
+        with torch.cuda.device(self.device):
+            L.check(self.lib.dsdf_fused_forward(C.byref(self.desc), self.pack.data_ptr(), cbias.data_ptr(), tile_scene.data_ptr(),
+                                                xyz.data_ptr(), N, sdf.data_ptr(), C.byref(io), self._st()))
+        return sdf
+
+    # ------------------------------------------------------------------ training
+    def train_buffers(self, n_rows: int, n_scenes: int) -> Dict[str, torch.Tensor]:
+        key = (n_rows, n_scenes)
+        if self._bufs_key == key:
+            return self._bufs
+        sizes = (C.c_size_t * 10)()
+        L.check(self.lib.dsdf_train_buf_sizes(C.byref(self.desc), n_rows, n_scenes, sizes))
+        names = ["acts", "dys", "bitmask", "dy", "tile_loss", "tile_part", "wg_part", "last_part", "scene_sums", "cbias"]
+        self._bufs = {}
+        for n, s in zip(names, sizes):
+            self._bufs[n] = torch.empty(max(int(s), 16), dtype=torch.uint8, device=self.device)
+        self._bufs["sdf"] = torch.empty(n_rows, device=self.device)
+        self._bufs["loss"] = torch.zeros(2, device=self.device)
+        tb = TrainBufs()
+        for n in names[:9]:
+            setattr(tb, n, self._bufs[n].data_ptr())
+        self._tb = tb
+        self._bufs_key = key
+        return self._bufs
+
+    def alloc_grads(self) -> Tuple[List[torch.Tensor], L.ParamGrads]:
+        """Gradient tensors in the order of ``decoder.flat_param_list()`` + the C struct pointing at them."""
+        grads = [torch.zeros_like(p) for p in self.decoder.flat_param_list()]
+        return grads, self.grads_struct(grads)
+
+    def grads_struct(self, grads: List[torch.Tensor]) -> L.ParamGrads:
+        PG = L.ParamGrads()
+        it = iter(grads)
+        for layer in range(self.spec.num_linear):
+            for name, t in zip(("v", "g", "b", "ln_w", "ln_b"), self.decoder.layer_tensors(layer)):
+                if t is not None:
+                    getattr(PG, name)[layer] = next(it).data_ptr()
+        return PG
+
+    def loss_and_grads(self, lat_table: torch.Tensor, scene_ids: torch.Tensor, tile_scene: torch.Tensor, xyz: torch.Tensor,
+                       gt: torch.Tensor, *, clamp: float, reg_lambda_eff: float, n_total: int, code_bound: Optional[float],
+                       seed: int, row0: int, PG: L.ParamGrads, lat_grad: torch.Tensor, training: bool = True) -> torch.Tensor:
+        """train_deep_sdf.py:483-533 for one (local) batch: returns the 2-element loss tensor (total, data term); fills
+        the decoder gradients behind ``PG`` and the dense latent gradient ``lat_grad`` [S_total, L].
+        ``n_total`` is the GLOBAL batch size (loss normaliser, :519)."""
+        N = xyz.shape[0]
+        if N % TILE:
+            raise L.DsdfError("fused training needs a multiple of 128 rows (SamplesPerScene % 128 == 0)")
+        S = scene_ids.numel()
+        b = self.train_buffers(N, S)
+        tb = self._tb
+        cb = self.scene_bias(lat_table, scene_ids, code_bound, out=b["cbias"].view(torch.float32)[:S * 1024].view(S, 2, 512))
+        io = L.TrainIO()
+        io.b_last = self._b_last().data_ptr()
+        io.training = int(training)
+        io.seed = seed
+        io.row0 = row0
+        io.gt = gt.data_ptr()
+        io.clamp = float(clamp or 0.0)
+        io.inv_n = 1.0 / float(n_total)
+        io.dy_out = b["dy"].data_ptr()
+        io.tile_loss = b["tile_loss"].data_ptr()
+        io.bitmask = b["bitmask"].data_ptr()
+        io.acts = b["acts"].data_ptr()
+        io.n_rows_pad = N
+        lib, desc, st = self.lib, self.desc, self._st()
+        with torch.cuda.device(self.device):
+            L.check(lib.dsdf_fused_forward(C.byref(desc), self.pack.data_ptr(), cb.data_ptr(), tile_scene.data_ptr(), xyz.data_ptr(),
+                                           N, b["sdf"].data_ptr(), C.byref(io), st))
+            L.check(lib.dsdf_fused_dgrad(C.byref(desc), self.pack.data_ptr(), C.byref(tb), xyz.data_ptr(), N, int(training), st))
+            L.check(lib.dsdf_fused_wgrad(C.byref(desc), C.byref(tb), N, st))
+            L.check(lib.dsdf_fused_finish(C.byref(desc), self.pack.data_ptr(), C.byref(self._P), C.byref(tb), tile_scene.data_ptr(), N,
+                                          lat_table.data_ptr(), scene_ids.data_ptr(), S, lat_table.shape[0], float(reg_lambda_eff),
+                                          1.0 / float(n_total), C.byref(PG), lat_grad.data_ptr(), b["loss"].data_ptr(), st))
+        return b["loss"]
+
+    def adam(self, p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int, lr: float,
+             grad_scale: float = 1.0, betas=(0.9, 0.999), eps: float = 1e-8) -> None:
+        with torch.cuda.device(self.device):
+            L.check(self.lib.dsdf_adam(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), float(lr), betas[0], betas[1],
+                                       eps, int(step), float(grad_scale), self._st()))

@@ -127,6 +127,43 @@ int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const float*
                        const float* xyz, int64_t n_rows, float* sdf_out, const dsdf_train_io* io, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Fused training step (scene mode).  All buffers are caller-owned device memory; dsdf_train_buf_sizes() fills
+ * sizes[10] (bytes) in the order of the struct members below (+ sizes[9] = cbias).  n_rows must be a multiple of 128
+ * and every 128-row tile must belong to one scene (SamplesPerScene % 128 == 0: 16384 and 16000 both are).
+ *   forward (training=1, gt given)  -> sdf, dy, tile_loss, bitmask, acts
+ *   dsdf_fused_dgrad                -> dys (bf16 dY per hidden layer), tile_part (per-tile column sums)
+ *   dsdf_fused_wgrad                -> wg_part (split-K partials of dW), last_part (last layer)
+ *   dsdf_fused_finish               -> parameter grads in the reference layout (dg, dv, db), dense latent grad
+ *                                      [n_scenes_total, L] (zeroed, rows of scene_ids written; scene_ids must be
+ *                                      unique within a batch), loss_out[0] = loss incl. regulariser, [1] = data term.
+ *                                      reg_lambda_eff = CodeRegularizationLambda * min(1, epoch/100) or 0.
+ * Every reduction has a fixed order: two runs on the same inputs give bit-identical gradients. */
+typedef struct dsdf_train_bufs {
+  void* acts;            /* bf16 [num_hidden][n_rows][512] */
+  void* dys;             /* bf16 [num_hidden][n_rows][512] */
+  uint32_t* bitmask;     /* [num_hidden][n_rows][16] */
+  float* dy;             /* [n_rows] */
+  float* tile_loss;      /* [n_rows/128] */
+  float* tile_part;      /* [n_rows/128][num_hidden+6][512] */
+  float* wg_part;
+  float* last_part;
+  float* scene_sums;
+} dsdf_train_bufs;
+
+int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, int32_t n_scenes, size_t* sizes);
+int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, const dsdf_train_bufs* bufs, const float* xyz,
+                     int64_t n_rows, int32_t training, void* stream);
+int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs* bufs, int64_t n_rows, void* stream);
+int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
+                      const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows, const float* lat_table,
+                      const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total, float reg_lambda_eff,
+                      float inv_n, const dsdf_param_grads* pgrads, float* lat_grad, float* loss_out, void* stream);
+/* torch.optim.Adam update of one flat fp32 tensor (dense, no weight decay); step counts from 1; g is multiplied by
+ * grad_scale first (e.g. gradient clipping). */
+int dsdf_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
+              int32_t step, float grad_scale, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * tcgen05 bring-up self test (see csrc/selftest.cu). */
 int dsdf_selftest_umma(int mode, const void* A, const void* B, float* C, void* A_store_out, int K, int N,
                        unsigned a_lbo, unsigned a_sbo, unsigned b_lbo, unsigned b_sbo, void* stream);

@@ -1,0 +1,189 @@
+"""GPU parity of the drop-in Decoder (generic fp32 CUDA path, through the C ABI) against the golden vectors of the
+REAL reference and against the CPU oracle.  Tolerances: fp32 path, 1e-5 abs on SDF, 1e-4 relative on gradients."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from deepsdf_b200 import _lib as L
+from oracle import decoder_oracle as O
+from tests.util import GOLDEN, build_module, load_cases
+
+pytestmark = pytest.mark.gpu
+META, BLOB = load_cases()
+DEV = "cuda:0"
+
+
+def _inputs(name):
+    m = META[name]
+    pre = name + "::"
+    table = torch.from_numpy(BLOB[pre + "table"].copy())
+    rows = torch.from_numpy(np.repeat(BLOB[pre + "scenes"], m["sps"])).long()
+    xyz = torch.from_numpy(BLOB[pre + "xyz"])
+    gt = torch.from_numpy(BLOB[pre + "gt"])
+    return m, pre, table, rows, xyz, gt
+
+
+def test_reference_export_outputs():
+    """The reference's own trained + exported 4x64 network: identical outputs (fp32 path)."""
+    z = np.load(os.path.join(GOLDEN, "small_net_export.npz"))
+    params = {k[len("param::"):]: torch.from_numpy(z[k]) for k in z.files if k.startswith("param::")}
+    mod = build_module(META["small_4x64_L2_tanh"]["spec"], params, DEV).eval()
+    with torch.no_grad():
+        y = mod(torch.from_numpy(z["input"]).to(DEV)).cpu().numpy()
+    assert np.abs(y - z["output"]).max() <= 1e-5
+
+
+@pytest.mark.parametrize("name", sorted(META))
+def test_eval_forward_and_input_grad(name):
+    m, pre, table, rows, xyz, gt = _inputs(name)
+    ospec = O.OracleSpec(**m["spec"])
+    params = O.make_params(ospec, m["seed"])
+    mod = build_module(m["spec"], params, DEV).eval()
+    inp = torch.cat([table[rows], xyz], 1).to(DEV).requires_grad_(True)
+    y = mod(inp)
+    assert y.shape == (inp.shape[0], 1)
+    assert np.abs(y.detach().cpu().numpy() - BLOB[pre + "eval_out"]).max() <= 1e-5
+    (G,) = torch.autograd.grad(y.sum(), inp)
+    ref_G = BLOB[pre + "input_grad"]
+    assert np.abs(G.cpu().numpy() - ref_G).max() <= 1e-4 * max(1.0, np.abs(ref_G).max())
+
+
+@pytest.mark.parametrize("name", sorted(META))
+def test_train_step_grads_match_reference(name):
+    """train_deep_sdf.py:483-533 re-typed around the drop-in module (decoder.eval(): no RNG), against the golden
+    loss / latent grad / parameter grads produced by the real reference."""
+    m, pre, table, rows, xyz, gt = _inputs(name)
+    ospec = O.OracleSpec(**m["spec"])
+    params = O.make_params(ospec, m["seed"])
+    mod = build_module(m["spec"], params, DEV).eval()
+    lat = torch.nn.Embedding(table.shape[0], table.shape[1], max_norm=m["code_bound"])
+    with torch.no_grad():
+        lat.weight.copy_(table)
+    clampd, lam, epoch = m["clamp"], m["lam"], m["epoch"]
+    n_total = xyz.shape[0]
+    sdf_gt = torch.clamp(gt, -clampd, clampd)
+    batch_vecs = lat(rows)
+    inp = torch.cat([batch_vecs, xyz], 1)
+    pred = mod(inp.to(DEV))
+    pred_c = torch.clamp(pred, -clampd, clampd)
+    loss = torch.nn.L1Loss(reduction="sum")(pred_c, sdf_gt.to(DEV)) / n_total
+    reg = (lam * min(1, epoch / 100) * torch.sum(torch.norm(batch_vecs, dim=1))) / n_total
+    loss = loss + reg.to(DEV)
+    loss.backward()
+    assert abs(float(loss) - float(BLOB[pre + "loss"][0])) <= 2e-6
+    ref_lg = BLOB[pre + "lat_grad"]
+    assert np.abs(lat.weight.grad.numpy() - ref_lg).max() <= 1e-6 + 2e-4 * np.abs(ref_lg).max()
+    for k, p in mod.named_parameters():
+        g = p.grad.detach().cpu().numpy()
+        ref_norm = float(BLOB[pre + "gnorm::" + k][0])
+        assert abs(np.linalg.norm(g.astype(np.float64)) - ref_norm) <= 2e-4 * ref_norm + 1e-8, k
+        if m["big"]:
+            idx = BLOB[pre + "gidx::" + k]
+            rg = BLOB[pre + "gsample::" + k]
+            assert np.abs(g.reshape(-1)[idx] - rg).max() <= 1e-6 + 2e-3 * np.abs(rg).max(), k
+        else:
+            rg = BLOB[pre + "grad::" + k]
+            assert np.abs(g - rg).max() <= 1e-6 + 2e-4 * np.abs(rg).max(), k
+
+
+@pytest.mark.parametrize("name", ["small_4x64_L2_tanh", "xyz_in_all_4x40_L4", "layernorm_4x48_L3", "big_8x512_L16"])
+def test_training_mode_with_shared_dropout_masks(name):
+    """Dropout parity needs a shared mask: the CUDA path exports its Philox keep-masks (dsdf_dropout_mask) and the
+    oracle consumes them."""
+    m, pre, table, rows, xyz, gt = _inputs(name)
+    kw = m["spec"]
+    ospec = O.OracleSpec(**kw)
+    params = O.make_params(ospec, m["seed"])
+    mod = build_module(kw, params, DEV).train()
+    inp_cpu = torch.cat([table[rows], xyz], 1)
+    N = inp_cpu.shape[0]
+    torch.manual_seed(77)
+    seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+    torch.manual_seed(77)
+    inp = inp_cpu.to(DEV).requires_grad_(True)
+    y = mod(inp)
+    w = torch.linspace(-1, 1, N, device=DEV).reshape(-1, 1)
+    (y * w).sum().backward()
+    lib = L.lib()
+    masks = {}
+    for l in range(ospec.num_linear - 1):
+        if ospec.dropout is not None and l in ospec.dropout and ospec.dropout_prob > 0:
+            buf = torch.empty(N, ospec.out_dims[l], dtype=torch.uint8, device=DEV)
+            L.check(lib.dsdf_dropout_mask(seed, l, 0, N, ospec.out_dims[l], float(ospec.dropout_prob), buf.data_ptr(), None))
+            masks[l] = buf.cpu().float()
+            frac = 1.0 - masks[l].mean().item()
+            assert abs(frac - lib.dsdf_dropout_effective_p(float(ospec.dropout_prob))) < 0.03
+    lat_mask = None
+    if ospec.latent_dropout:
+        buf = torch.empty(N, ospec.latent_size, dtype=torch.uint8, device=DEV)
+        L.check(lib.dsdf_dropout_mask(seed, 0xFFFF, 0, N, ospec.latent_size, 0.2, buf.data_ptr(), None))
+        lat_mask = buf.cpu().float()
+    torch.cuda.synchronize()
+    P = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    x = inp_cpu.clone().requires_grad_(True)
+    yo = O.decoder_forward(ospec, P, x, training=True, masks=masks, latent_mask=lat_mask)
+    (yo * w.cpu()).sum().backward()
+    assert (y.detach().cpu() - yo.detach()).abs().max().item() <= 1e-5
+    assert (inp.grad.cpu() - x.grad).abs().max().item() <= 1e-4 * max(1.0, x.grad.abs().max().item())
+    for k, p in mod.named_parameters():
+        ref = P[k].grad
+        assert (p.grad.cpu() - ref).abs().max().item() <= 1e-6 + 2e-4 * ref.abs().max().item(), k
+
+
+def test_jvp_double_backward_matches_G():
+    """deep_sdf/mesh.py:405-422 computes torch.autograd.functional.jvp through the decoder (double-backward trick)."""
+    name = "small_4x32_L1"
+    m, pre, table, rows, xyz, gt = _inputs(name)
+    ospec = O.OracleSpec(**m["spec"])
+    params = O.make_params(ospec, m["seed"])
+    mod = build_module(m["spec"], params, DEV).eval()
+    inp_cpu = torch.cat([table[rows], xyz], 1)
+    G = O.input_gradient(ospec, params, inp_cpu)
+    lat = inp_cpu[:, 0].to(DEV)
+    rest = inp_cpu[:, 1:].to(DEV)
+    v = torch.linspace(0.5, 1.5, inp_cpu.shape[0], device=DEV)
+
+    def f(latcol):
+        return mod(torch.cat([latcol.reshape(-1, 1), rest], 1)).squeeze(1)
+
+    out, jv = torch.autograd.functional.jvp(f, lat, v=v)
+    ref = G[:, 0] * v.cpu()
+    assert (jv.cpu() - ref).abs().max().item() <= 1e-5 * max(1.0, ref.abs().max().item())
+
+
+def test_dataparallel_wrapper_and_cpu_input():
+    """train_deep_sdf.py:353 always wraps in DataParallel and hands it a CPU tensor (lat_vecs lives on the CPU)."""
+    name = "small_4x64_L2_tanh"
+    m, pre, table, rows, xyz, gt = _inputs(name)
+    ospec = O.OracleSpec(**m["spec"])
+    params = O.make_params(ospec, m["seed"])
+    mod = build_module(m["spec"], params).cuda()
+    dp = torch.nn.DataParallel(mod, device_ids=[0]).eval()
+    inp = torch.cat([table[rows], xyz], 1)
+    y = dp(inp)
+    assert y.is_cuda and np.abs(y.detach().cpu().numpy() - BLOB[pre + "eval_out"]).max() <= 1e-5
+    sd = dp.state_dict()
+    assert all(k.startswith("module.lin") for k in sd)
+
+
+def test_chunked_recompute_path(monkeypatch):
+    import deepsdf_b200.networks.deep_sdf_decoder as D
+    monkeypatch.setattr(D, "_WS_SINGLE_PASS_LIMIT", 1)
+    monkeypatch.setattr(D, "_CHUNK_ROWS", 40)
+    name = "small_4x32_L1"
+    m, pre, table, rows, xyz, gt = _inputs(name)
+    ospec = O.OracleSpec(**m["spec"])
+    params = O.make_params(ospec, m["seed"])
+    mod = build_module(m["spec"], params, DEV).eval()
+    inp = torch.cat([table[rows], xyz], 1).to(DEV).requires_grad_(True)
+    y = mod(inp)
+    y.sum().backward()
+    assert np.abs(y.detach().cpu().numpy() - BLOB[pre + "eval_out"]).max() <= 1e-5
+    P = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    yo = O.decoder_forward(ospec, P, inp.detach().cpu())
+    yo.sum().backward()
+    for k, p in mod.named_parameters():
+        assert (p.grad.cpu() - P[k].grad).abs().max().item() <= 1e-6 + 2e-4 * P[k].grad.abs().max().item(), k

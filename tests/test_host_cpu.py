@@ -1,0 +1,71 @@
+"""CPU-only checks: the C-ABI library loads and exports every symbol include/dsdf.h declares, the drop-in Decoder
+mirrors the reference's parameter names / shapes / attributes, NetSpec resolves layer sizes like the oracle."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from deepsdf_b200 import _lib as L
+from deepsdf_b200.spec import NetSpec
+from oracle import decoder_oracle as O
+from tests.util import build_module, load_cases
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+META, BLOB = load_cases()
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "dsdf.h")).read()
+    names = set(re.findall(r"\b(dsdf_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 10
+    lib = L.lib()
+    for n in sorted(names):
+        assert hasattr(lib, n), f"{n} declared in include/dsdf.h but not exported by libdsdf_b200.so"
+    assert lib.dsdf_abi_version() == 1
+
+
+def test_no_gpu_means_loud_failure():
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    m = build_module(META["small_4x32_L1"]["spec"])
+    with pytest.raises(L.DsdfError):
+        m(torch.zeros(4, 4))
+
+
+@pytest.mark.parametrize("name", sorted(META))
+def test_spec_and_module_mirror_reference(name):
+    kw = META[name]["spec"]
+    o = O.OracleSpec(**kw)
+    s = NetSpec(**kw)
+    assert s.in_dims == o.in_dims and s.out_dims == o.out_dims
+    m = build_module(kw)
+    sd = m.state_dict()
+    assert list(sd.keys()) == o.param_names() or sorted(sd.keys()) == sorted(o.param_names())
+    for k, shp in o.param_shapes().items():
+        assert tuple(sd[k].shape) == shp
+    assert [n for n, _ in m.named_parameters()] == o.param_names()
+    assert m.geom_dimension == kw["geom_dimension"] and m.num_layers == len(kw["dims"]) + 2
+    # loads a reference-format checkpoint (DataParallel prefix stripped by the caller, as workspace.py does)
+    params = O.make_params(o, META[name]["seed"])
+    m.load_state_dict(params, strict=True)
+    d = s.desc()
+    assert d.num_linear == o.num_linear
+
+
+def test_fused_support_matrix():
+    lib = L.lib()
+    exp = {"big_8x512_L256": 1, "big_8x512_L2": 1, "big_8x512_L16": 1, "small_4x64_L2_tanh": 0, "mid_6x128_L1": 0,
+           "layernorm_4x48_L3": 0}
+    for name, want in exp.items():
+        d = NetSpec(**META[name]["spec"]).desc()
+        assert lib.dsdf_fused_supported(C.byref(d)) == want, name
+
+
+def test_reference_export_keys_load():
+    z = np.load(os.path.join(ROOT, "tests", "golden", "small_net_export.npz"))
+    params = {k[len("param::"):]: torch.from_numpy(z[k]) for k in z.files if k.startswith("param::")}
+    m = build_module(META["small_4x64_L2_tanh"]["spec"], params)
+    assert torch.equal(m.lin4.parametrizations.weight.original1, params["lin4.parametrizations.weight.original1"])

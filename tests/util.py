@@ -1,0 +1,85 @@
+"""Shared helpers for the parity tests."""
+import json
+import os
+
+import numpy as np
+import torch
+
+from oracle import decoder_oracle as O
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def load_cases():
+    with open(os.path.join(GOLDEN, "decoder_cases.json")) as f:
+        meta = json.load(f)
+    blob = np.load(os.path.join(GOLDEN, "decoder_cases.npz"))
+    return meta, blob
+
+
+def build_module(kw, params=None, device=None):
+    from deepsdf_b200.networks.deep_sdf_decoder import Decoder
+    m = Decoder(kw["latent_size"], **{k: v for k, v in kw.items() if k != "latent_size"})
+    if params is not None:
+        res = m.load_state_dict(params, strict=True)
+        assert not res.missing_keys and not res.unexpected_keys
+    if device is not None:
+        m = m.to(device)
+    return m
+
+
+def sdf_scale_params(ospec, seed, out_scale=0.08):
+    """Synthetic parameters whose outputs live on the SDF scale (|sdf| <~ 0.2), like a trained DeepSDF network:
+    He-gain hidden layers and a last layer shrunk so that the pre-tanh output has std ~ out_scale."""
+    p = O.make_params(ospec, seed)
+    n = ospec.num_linear - 1
+    key = f"lin{n}.parametrizations.weight.original0" if ospec.is_weight_normed(n) else f"lin{n}.weight"
+    rng = np.random.RandomState(seed + 999)
+    L, D = ospec.latent_size, ospec.geom_dimension
+    x = torch.from_numpy(np.concatenate([rng.normal(0, 1 / np.sqrt(L), (256, L)), rng.uniform(-1, 1, (256, D))], 1).astype(np.float32))
+    q = {k: v.clone() for k, v in p.items()}
+    # measure the pre-tanh std with the last layer at its synthetic value
+    y = O.decoder_forward(ospec, q, x)
+    pre = torch.atanh(y.clamp(-0.999999, 0.999999))
+    if ospec.use_tanh:
+        pre = torch.atanh(pre.clamp(-0.999999, 0.999999))
+    s = float(pre.std()) + 1e-6
+    q[key] = q[key] * (out_scale / s)
+    q[f"lin{n}.bias"] = q[f"lin{n}.bias"] * 0.0 + 0.01
+    return q
+
+
+def bf16r(x):
+    return x.to(torch.bfloat16).float()
+
+
+def emulate_fused_forward(ospec, params, table, row_scene, xyz, masks=None):
+    """CPU emulation of the fused tcgen05 forward's arithmetic: bf16 weights and bf16 inter-layer activations with fp32
+    accumulation for the hidden-activation columns; latent and xyz columns, biases and the last layer in fp32.
+    Returns (sdf[N,1], pre-tanh y[N,1], list of post-activation fp32 tensors before bf16 rounding)."""
+    L, D = ospec.latent_size, ospec.geom_dimension
+    nh = ospec.num_linear - 1
+    z = table[row_scene]
+    a = None
+    acts = []
+    for l in range(nh):
+        W = O.effective_weight(ospec, params, l)
+        b = params[f"lin{l}.bias"]
+        if l == 0:
+            h = z @ W[:, :L].t() + b + xyz @ W[:, L:L + D].t()
+        elif l in ospec.latent_in:
+            xw = ospec.in_dims[l] - (L + D)
+            h = a[:, :xw] @ bf16r(W[:, :xw]).t() + (z @ W[:, xw:xw + L].t() + b) + xyz @ W[:, xw + L:].t()
+        else:
+            h = a @ bf16r(W).t() + b
+        h = torch.relu(h)
+        if masks is not None and l in masks:
+            h = h * masks[l] / (1.0 - ospec.dropout_prob)
+        acts.append(h)
+        a = bf16r(h)
+    Wl = O.effective_weight(ospec, params, nh)
+    y = acts[-1] @ Wl.t() + params[f"lin{nh}.bias"]
+    t = torch.tanh(y)
+    if ospec.use_tanh:
+        t = torch.tanh(t)
+    return t, y, acts

@@ -15,6 +15,7 @@ sys.path.insert(0, ROOT)
 from deepsdf_b200 import _lib as L  # noqa: E402
 from deepsdf_b200.spec import NetSpec  # noqa: E402
 from oracle import decoder_oracle as O  # noqa: E402
+from tests.util import emulate_fused_forward, sdf_scale_params  # noqa: E402
 
 dev = torch.device("cuda:0")
 lib = L.lib()
@@ -85,12 +86,12 @@ def to_params_struct(spec, params):
     return P
 
 
-def fused_forward_check(name="big_8x512_L256", n_rows=1000, tag="eval"):
+def fused_forward_check(name="big_8x512_L256", n_rows=1000, tag="eval", sdf_scale=True, timing=False):
     meta = json.load(open(os.path.join(ROOT, "tests", "golden", "decoder_cases.json")))[name]
     kw = meta["spec"]
     ospec = O.OracleSpec(**kw)
     spec = NetSpec(**kw)
-    params_cpu = O.make_params(ospec, meta["seed"])
+    params_cpu = sdf_scale_params(ospec, meta["seed"]) if sdf_scale else O.make_params(ospec, meta["seed"])
     params = {k: v.to(dev).contiguous() for k, v in params_cpu.items()}
     desc = spec.desc()
     assert lib.dsdf_fused_supported(C.byref(desc)) == 1
@@ -131,12 +132,14 @@ def fused_forward_check(name="big_8x512_L256", n_rows=1000, tag="eval"):
     W0 = O.effective_weight(ospec, params_cpu, 0)
     c0_ref = table[scene_ids] @ W0[:, :spec.latent_size].t() + params_cpu["lin0.bias"]
     cerr = (cbias[:, 0, :].cpu() - c0_ref).abs().max().item()
+    emu, _, _ = emulate_fused_forward(ospec, params_cpu, table, row_scene, xyz)
+    emu_err = (out.cpu() - emu.squeeze(1)).abs().max().item()
     err = (out.cpu() - ref).abs()
-    print(f"[fused fwd {name} {tag}] rows={n_rows} cbias_err={cerr:.3g} max_abs_err={err.max().item():.4g} mean_abs_err={err.mean().item():.4g} "
+    print(f"[fused fwd {name} {tag}] rows={n_rows} sdf_scale={sdf_scale} cbias_err={cerr:.3g} vs_bf16_emulation={emu_err:.3g} max_abs_err={err.max().item():.4g} mean_abs_err={err.mean().item():.4g} "
           f"ref range [{ref.min().item():.3f},{ref.max().item():.3f}] nan={int(torch.isnan(out).sum())} -> "
           f"{'OK' if err.max().item() < 2e-3 else 'MISMATCH'}")
     # timing of a larger eval run
-    if err.max().item() < 2e-3:
+    if timing:
         N = 1 << 20
         xyz_b = torch.rand(N, 3, device=dev) * 2 - 1
         ts_b = torch.zeros(N // 128, dtype=torch.int32, device=dev)
@@ -162,7 +165,8 @@ if __name__ == "__main__":
     which = sys.argv[1:] or ["big_8x512_L256", "big_8x512_L2", "big_8x512_L16"]
     if r.get("kk_256_256") and r.get("manualA"):
         for nm in which:
-            fused_forward_check(nm)
+            fused_forward_check(nm, sdf_scale=True, timing=(nm == which[0]))
+            fused_forward_check(nm, sdf_scale=False)
     else:
         print("skipping fused forward: basic UMMA self-tests failed")
     print(f"done in {time.time() - t0:.1f}s")
