@@ -1,0 +1,357 @@
+#!/usr/bin/env python3
+"""Headline benchmark: DeepSDF auto-decoder training step (fwd + bwd + optimiser), BASELINE.json config #2.
+
+  python bench.py --gpus N --steps K --warmup W            this repo's sm_100a path (one process per GPU under torchrun)
+  python bench.py --impl reference ...                      the CPU reference arm (oracle port of train_deep_sdf.py:483-545)
+
+Workload: Decoder 8x512, latent 256, latent_in=[4], weight_norm, dropout 0.2 on every hidden
+layer; per GPU and step 64 scenes x 16384 samples = 1 048 576 rows of synthetic (xyz, sdf) from the analytic
+CornerSpheres family; clamped-L1 loss + code regulariser; Adam on decoder and on all latent rows.  A step is one full
+optimiser iteration; nothing is skipped.  Weak scaling: every GPU gets its own 64 scenes per step; the flat decoder
+gradient is all-reduced over NCCL.
+
+One JSON line on stdout (rank 0).  `value` = samples/s with the batch already in HBM; `e2e` = the same step fed from
+pinned host memory (H2D of the [N,4] samples inside the timed region, loss read back every step).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_FWD_PER_ROW = 2 * 1835520            # 3.671 MFLOP/row forward (algorithmic)
+FLOP_TRAIN_PER_ROW = 3 * FLOP_FWD_PER_ROW  # fwd + dgrad + wgrad
+SCENES_PER_STEP = 64
+SAMPLES_PER_SCENE = 16384
+SCENES_TOTAL = 1024                        # lat_vecs rows per GPU
+N_HOST_BATCHES = 4
+
+SPECS = {
+    "Description": "bench: original DeepSDF decoder 8x512, latent 256 (BASELINE.json config #2)",
+    "NetworkArch": "deep_sdf_decoder",
+    "NetworkSpecs": {
+        "dims": [512] * 8, "dropout": list(range(8)), "dropout_prob": 0.2, "norm_layers": list(range(8)),
+        "latent_in": [4], "xyz_in_all": False, "use_tanh": False, "latent_dropout": False, "weight_norm": True,
+        "geom_dimension": 3,
+    },
+    "CodeLength": 256,
+    "LearningRateSchedule": [
+        {"Type": "Step", "Initial": 0.0005, "Interval": 500, "Factor": 0.5},
+        {"Type": "Step", "Initial": 0.001, "Interval": 500, "Factor": 0.5},
+    ],
+    "SamplesPerScene": SAMPLES_PER_SCENE, "ScenesPerBatch": SCENES_PER_STEP, "ClampingDistance": 0.1,
+    "CodeRegularization": True, "CodeRegularizationLambda": 1e-4, "CodeBound": 1.0,
+}
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"burst": d.get("bf16_tflops"), "sustained": d.get("bf16_tflops_sustained"), "hbm": d.get("hbm_gbs"),
+                "source": "measured"}
+    return {"burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0, "source": "fallback"}
+
+
+# ------------------------------------------------------------------------------------------------ synthetic data
+def corner_spheres_sdf_torch(xyz: torch.Tensor, radius: torch.Tensor, limit: float = 0.9) -> torch.Tensor:
+    """sdf_sampler/microstructures.py:23-36 CornerSpheresSDF (inf-norm box minus eight 3-norm corner 'spheres')."""
+    out = xyz.abs().amax(dim=1) - limit
+    for sx in (-1.0, 1.0):
+        for sy in (-1.0, 1.0):
+            for sz in (-1.0, 1.0):
+                c = torch.tensor([sx, sy, sz], device=xyz.device)
+                d = (xyz - c).abs().pow(3).sum(dim=1).pow(1.0 / 3.0) - radius
+                out = torch.maximum(out, -d)
+    return out
+
+
+def make_batch(gen: torch.Generator, device, scene_ids: torch.Tensor, scenes_total: int) -> torch.Tensor:
+    """[S*SPS, 4] fp32 (x, y, z, sdf), scene-major, as the reference's DataLoader yields after reshape(-1, 4)."""
+    S = scene_ids.numel()
+    n = S * SAMPLES_PER_SCENE
+    xyz = torch.rand(n, 3, generator=gen, device=device) * 2.0 - 1.0
+    r = (0.4 + 0.6 * scene_ids.to(device).float() / max(1, scenes_total - 1)).repeat_interleave(SAMPLES_PER_SCENE)
+    sdf = corner_spheres_sdf_torch(xyz, r)
+    return torch.cat([xyz, sdf.unsqueeze(1)], dim=1).contiguous()
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc, self.thread = index, [], None, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for row in self.rows:
+            f = [x.strip() for x in row.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        hot = [c for c, p in zip(sm, pw) if p >= 0.5 * max(pw)] or sm
+        return {"sm_mhz": statistics.median(hot), "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU reference arm
+def cpu_train_step_rate(n_scenes: int, steps: int, warmup: int):
+    """Oracle port of the reference train step (train_deep_sdf.py:483-545 with the reference Decoder's math) on the host
+    cores: same network, same per-row work, ``n_scenes`` x 16384 rows per step.  Returns (samples/s, ms/step, threads)."""
+    from oracle import decoder_oracle as O
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    ns = SPECS["NetworkSpecs"]
+    spec = O.OracleSpec(latent_size=SPECS["CodeLength"], **ns)
+    torch.manual_seed(0)
+    params = O.make_params(spec, 0)
+    n = n_scenes * SAMPLES_PER_SCENE
+    g = torch.Generator().manual_seed(2)
+    table = torch.randn(SCENES_TOTAL, spec.latent_size, generator=g) / (spec.latent_size ** 0.5)
+    ids = torch.arange(n_scenes)
+    batch = make_batch(g, "cpu", ids, SCENES_TOTAL)
+    row_scene = ids.repeat_interleave(SAMPLES_PER_SCENE)
+    names = list(params)
+    m = {k: torch.zeros_like(v) for k, v in params.items()}
+    v2 = {k: torch.zeros_like(v) for k, v in params.items()}
+    lm, lv = torch.zeros_like(table), torch.zeros_like(table)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        masks = {l: (torch.rand(n, spec.out_dims[l], generator=g) >= 0.2).float() for l in range(spec.num_linear - 1)}
+        _, grads, lat_grad, _ = O.train_loss_and_grads(spec, params, table, row_scene, batch[:, :3], batch[:, 3], 0.1, 1e-4, 1,
+                                                       masks=masks, code_bound=1.0)
+        for k in names:
+            O.adam_step_(params[k], grads[k], m[k], v2[k], it + 1, 5e-4)
+        O.adam_step_(table, lat_grad, lm, lv, it + 1, 1e-3)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    return n / (ms / 1e3), ms, threads
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_scenes = 4
+    rate, ms, threads = cpu_train_step_rate(n_scenes, args.steps, args.warmup)
+    sample = f"{n_scenes} scenes x {SAMPLES_PER_SCENE} rows per step ({n_scenes * SAMPLES_PER_SCENE} of the 1048576-row batch), same network and step math"
+    line = {
+        "impl": "reference", "metric": "train SDF samples/s (fwd+bwd+optimizer)", "value": rate, "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "config#2: Decoder 8x512 L=256 latent_in=[4], 64 scenes x 16384 samples/step/GPU (CPU arm: bounded sample)",
+                   "note": "reference arm = oracle port of train_deep_sdf.py:483-545 (PyTorch CPU fp32); the reference is Python and does not travel to the GPU box"},
+        "cpu_baseline": {"value": rate, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def run_gpu(args):
+    import torch.distributed as dist
+    from deepsdf_b200.trainer import SceneTrainer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (sm_100a); there is no CPU path for the product arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    peaks = load_peaks()
+
+    trainer = SceneTrainer(SPECS, SCENES_TOTAL, dev, rank=rank, world_size=world, seed=0)
+    N = SCENES_PER_STEP * SAMPLES_PER_SCENE
+    gen = torch.Generator(device=dev).manual_seed(2 + rank)
+    gcpu = torch.Generator().manual_seed(5 + rank)
+    dev_batches, host_batches, dev_ids, host_ids = [], [], [], []
+    for b in range(N_HOST_BATCHES):
+        ids = torch.randperm(SCENES_TOTAL, generator=gcpu)[:SCENES_PER_STEP].sort().values
+        db = make_batch(gen, dev, ids, SCENES_TOTAL)
+        dev_batches.append(db)
+        host_batches.append(db.cpu().pin_memory())
+        dev_ids.append(ids.to(dev))
+        host_ids.append(ids.pin_memory())
+    staging = {"samples": torch.empty_like(dev_batches[0]), "scene_ids": torch.empty_like(dev_ids[0])}
+    global_rows = N * world
+    row0 = rank * N
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- warm-up
+    for i in range(max(3, args.warmup)):
+        trainer.step(dev_batches[i % N_HOST_BATCHES], dev_ids[i % N_HOST_BATCHES], epoch=1, global_rows=global_rows, row0=row0)
+    barrier()
+
+    # ---- timed region 1: inputs resident in HBM
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    trainer.engine.kernel_events = []
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        loss = trainer.step(dev_batches[i % N_HOST_BATCHES], dev_ids[i % N_HOST_BATCHES], epoch=1, global_rows=global_rows,
+                            row0=row0)
+    e1.record()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    kev = trainer.engine.kernel_events
+    trainer.engine.kernel_events = None
+    ms_step = ms_total / args.steps
+    value = global_rows / (ms_step / 1e3)
+    loss_dev = [float(x) for x in loss.cpu()]
+
+    # ---- timed region 2: end to end from pinned host memory, loss read back every step
+    for i in range(2):
+        trainer.step_from_host(host_batches[i], host_ids[i], 1, staging, global_rows=global_rows, row0=row0).cpu()
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    last = None
+    for i in range(args.steps):
+        l = trainer.step_from_host(host_batches[i % N_HOST_BATCHES], host_ids[i % N_HOST_BATCHES], 1, staging,
+                                   global_rows=global_rows, row0=row0)
+        last = l.cpu()                    # device -> host read of the step's loss (synchronises, like .item() at :535)
+    e3.record()
+    barrier()
+    ms_e2e = max_over_ranks(e2.elapsed_time(e3)) / args.steps
+    clk = clocks.stop() if rank == 0 else None
+    e2e_value = global_rows / (ms_e2e / 1e3)
+    h2d = host_batches[0].numel() * 4 + host_ids[0].numel() * 8
+    d2h = 8
+
+    # ---- per-kernel durations (CUDA events on the launching stream, inside timed region 1)
+    per = {}
+    for name, a, b in kev:
+        per.setdefault(name, []).append(a.elapsed_time(b))
+    kern = {k: sum(v) / len(v) for k, v in per.items()}
+    tensor_kernels = {k: kern[k] for k in ("fused_forward", "fused_dgrad", "wgrad") if k in kern}
+    dom = max(tensor_kernels, key=tensor_kernels.get)
+    dom_ms = tensor_kernels[dom]
+    achieved = FLOP_FWD_PER_ROW * N / (dom_ms / 1e3) / 1e12
+    peak = peaks["sustained"]
+    roofline = {
+        "bound": "tensor", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+        "traffic": None, "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
+        "flops_per_launch": FLOP_FWD_PER_ROW * N,
+        "kernels_ms": kern,
+        "kernels_tflops": {k: FLOP_FWD_PER_ROW * N / (v / 1e3) / 1e12 for k, v in tensor_kernels.items()},
+        "step_tflops_algorithmic": FLOP_TRAIN_PER_ROW * N / (ms_step / 1e3) / 1e12,
+        "step_frac_of_peak": FLOP_TRAIN_PER_ROW * N / (ms_step / 1e3) / 1e12 / peak,
+        "step_frac_of_datasheet_2250": FLOP_TRAIN_PER_ROW * N / (ms_step / 1e3) / 1e12 / 2250.0,
+    }
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        n_sc = 2
+        rate, ms_cpu, threads = cpu_train_step_rate(n_sc, steps=2, warmup=1)
+        cpu = {"value": rate, "unit": "samples/s", "cores": threads, "kind": "port",
+               "sample": f"{n_sc} scenes x {SAMPLES_PER_SCENE} rows per step, 1 warm-up + 2 timed steps, oracle port of train_deep_sdf.py:483-545 (PyTorch CPU fp32)",
+               "ms_per_step": ms_cpu}
+
+    line = {
+        "metric": "train SDF samples/s (fwd+bwd+optimizer)", "value": value, "unit": "samples/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "config#2: Decoder 8x512 L=256 latent_in=[4] weight_norm dropout0.2, 64 scenes x 16384 samples per GPU per step",
+                   "rows_per_gpu_step": N, "global_rows_per_step": global_rows, "parallelism": f"dp{world}",
+                   "cache": "per-step working set (bf16 activation + dY stashes, 17 GB) is far larger than the 126 MB L2; 4 rotating input batches"},
+        "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e},
+        "gpu_launches": 13 * args.steps,
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "clocks": clk,
+        "loss_last_step": loss_dev,
+        "loss_last_step_e2e": [float(x) for x in last],
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -37,7 +37,7 @@ class ParamGrads(C.Structure):
 class TrainIO(C.Structure):
     _fields_ = [
         ("b_last", C.c_void_p), ("training", C.c_int32), ("seed", C.c_uint64), ("row0", C.c_uint64),
-        ("gt", C.c_void_p), ("clamp", C.c_float), ("inv_n", C.c_float), ("dy_out", C.c_void_p),
+        ("gt", C.c_void_p), ("gt_stride", C.c_int32), ("clamp", C.c_float), ("inv_n", C.c_float), ("dy_out", C.c_void_p),
         ("tile_loss", C.c_void_p), ("bitmask", C.c_void_p), ("acts", C.c_void_p), ("n_rows_pad", C.c_int64),
     ]
 
@@ -66,7 +66,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_pack_bytes": (sz, [P(NetDesc)]),
         "dsdf_pack_weights": (C.c_int, [P(NetDesc), P(Params), vp, vp]),
         "dsdf_scene_prepare": (C.c_int, [P(NetDesc), vp, vp, vp, i32, f32, vp, vp]),
-        "dsdf_fused_forward": (C.c_int, [P(NetDesc), vp, vp, vp, vp, i64, vp, P(TrainIO), vp]),
+        "dsdf_fused_forward": (C.c_int, [P(NetDesc), vp, vp, vp, vp, i32, i64, vp, P(TrainIO), vp]),
         "dsdf_selftest_umma": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint,
                                          C.c_uint, vp]),
     }

@@ -43,7 +43,9 @@ struct FwdArgs {
   const float* b_last;                      // [1]
   const int32_t* tile_scene;                // [n_tiles] -> row of cbias
   const float* cbias;                       // [S][2][512] per-scene biases (latent part of lin0 / skip layer + bias)
-  const float* xyz;                         // [N][3]
+  const float* xyz;                         // row r at xyz + r*xyz_stride (3 floats)
+  int32_t xyz_stride;                       // floats between rows: 3 ([N,3]) or 4 ([N,4] xyz+sdf samples)
+  int32_t gt_stride;                        // floats between gt values: 1 or 4
   float* sdf_out;                           // [N]
   int32_t use_tanh;
   int32_t training;
@@ -70,7 +72,8 @@ struct BwdArgs {
   const float* dy;                          // [N_pad]
   const uint32_t* bitmask;                  // [num_hidden][N_pad][16]
   float scale[DSDF_MAX_LAYERS];             // backward factor of hidden layer l where its mask bit is set
-  const float* xyz;                         // [N][3]
+  const float* xyz;                         // row r at xyz + r*xyz_stride
+  int32_t xyz_stride;
   float* tile_part;                         // [n_tiles][part_stride] per-tile column sums
   int32_t part_stride;
   int32_t colsum_slot[DSDF_MAX_LAYERS];     // slot (x512 floats) of colsum(dY_l) in tile_part, or -1

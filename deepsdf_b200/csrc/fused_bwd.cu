@@ -139,9 +139,10 @@ fused_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       const bool valid = lrow < args.n_rows;
       const float dyv = __ldg(args.dy + lrow);     // dy buffer is padded to n_rows_pad and zero beyond n_rows
       if (j == 0) {
-        s_xyz[0][rt] = valid ? __ldg(args.xyz + lrow * 3 + 0) : 0.0f;
-        s_xyz[1][rt] = valid ? __ldg(args.xyz + lrow * 3 + 1) : 0.0f;
-        s_xyz[2][rt] = valid ? __ldg(args.xyz + lrow * 3 + 2) : 0.0f;
+        const float* pt = args.xyz + lrow * args.xyz_stride;
+        s_xyz[0][rt] = valid ? __ldg(pt + 0) : 0.0f;
+        s_xyz[1][rt] = valid ? __ldg(pt + 1) : 0.0f;
+        s_xyz[2][rt] = valid ? __ldg(pt + 2) : 0.0f;
       }
       for (int t = nh - 1; t >= 0; --t) {
         const bool has_mma = (t < nh - 1);

@@ -203,7 +203,7 @@ fused_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       const bool valid = lrow < args.n_rows;
       EpiCtx cx;
       cx.x = cx.y = cx.z = 0.0f;
-      if (valid) { cx.x = __ldg(args.xyz + lrow * 3 + 0); cx.y = __ldg(args.xyz + lrow * 3 + 1); cx.z = __ldg(args.xyz + lrow * 3 + 2); }
+      if (valid) { const float* pt = args.xyz + lrow * args.xyz_stride; cx.x = __ldg(pt); cx.y = __ldg(pt + 1); cx.z = __ldg(pt + 2); }
       cx.thr = args.drop_thr; cx.scale = args.drop_scale; cx.seed = args.seed; cx.grow = args.row0 + uint64_t(lrow);
       const float* cb = args.cbias + size_t(__ldg(args.tile_scene + tile)) * 2 * FH;
       float ydot = 0.0f;
@@ -316,7 +316,7 @@ fused_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         if (args.use_tanh) { t = tanhf(t1); dt *= (1.0f - t * t); }
         if (valid) args.sdf_out[lrow] = t;
         if (kTrain && args.gt != nullptr) {
-          float g = valid ? __ldg(args.gt + lrow) : 0.0f;
+          float g = valid ? __ldg(args.gt + lrow * args.gt_stride) : 0.0f;
           float pc = t, gc = g, inside = 1.0f;
           if (args.clamp > 0.0f) {
             pc = fminf(fmaxf(t, -args.clamp), args.clamp);

@@ -253,8 +253,8 @@ extern "C" int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, f
 }
 
 extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const float* cbias,
-                                  const int32_t* tile_scene, const float* xyz, int64_t n_rows, float* sdf_out,
-                                  const dsdf_train_io* tr, void* stream) {
+                                  const int32_t* tile_scene, const float* xyz, int32_t xyz_stride, int64_t n_rows,
+                                  float* sdf_out, const dsdf_train_io* tr, void* stream) {
   if (int e = require_sm100()) return e;
   FusedLayout lo;
   if (int e = fused_layout(desc, &lo)) return e;
@@ -279,6 +279,9 @@ extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, c
   a.tile_scene = tile_scene;
   a.cbias = cbias;
   a.xyz = xyz;
+  DSDF_REQUIRE(xyz_stride >= 3, "xyz_stride must be >= 3");
+  a.xyz_stride = xyz_stride;
+  a.gt_stride = tr->gt_stride > 0 ? tr->gt_stride : 1;
   a.sdf_out = sdf_out;
   a.use_tanh = desc->use_tanh;
   a.training = tr->training;

@@ -82,7 +82,7 @@ extern "C" int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, i
 }
 
 extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, const dsdf_train_bufs* bufs, const float* xyz,
-                                int64_t n_rows, int32_t training, void* stream) {
+                                int32_t xyz_stride, int64_t n_rows, int32_t training, void* stream) {
   if (int e = require_sm100()) return e;
   FusedLayout lo;
   if (int e = fused_layout(desc, &lo)) return e;
@@ -115,6 +115,8 @@ extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, con
     a.xyzsum_slot[l] = (l == 0) ? lo.num_hidden : (l == lo.lat_layer ? lo.num_hidden + 3 : -1);
   }
   a.xyz = xyz;
+  DSDF_REQUIRE(xyz_stride >= 3, "xyz_stride must be >= 3");
+  a.xyz_stride = xyz_stride;
   a.tile_part = bufs->tile_part;
   a.part_stride = n_slots(lo) * FH;
   a.store_dys = 1;
@@ -206,14 +208,24 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
 }
 
 extern "C" int dsdf_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
-                         int32_t step, float grad_scale, void* stream) {
+                         int32_t step, float grad_scale, const float* grad_scale_dev, void* stream) {
   if (int e = require_sm100()) return e;
   if (n <= 0) return 0;
   DSDF_REQUIRE(step >= 1, "Adam step counter starts at 1");
   const float bc1 = float(1.0 - pow(double(beta1), double(step)));
   const float bc2 = float(1.0 - pow(double(beta2), double(step)));
   adam_kernel<<<unsigned((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1,
-                                                                                       sqrtf(bc2), grad_scale);
+                                                                                       sqrtf(bc2), grad_scale, grad_scale_dev);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dsdf_clip_coef(const float* g, int64_t n, float max_norm, float* scratch, float* out, void* stream) {
+  if (int e = require_sm100()) return e;
+  DSDF_REQUIRE(n > 0 && g && scratch && out, "dsdf_clip_coef: bad arguments");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  sumsq_partial_kernel<<<1024, 256, 0, st>>>(g, n, scratch);
+  clip_coef_kernel<<<1, 1024, 0, st>>>(scratch, max_norm, out);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

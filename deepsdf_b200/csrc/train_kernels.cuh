@@ -159,9 +159,11 @@ __global__ void __launch_bounds__(256) loss_kernel(const __grid_constant__ Finis
 
 // torch.optim.Adam (no weight decay, no amsgrad), one flat tensor.  step >= 1.
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n,
-                            float lr, float beta1, float beta2, float eps, float bc1, float bc2_sqrt, float grad_scale) {
+                            float lr, float beta1, float beta2, float eps, float bc1, float bc2_sqrt, float grad_scale,
+                            const float* __restrict__ grad_scale_dev) {
   const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  if (grad_scale_dev != nullptr) grad_scale *= __ldg(grad_scale_dev);
   const float gi = g[i] * grad_scale;
   const float mi = beta1 * m[i] + (1.f - beta1) * gi;
   const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
@@ -169,6 +171,39 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
   v[i] = vi;
   const float denom = sqrtf(vi) / bc2_sqrt + eps;
   p[i] -= (lr / bc1) * (mi / denom);
+}
+
+// ||g||^2 in two deterministic stages: 1024 blocks of fixed element ranges, then one block.
+__global__ void __launch_bounds__(256) sumsq_partial_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ part) {
+  __shared__ float red[256];
+  const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+  const int64_t b = per * blockIdx.x;
+  int64_t e = b + per;
+  if (e > n) e = n;
+  float acc = 0.f;
+  for (int64_t i = b + threadIdx.x; i < e; i += 256) { const float t = g[i]; acc += t * t; }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) part[blockIdx.x] = red[0];
+}
+__global__ void __launch_bounds__(1024) clip_coef_kernel(const float* __restrict__ part, float max_norm, float* __restrict__ out) {
+  __shared__ float red[1024];
+  red[threadIdx.x] = part[threadIdx.x];
+  __syncthreads();
+  for (int w = 512; w > 0; w >>= 1) {
+    if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const float nrm = sqrtf(red[0]);
+    out[0] = nrm;
+    const float c = max_norm / (nrm + 1e-6f);
+    out[1] = c < 1.0f ? c : 1.0f;
+  }
 }
 
 }  // namespace dsdf

@@ -35,14 +35,16 @@ def _declare_train(lib) -> None:
     lib.dsdf_train_buf_sizes.restype = C.c_int
     lib.dsdf_train_buf_sizes.argtypes = [P(L.NetDesc), i64, i32, P(sz)]
     lib.dsdf_fused_dgrad.restype = C.c_int
-    lib.dsdf_fused_dgrad.argtypes = [P(L.NetDesc), vp, P(TrainBufs), vp, i64, i32, vp]
+    lib.dsdf_fused_dgrad.argtypes = [P(L.NetDesc), vp, P(TrainBufs), vp, i32, i64, i32, vp]
     lib.dsdf_fused_wgrad.restype = C.c_int
     lib.dsdf_fused_wgrad.argtypes = [P(L.NetDesc), P(TrainBufs), i64, vp]
     lib.dsdf_fused_finish.restype = C.c_int
     lib.dsdf_fused_finish.argtypes = [P(L.NetDesc), vp, P(L.Params), P(TrainBufs), vp, i64, vp, vp, i32, i64, f32, f32,
                                       P(L.ParamGrads), vp, vp, vp]
     lib.dsdf_adam.restype = C.c_int
-    lib.dsdf_adam.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp]
+    lib.dsdf_adam.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp, vp]
+    lib.dsdf_clip_coef.restype = C.c_int
+    lib.dsdf_clip_coef.argtypes = [vp, i64, f32, vp, vp, vp]
     lib._dsdf_train_declared = True
 
 
@@ -69,6 +71,7 @@ class FusedEngine:
         self.num_hidden = self.spec.num_linear - 1
         self._bufs_key = None
         self._bufs: Dict[str, torch.Tensor] = {}
+        self.kernel_events = None      # set to a list to collect (name, start_event, end_event) per fused kernel call
         self.repack()
 
     # ------------------------------------------------------------------ weights
@@ -111,7 +114,7 @@ class FusedEngine:
         io.training = 0
         with torch.cuda.device(self.device):
             L.check(self.lib.dsdf_fused_forward(C.byref(self.desc), self.pack.data_ptr(), cbias.data_ptr(), tile_scene.data_ptr(),
-                                                xyz.data_ptr(), N, sdf.data_ptr(), C.byref(io), self._st()))
+                                                xyz.data_ptr(), 3, N, sdf.data_ptr(), C.byref(io), self._st()))
         return sdf
 
     # ------------------------------------------------------------------ training
@@ -150,11 +153,13 @@ class FusedEngine:
 
     def loss_and_grads(self, lat_table: torch.Tensor, scene_ids: torch.Tensor, tile_scene: torch.Tensor, xyz: torch.Tensor,
                        gt: torch.Tensor, *, clamp: float, reg_lambda_eff: float, n_total: int, code_bound: Optional[float],
-                       seed: int, row0: int, PG: L.ParamGrads, lat_grad: torch.Tensor, training: bool = True) -> torch.Tensor:
+                       seed: int, row0: int, PG: L.ParamGrads, lat_grad: torch.Tensor, training: bool = True,
+                       point_stride: int = 3, gt_stride: int = 1, n_rows: Optional[int] = None) -> torch.Tensor:
         """train_deep_sdf.py:483-533 for one (local) batch: returns the 2-element loss tensor (total, data term); fills
         the decoder gradients behind ``PG`` and the dense latent gradient ``lat_grad`` [S_total, L].
-        ``n_total`` is the GLOBAL batch size (loss normaliser, :519)."""
-        N = xyz.shape[0]
+        ``n_total`` is the GLOBAL batch size (loss normaliser, :519).  ``point_stride=4, gt_stride=4`` read the
+        reference's [N,4] (xyz, sdf) sample rows in place: pass ``xyz = samples`` and ``gt = samples.view(-1)[3:]``."""
+        N = int(n_rows) if n_rows is not None else xyz.shape[0]
         if N % TILE:
             raise L.DsdfError("fused training needs a multiple of 128 rows (SamplesPerScene % 128 == 0)")
         S = scene_ids.numel()
@@ -167,6 +172,7 @@ class FusedEngine:
         io.seed = seed
         io.row0 = row0
         io.gt = gt.data_ptr()
+        io.gt_stride = gt_stride
         io.clamp = float(clamp or 0.0)
         io.inv_n = 1.0 / float(n_total)
         io.dy_out = b["dy"].data_ptr()
@@ -175,18 +181,43 @@ class FusedEngine:
         io.acts = b["acts"].data_ptr()
         io.n_rows_pad = N
         lib, desc, st = self.lib, self.desc, self._st()
+        ev = self.kernel_events
+
+        def mark():
+            if ev is None:
+                return None
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            return e
+
         with torch.cuda.device(self.device):
+            e0 = mark()
             L.check(lib.dsdf_fused_forward(C.byref(desc), self.pack.data_ptr(), cb.data_ptr(), tile_scene.data_ptr(), xyz.data_ptr(),
-                                           N, b["sdf"].data_ptr(), C.byref(io), st))
-            L.check(lib.dsdf_fused_dgrad(C.byref(desc), self.pack.data_ptr(), C.byref(tb), xyz.data_ptr(), N, int(training), st))
+                                           point_stride, N, b["sdf"].data_ptr(), C.byref(io), st))
+            e1 = mark()
+            L.check(lib.dsdf_fused_dgrad(C.byref(desc), self.pack.data_ptr(), C.byref(tb), xyz.data_ptr(), point_stride, N,
+                                         int(training), st))
+            e2 = mark()
             L.check(lib.dsdf_fused_wgrad(C.byref(desc), C.byref(tb), N, st))
+            e3 = mark()
             L.check(lib.dsdf_fused_finish(C.byref(desc), self.pack.data_ptr(), C.byref(self._P), C.byref(tb), tile_scene.data_ptr(), N,
                                           lat_table.data_ptr(), scene_ids.data_ptr(), S, lat_table.shape[0], float(reg_lambda_eff),
                                           1.0 / float(n_total), C.byref(PG), lat_grad.data_ptr(), b["loss"].data_ptr(), st))
+            e4 = mark()
+        if ev is not None:
+            ev.extend([("fused_forward", e0, e1), ("fused_dgrad", e1, e2), ("wgrad", e2, e3), ("finish", e3, e4)])
         return b["loss"]
 
     def adam(self, p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int, lr: float,
-             grad_scale: float = 1.0, betas=(0.9, 0.999), eps: float = 1e-8) -> None:
+             grad_scale: float = 1.0, betas=(0.9, 0.999), eps: float = 1e-8, scale_dev: Optional[torch.Tensor] = None) -> None:
+        """torch.optim.Adam update (train_deep_sdf.py:400-411,545) of one flat fp32 tensor."""
         with torch.cuda.device(self.device):
             L.check(self.lib.dsdf_adam(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), float(lr), betas[0], betas[1],
-                                       eps, int(step), float(grad_scale), self._st()))
+                                       eps, int(step), float(grad_scale), scale_dev.data_ptr() if scale_dev is not None else None,
+                                       self._st()))
+
+    def clip_coef(self, g: torch.Tensor, max_norm: float, scratch: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """clip_grad_norm_ (train_deep_sdf.py:541-543): out[0] = ||g||, out[1] = min(1, max_norm/(||g||+1e-6))."""
+        with torch.cuda.device(self.device):
+            L.check(self.lib.dsdf_clip_coef(g.data_ptr(), g.numel(), float(max_norm), scratch.data_ptr(), out.data_ptr(), self._st()))
+        return out

@@ -90,6 +90,11 @@ class Decoder(nn.Module):
             out.extend(t for t in self.layer_tensors(layer) if t is not None)
         return out
 
+    def flat_param_names(self) -> List[str]:
+        """state_dict names in the order of ``flat_param_list()``."""
+        ids = {id(p): n for n, p in self.named_parameters()}
+        return [ids[id(t)] for t in self.flat_param_list()]
+
     def c_params(self, tensors: Optional[List[torch.Tensor]] = None) -> L.Params:
         """Fill the C struct from the live parameters (or from a same-order tensor list)."""
         P = L.Params()

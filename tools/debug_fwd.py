@@ -69,7 +69,7 @@ def run(name, n_rows=1000, p_drop=0.0):
     io.acts = acts.data_ptr()
     io.n_rows_pad = n_pad
     xyz_d, ts_d = xyz.to(dev), tile_scene.to(dev)
-    L.check(lib.dsdf_fused_forward(C.byref(desc), pack.data_ptr(), cbias.data_ptr(), ts_d.data_ptr(), xyz_d.data_ptr(),
+    L.check(lib.dsdf_fused_forward(C.byref(desc), pack.data_ptr(), cbias.data_ptr(), ts_d.data_ptr(), xyz_d.data_ptr(), 3,
                                    n_rows, out.data_ptr(), C.byref(io), st()))
     torch.cuda.synchronize()
     row_scene = scene_ids[tile_scene.long()].repeat_interleave(128)[:n_rows]
