@@ -77,6 +77,18 @@ def test_fused_train_step_grads(name, drop):
     N = xyz.shape[0]
     n_total = 2 * N                     # as if another rank held the other half of the global batch
     clampd, lam_eff, bound, seed = 0.1, 1e-4 * 0.37, 1.0, 4242
+    # shared Philox masks -> oracle
+    masks = {}
+    if drop > 0:
+        for l in range(ospec.num_linear - 1):
+            buf = torch.empty(N, ospec.out_dims[l], dtype=torch.uint8, device=DEV)
+            L.check(eng.lib.dsdf_dropout_mask(seed, l, 0, N, ospec.out_dims[l], drop, buf.data_ptr(), None))
+            masks[l] = buf.cpu().float()
+    table_o = table.clone()
+    O.embedding_renorm_(table_o, row_scene, bound)
+    # inputs whose loss derivative is not within bf16 noise of a sign / clamp-band flip (see the helper's docstring)
+    xyz, gt, n_unsafe = O.well_conditioned_batch(ospec, params, table_o, row_scene, masks if drop > 0 else None, clampd, seed=5)
+    assert n_unsafe <= 2
     tab_d = table.clone().to(DEV)
     grads, PG = eng.alloc_grads()
     lat_grad = torch.full_like(tab_d, float("nan"))
@@ -87,15 +99,6 @@ def test_fused_train_step_grads(name, drop):
     loss_v = loss.cpu().numpy().copy()
     g1 = [g.clone() for g in grads]
     lg1 = lat_grad.clone()
-    # shared Philox masks -> oracle
-    masks = {}
-    if drop > 0:
-        for l in range(ospec.num_linear - 1):
-            buf = torch.empty(N, ospec.out_dims[l], dtype=torch.uint8, device=DEV)
-            L.check(eng.lib.dsdf_dropout_mask(seed, l, 0, N, ospec.out_dims[l], drop, buf.data_ptr(), None))
-            masks[l] = buf.cpu().float()
-    table_o = table.clone()
-    O.embedding_renorm_(table_o, row_scene, bound)
     assert (tab_d.cpu() - table_o).abs().max().item() <= 1e-6       # max_norm renorm happened in place
     P = {k: v.clone().requires_grad_(True) for k, v in params.items()}
     Z = table_o.clone().requires_grad_(True)
@@ -105,7 +108,7 @@ def test_fused_train_step_grads(name, drop):
     data = (pred.clamp(-clampd, clampd) - gtc).abs().sum() / n_total
     reg = lam_eff * torch.sum(torch.norm(bv, dim=1)) / n_total
     (data + reg).backward()
-    print(f"{name}: loss {loss_v[0]:.6f} vs oracle {float(data + reg):.6f}")
+    print(f"{name}: loss {loss_v[0]:.6f} vs oracle {float((data + reg).detach()):.6f}")
     assert abs(loss_v[0] - float(data + reg)) <= 2e-3 * abs(float(data + reg))
     assert abs(loss_v[1] - float(data)) <= 2e-3 * abs(float(data))
     names = mod.flat_param_names()
