@@ -404,3 +404,85 @@ def well_conditioned_batch(spec: OracleSpec, params, lat_table: torch.Tensor, sc
     over = gt.abs() > clamp_dist          # gt is clamped too (train_deep_sdf.py:493): keep it inside the band
     gt[over] = (pc - sign * gap)[over]
     return xyz, gt, int((~done).sum())
+
+
+# --------------------------------------------------------------------------------------
+# the same step at the CUDA path's operand precision (checker for the backward kernels)
+# --------------------------------------------------------------------------------------
+class _RoundBF16(torch.autograd.Function):
+    """Round to bf16 in the forward, identity in the backward (straight-through)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+def decoder_forward_bf16_operands(spec: OracleSpec, params, lat_rows: torch.Tensor, xyz: torch.Tensor,
+                                  training: bool = False, masks: Optional[Dict[int, torch.Tensor]] = None,
+                                  gates: Optional[Dict[int, torch.Tensor]] = None) -> torch.Tensor:
+    """``decoder_forward`` (deep_sdf_decoder.py:76-111) with the operand rounding of the fused tcgen05 path: hidden
+    activations and the hidden-column weight blocks are rounded to bf16 before each product (fp32 accumulate); the latent
+    and xyz columns of lin0 / the latent_in layer, all biases, and the last layer stay fp32.  ``lat_rows`` = the gathered
+    latent rows [N, L].  Differentiable (straight-through rounding), so autograd through it gives the EXACT gradient of
+    the function the kernels evaluate.  Why it exists: ReLU gates whose fp32 pre-activation is within bf16 noise of zero
+    open or close differently under bf16 operands; each flipped gate changes its gradient entry by 100 %, so a gradient
+    comparison against the pure fp32 forward measures the gate flips (about 3-4 % relative norm per layer with random
+    weights, independent of the batch size), not the backward kernels.  Even two bf16-operand forwards that differ only
+    in fp32 summation order disagree on a few gates (0.5-0.8 % relative norm per gradient, measured), so for the 1e-2
+    gradient check the caller can hand over the gates the CUDA forward actually took, like the shared dropout masks:
+    ``gates[l]`` = {0,1} [N, out_dim] = relu gate AND dropout keep of hidden layer l; then h = pre * gate * scale.
+    Restricted to the fused path's network class (weight-norm or plain layers, one latent_in layer, no LayerNorm /
+    xyz_in_all / latent_dropout)."""
+    L, D = spec.latent_size, spec.geom_dimension
+    nh = spec.num_linear - 1
+    a = None
+    h = None
+    for l in range(nh):
+        W = effective_weight(spec, params, l)
+        b = params[f"lin{l}.bias"]
+        if l == 0:
+            h = lat_rows @ W[:, :L].t() + b + xyz @ W[:, L:L + D].t()
+        elif l in spec.latent_in:
+            xw = spec.in_dims[l] - (L + D)
+            h = a[:, :xw] @ _RoundBF16.apply(W[:, :xw]).t() + (lat_rows @ W[:, xw:xw + L].t() + b) + xyz @ W[:, xw + L:].t()
+        else:
+            h = a @ _RoundBF16.apply(W).t() + b
+        drop = training and spec.dropout is not None and l in spec.dropout and spec.dropout_prob > 0
+        if gates is not None:
+            h = h * gates[l]
+            if drop:
+                h = h / (1.0 - spec.dropout_prob)
+        else:
+            h = torch.relu(h)
+            if drop:
+                h = h * masks[l] / (1.0 - spec.dropout_prob)
+        a = _RoundBF16.apply(h)
+    y = h @ effective_weight(spec, params, nh).t() + params[f"lin{nh}.bias"]
+    if spec.use_tanh:
+        y = torch.tanh(y)
+    return torch.tanh(y)
+
+
+def train_loss_and_grads_bf16_operands(spec: OracleSpec, params, lat_table, scene_of_row, xyz, sdf_gt, clamp_dist,
+                                       reg_lambda_eff: float, n_total: int, masks=None, training: bool = True, gates=None):
+    """train_deep_sdf.py:483-533 evaluated through ``decoder_forward_bf16_operands``.  ``lat_table`` must already be
+    renormalised; ``reg_lambda_eff`` = CodeRegularizationLambda * min(1, epoch/100) (or 0); ``n_total`` the global rows."""
+    P = {k: v.detach().clone().requires_grad_(True) for k, v in params.items()}
+    Z = lat_table.detach().clone().requires_grad_(True)
+    bv = Z[scene_of_row]
+    pred = decoder_forward_bf16_operands(spec, P, bv, xyz, training=training, masks=masks, gates=gates)
+    gt = sdf_gt.reshape(-1, 1)
+    if clamp_dist is not None:
+        gt = gt.clamp(-clamp_dist, clamp_dist)
+        pred_c = pred.clamp(-clamp_dist, clamp_dist)
+    else:
+        pred_c = pred
+    loss = (pred_c - gt).abs().sum() / n_total
+    if reg_lambda_eff:
+        loss = loss + reg_lambda_eff * torch.sum(torch.norm(bv, dim=1)) / n_total
+    loss.backward()
+    return float(loss.detach()), {k: v.grad.detach() for k, v in P.items()}, Z.grad.detach(), pred.detach()
