@@ -12,7 +12,7 @@ int launch_wgrad_last(const void* x_last, const float* dy, int64_t n_rows_pad, f
 namespace {
 
 constexpr int kPlanCtas = 148;        // the split plan is fixed (not device dependent) so results are reproducible
-constexpr int kLastBlocks = 148;
+constexpr int kLastBlocks = 1184;   // fixed (not device dependent): 8 x 148
 
 struct WgradPlan {
   int n_slabs;
@@ -194,7 +194,7 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
   scene_sums_kernel<<<dim3(n_scenes, a.n_slots), FH, 0, st>>>(a.tile_part, tile_scene, a.n_tiles, a.n_slots, a.scene_sums);
   if (lat_grad) {
     DSDF_CHECK_CUDA(cudaMemsetAsync(lat_grad, 0, size_t(n_scenes_total) * desc->latent_size * sizeof(float), st));
-    latent_grad_kernel<<<n_scenes, 256, 0, st>>>(a);
+    latent_grad_kernel<<<dim3(n_scenes, (desc->latent_size + 7) / 8), 256, 0, st>>>(a);
   }
   int max_out = 0;
   for (int l = 0; l < desc->num_linear; ++l) max_out = desc->out_dim[l] > max_out ? desc->out_dim[l] : max_out;

@@ -34,13 +34,29 @@ struct FinishArgs {
   int32_t xyz_slot0;            // first xyz-sum slot of lin0 (3 slots), skip layer follows (+3)
 };
 
-// scene_sums[s][slot][c] = sum over the tiles of scene s (ascending tile order) of tile_part[tile][slot][c]
+// scene_sums[s][slot][c] = sum over the tiles of scene s (ascending tile order) of tile_part[tile][slot][c].
+// grid (S, n_slots), block 512.  The tile list of the scene is compacted (in order) 512 tiles at a time with ballots.
 __global__ void __launch_bounds__(FH) scene_sums_kernel(const float* __restrict__ tile_part, const int32_t* __restrict__ tile_scene,
                                                         int n_tiles, int n_slots, float* __restrict__ scene_sums) {
   const int s = blockIdx.x, slot = blockIdx.y, c = threadIdx.x;
+  const int warp = c >> 5, lane = c & 31;
+  __shared__ int s_list[FH];
+  __shared__ int s_wcount[FH / 32];
   float acc = 0.f;
-  for (int t = 0; t < n_tiles; ++t)
-    if (__ldg(tile_scene + t) == s) acc += __ldg(tile_part + (size_t(t) * n_slots + slot) * FH + c);
+  for (int base = 0; base < n_tiles; base += FH) {
+    const int t = base + c;
+    const bool mine = (t < n_tiles) && (__ldg(tile_scene + t) == s);
+    const unsigned bal = __ballot_sync(0xffffffffu, mine);
+    if (lane == 0) s_wcount[warp] = __popc(bal);
+    __syncthreads();
+    int off = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < FH / 32; ++w) { const int n = s_wcount[w]; if (w < warp) off += n; total += n; }
+    if (mine) s_list[off + __popc(bal & ((1u << lane) - 1u))] = t;
+    __syncthreads();
+    for (int i = 0; i < total; ++i) acc += __ldg(tile_part + (size_t(s_list[i]) * n_slots + slot) * FH + c);
+    __syncthreads();
+  }
   scene_sums[(size_t(s) * n_slots + slot) * FH + c] = acc;
 }
 
@@ -100,7 +116,8 @@ __global__ void __launch_bounds__(128) assemble_grads_kernel(const __grid_consta
 }
 
 // lat_grad[scene_ids[s]][k] = colsum_s(dY_0) . W0[:, k] + colsum_s(dY_skip) . Wskip[:, xw+k] + reg * rows_s * z/||z||
-// grid S, block 256 (8 warps; warp w handles k = w, w+8, ...; lanes stride the 512 outputs -> coalesced wlatT reads)
+// grid (S, ceil(L/8)), block 256: warp w handles latent column k = 8*blockIdx.y + w; lanes stride the 512 outputs
+// (coalesced wlatT reads, fixed shuffle-tree order -> deterministic).
 __global__ void __launch_bounds__(256) latent_grad_kernel(const __grid_constant__ FinishArgs a) {
   const int s = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int L = a.desc.latent_size;
@@ -109,28 +126,36 @@ __global__ void __launch_bounds__(256) latent_grad_kernel(const __grid_constant_
   const float* ss1 = a.lo.lat_layer > 0 ? a.scene_sums + (size_t(s) * a.n_slots + a.lo.lat_layer) * FH : nullptr;
   const float* z = a.lat_table + size_t(a.scene_ids[s]) * L;
   __shared__ float s_norm;
-  __shared__ int s_rows;
+  __shared__ int s_cnt[8];
+  {
+    int cnt = 0;
+    for (int t = threadIdx.x; t < a.n_tiles; t += 256) cnt += (__ldg(a.tile_scene + t) == s);
+    for (int off = 16; off > 0; off >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+    if (lane == 0) s_cnt[warp] = cnt;
+  }
   if (warp == 0) {
     float q = 0.f;
     for (int k = lane; k < L; k += 32) q += z[k] * z[k];
     for (int off = 16; off > 0; off >>= 1) q += __shfl_xor_sync(0xffffffffu, q, off);
-    int cnt = 0;
-    for (int t = lane; t < a.n_tiles; t += 32) cnt += (a.tile_scene[t] == s);
-    for (int off = 16; off > 0; off >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
-    if (lane == 0) { s_norm = sqrtf(q); s_rows = cnt * TILE_M; a.scene_reg[s] = sqrtf(q) * float(cnt * TILE_M); }
+    if (lane == 0) s_norm = sqrtf(q);
   }
   __syncthreads();
-  for (int k = warp; k < L; k += 8) {
-    float acc = 0.f;
-    for (int o = lane; o < FH; o += 32) {
-      acc += ss0[o] * wlatT[size_t(k) * FH + o];
-      if (ss1) acc += ss1[o] * wlatT[(size_t(L) + k) * FH + o];
-    }
-    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
-    if (lane == 0) {
-      if (a.reg_scale != 0.f && s_norm > 0.f) acc += a.reg_scale * float(s_rows) * z[k] / s_norm;
-      a.lat_grad[size_t(a.scene_ids[s]) * L + k] = acc;
-    }
+  int rows = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) rows += s_cnt[w];
+  rows *= TILE_M;
+  if (blockIdx.y == 0 && threadIdx.x == 0) a.scene_reg[s] = s_norm * float(rows);
+  const int k = blockIdx.y * 8 + warp;
+  if (k >= L) return;
+  float acc = 0.f;
+  for (int o = lane; o < FH; o += 32) {
+    acc += ss0[o] * wlatT[size_t(k) * FH + o];
+    if (ss1) acc += ss1[o] * wlatT[(size_t(L) + k) * FH + o];
+  }
+  for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if (lane == 0) {
+    if (a.reg_scale != 0.f && s_norm > 0.f) acc += a.reg_scale * float(rows) * z[k] / s_norm;
+    a.lat_grad[size_t(a.scene_ids[s]) * L + k] = acc;
   }
 }
 
