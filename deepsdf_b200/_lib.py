@@ -67,6 +67,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_pack_weights": (C.c_int, [P(NetDesc), P(Params), vp, vp]),
         "dsdf_scene_prepare": (C.c_int, [P(NetDesc), vp, vp, vp, i32, f32, vp, vp]),
         "dsdf_fused_forward": (C.c_int, [P(NetDesc), vp, vp, vp, vp, i32, i64, vp, P(TrainIO), vp]),
+        "dsdf_selftest_umma_pair": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp]),
         "dsdf_selftest_umma": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint,
                                          C.c_uint, vp]),
     }

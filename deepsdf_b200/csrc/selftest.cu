@@ -142,3 +142,118 @@ extern "C" int dsdf_selftest_umma(int mode, const void* A, const void* B, float*
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// CTA-pair (cta_group::2) bring-up: C[256 x 256] = A[256 x K] * B[256 x K]^T with ONE cluster of two CTAs.
+// Each CTA owns 128 rows of A and of C (its own TMEM) and HALF of B's N rows (rank r: B rows [128r, 128r+128)).
+// Checks, against a PyTorch matmul: the pair TMEM allocation, the 2-SM TMA load signalling the leader's barrier, the
+// M=256 instruction descriptor, the multicast commit, and the epilogue->MMA hand-over used by the fused chain kernels:
+// mode bit2: A is written by the CTA's own threads (generic proxy, sw128_offset) and handed to the leader's MMA thread
+// through a remote mbarrier arrive (peer CTA -> leader CTA).
+namespace dsdf {
+
+struct Selftest2Args {
+  int K, mode;
+  const __nv_bfloat16* a_raw;   // [256][K]
+  float* C;                     // [256][256]
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(ST_THREADS, 1)
+umma_pair_selftest_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Selftest2Args args) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int K = args.K;
+  const bool manual_a = args.mode & 4;
+  uint8_t* sA = smem;                         // [K/64 chunks][128 rows][64] = up to 64 KB
+  uint8_t* sB = smem + 65536;                 // [K/64 chunks][128 N rows][64] = up to 64 KB (this CTA's half of B)
+  __shared__ uint64_t bar_full, bar_done, bar_a_ready;
+  __shared__ uint32_t tmem_base_slot;
+  const int warp = threadIdx.x >> 5;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&bar_full, 1);
+    mbar_init(&bar_done, 1);
+    mbar_init(&bar_a_ready, 2 * 4);            // 4 epilogue warps of each CTA
+    fence_barrier_init();
+  }
+  if (warp == 5) tmem_alloc_pair<256>(&tmem_base_slot);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t full_leader = mapa_u32(smem_u32(&bar_full), 0);
+  const uint32_t ready_leader = mapa_u32(smem_u32(&bar_a_ready), 0);
+  const uint32_t bytes_per_cta = 2u * 128u * uint32_t(K) * 2u;   // A half + B half
+
+  if (warp < 4) {
+    if (manual_a) {
+      for (int idx = threadIdx.x; idx < 128 * K; idx += 128) {
+        int r = idx / K, c = idx % K;
+        uint32_t off = (c >> 6) * (128u * 128u) + sw128_offset(r, c & 63);
+        *reinterpret_cast<__nv_bfloat16*>(sA + off) = args.a_raw[size_t(rank * 128 + r) * K + c];
+      }
+      fence_proxy_async_all();
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (lane_id() == 0) mbar_arrive_cluster(ready_leader);
+  }
+  if (warp == 4 && elect_one()) {
+    if (leader) mbar_arrive_expect_tx(&bar_full, 2u * bytes_per_cta - (manual_a ? 2u * 128u * uint32_t(K) * 2u : 0u));
+    for (int kc = 0; kc < K / 64; ++kc) {
+      if (!manual_a) tma_load_2d_pair(sA + kc * 16384, &tmA, full_leader, kc * 64, int(rank) * 128);
+      tma_load_2d_pair(sB + kc * 16384, &tmB, full_leader, kc * 64, int(rank) * 128);
+    }
+  }
+  if (warp == 5 && leader) {
+    mbar_wait(&bar_full, 0);
+    mbar_wait_cluster(&bar_a_ready, 0);
+    tc_fence_after();
+    if (elect_one()) {
+      const uint32_t idesc = umma_idesc_bf16(256, 256, 0, 0);
+      const uint64_t hi = umma_desc_hi_sw128(16, 1024);
+      for (int ks = 0; ks < K / 16; ++ks) {
+        const uint32_t off = (ks >> 2) * 16384u + (ks & 3) * 32u;
+        umma_bf16_ss_pair(tmem_base, umma_desc(smem_u32(sA) + off, hi), umma_desc(smem_u32(sB) + off, hi), idesc, ks > 0 ? 1u : 0u);
+      }
+      umma_commit_pair(&bar_done, 0b11);
+    }
+    __syncwarp();
+  }
+  if (warp < 4) {
+    mbar_wait(&bar_done, 0);
+    tc_fence_after();
+    const int row = warp * 32 + lane_id();
+    for (int c0 = 0; c0 < 256; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem_base + (uint32_t(warp * 32) << 16) + c0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) args.C[size_t(rank * 128 + row) * 256 + c0 + j] = __uint_as_float(v[j]);
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 5) tmem_dealloc_pair<256>(tmem_base);
+}
+
+}  // namespace dsdf
+
+extern "C" int dsdf_selftest_umma_pair(int mode, const void* A, const void* B, float* C, int K, void* stream) {
+  using namespace dsdf;
+  if (int e = require_sm100()) return e;
+  DSDF_REQUIRE(K % 64 == 0 && K >= 64 && K <= 256, "selftest: K must be 64..256, multiple of 64");
+  CUtensorMap tmA, tmB;
+  if (int e = make_tmap_bf16_2d(&tmA, A, K, 256, uint64_t(K) * 2, 64, 128)) return e;
+  if (int e = make_tmap_bf16_2d(&tmB, B, K, 256, uint64_t(K) * 2, 64, 128)) return e;
+  Selftest2Args args{K, mode, reinterpret_cast<const __nv_bfloat16*>(A), C};
+  const size_t smem = 65536 + 65536 + 1024;
+  DSDF_CHECK_CUDA(cudaFuncSetAttribute(umma_pair_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  umma_pair_selftest_kernel<<<2, ST_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB, args);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
