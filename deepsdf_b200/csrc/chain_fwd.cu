@@ -1,0 +1,418 @@
+// Fused DeepSDF decoder forward, CTA-pair version (sm_100a: tcgen05 cta_group::2 + TMEM + TMA, 2-CTA clusters).
+//
+// Two CTAs on the two SMs of a TPC form a pair.  Each CTA owns one 128-row point tile (its activation tile [128 x 512]
+// bf16 in its own shared memory, its accumulators [128 x 512] fp32 in its own TMEM) and the pair shares every weight
+// tile: for a [256 out x 64 K] weight block each CTA TMA-loads only its 128 output rows, and one tcgen05.mma
+// (cta_group::2, M = 256 over the pair, N = 256, K = 16) issued by the leader CTA multiplies both activation tiles with
+// both halves.  That halves the L2 -> SM weight traffic and the shared-memory space of the weight ring per row, which
+// is what makes room for a 5-stage ring, bias / xyz-weight staging and 16 epilogue warps.
+//
+// Per layer, per pair:   MMA order  (half 0: K chunks 0..7), (half 1: K chunks 0..7)
+//   * tmem_full[0] (multicast commit) -> both CTAs' epilogues post-process accumulator half 0 into REGISTERS while the
+//     tensor cores compute half 1;  free_lo (commit after half 1's K chunk 3) says activation chunks 0..3 are no longer
+//     read, so half 0 is written into the A tile before the layer's MMAs have even finished;
+//   * tmem_full[1] -> half 1 is post-processed and written quarter by quarter (128 columns); the next layer's MMAs start
+//     on the K chunks that are already there (a_ready[0..3], one mbarrier per quarter, arrivals from both CTAs).
+// Epilogue per element: FFMA (bias and dropout scale folded, bias staged in shared memory), sign-bit funnel -> ReLU
+// gate word, AND with the bit-sliced Philox keep word (computed before the accumulators are ready), select, bf16 pack.
+// The final 512 -> 1 layer, tanh, clamp, L1 loss and dL/dy are fused into the last epilogue; in training every layer's
+// activation tile is TMA-stored (bf16) for wgrad together with its 1-bit gates.
+// Replaces Decoder.forward (deep_sdf/networks/deep_sdf_decoder.py:76-111) and train_deep_sdf.py:511-519.
+#include "common.cuh"
+#include "fused.cuh"
+#include "host_util.h"
+
+namespace dsdf {
+
+namespace {
+
+constexpr int P_EPI_WARPS = 16;
+constexpr int P_EPI_THREADS = P_EPI_WARPS * 32;        // 512
+constexpr int P_THREADS = (P_EPI_WARPS + 2) * 32;      // + TMA warp + MMA warp
+constexpr int P_STAGES = 5;
+constexpr int P_STAGE_BYTES = 128 * 128;               // this CTA's half ([128 out rows][64 K] bf16) of a weight block
+constexpr int P_OFF_B = A_BYTES;
+constexpr int P_OFF_BIAS = P_OFF_B + P_STAGES * P_STAGE_BYTES;   // f32 [2][512]  (double-buffered per layer)
+constexpr int P_OFF_WXYZ = P_OFF_BIAS + 2 * FH * 4;              // f32 [3][512]
+constexpr int P_OFF_WLAST = P_OFF_WXYZ + 3 * FH * 4;             // f32 [512]
+constexpr int P_OFF_YPART = P_OFF_WLAST + FH * 4;                // f32 [4][128]
+constexpr int P_SMEM = P_OFF_YPART + 4 * TILE_M * 4 + 1024;
+
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(P_EPI_THREADS) : "memory"); }
+
+// Post-process 16 consecutive columns [c0, c0+16) of one row and write them (bf16) into the SW128 activation tile.
+//   has_acc  read the fp32 accumulators from TMEM (taddr) - false for the MMA-less first layer
+//   sb       shared-memory bias (already multiplied by the dropout scale); swx xyz weight rows (same scaling) or null
+//   keep16   low 16 bits: Philox keep bits of these columns (all ones when the layer has no dropout)
+// Returns the 16 gate bits (relu AND keep); adds this row's share of the last-layer dot product to ydot.
+template <bool kTrain>
+__device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, float ascale, const float* sb, const float* swx,
+                                               float x, float y, float z, uint32_t keep16, const float* swl, uint8_t* sA,
+                                               uint32_t row, uint32_t c0, float& ydot) {
+  float v[16];
+  if (has_acc) {
+    uint32_t r[16];
+    tmem_ld16(taddr, r);
+    tmem_ld_wait();
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float4 b = *reinterpret_cast<const float4*>(sb + 4 * k);
+      v[4 * k + 0] = fmaf(__uint_as_float(r[4 * k + 0]), ascale, b.x);
+      v[4 * k + 1] = fmaf(__uint_as_float(r[4 * k + 1]), ascale, b.y);
+      v[4 * k + 2] = fmaf(__uint_as_float(r[4 * k + 2]), ascale, b.z);
+      v[4 * k + 3] = fmaf(__uint_as_float(r[4 * k + 3]), ascale, b.w);
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float4 b = *reinterpret_cast<const float4*>(sb + 4 * k);
+      v[4 * k + 0] = b.x; v[4 * k + 1] = b.y; v[4 * k + 2] = b.z; v[4 * k + 3] = b.w;
+    }
+  }
+  if (swx != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float4 wx = *reinterpret_cast<const float4*>(swx + 4 * k);
+      const float4 wy = *reinterpret_cast<const float4*>(swx + FH + 4 * k);
+      const float4 wz = *reinterpret_cast<const float4*>(swx + 2 * FH + 4 * k);
+      v[4 * k + 0] += x * wx.x + y * wy.x + z * wz.x;
+      v[4 * k + 1] += x * wx.y + y * wy.y + z * wz.y;
+      v[4 * k + 2] += x * wx.z + y * wy.z + z * wz.z;
+      v[4 * k + 3] += x * wx.w + y * wy.w + z * wz.w;
+    }
+  }
+  uint32_t gate = 0;
+  if (kTrain) {
+    uint32_t sg = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) sg = __funnelshift_l(__float_as_uint(v[i]), sg, 1);   // bit (15-i) = sign of v[i]
+    gate = (~(__brev(sg) >> 16)) & keep16 & 0xFFFFu;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = (gate & (1u << i)) ? v[i] : 0.0f;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.0f);
+  }
+  if (swl != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float4 w = *reinterpret_cast<const float4*>(swl + 4 * k);
+      ydot += v[4 * k + 0] * w.x + v[4 * k + 1] * w.y + v[4 * k + 2] * w.z + v[4 * k + 3] * w.w;
+    }
+  }
+  uint8_t* base = sA + (c0 >> 6) * A_CHUNK_BYTES + row * 128u;
+  const uint32_t piece0 = (c0 & 63u) >> 3;
+  *reinterpret_cast<uint4*>(base + ((piece0 ^ (row & 7u)) << 4)) =
+      make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  *reinterpret_cast<uint4*>(base + (((piece0 + 1) ^ (row & 7u)) << 4)) =
+      make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+  return gate;
+}
+
+}  // namespace
+
+template <bool kTrain>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1)
+chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmActs,
+                     const __grid_constant__ FwdArgs args) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + P_OFF_B;
+  float* s_bias = reinterpret_cast<float*>(smem + P_OFF_BIAS);
+  float* s_wxyz = reinterpret_cast<float*>(smem + P_OFF_WXYZ);
+  float* s_wlast = reinterpret_cast<float*>(smem + P_OFF_WLAST);
+  float* s_ypart = reinterpret_cast<float*>(smem + P_OFF_YPART);
+  __shared__ uint64_t bar_full[P_STAGES], bar_empty[P_STAGES], bar_tmem_full[2], bar_free_q0, bar_free_lo, bar_a_ready[4];
+  __shared__ uint32_t tmem_slot;
+  __shared__ float s_loss[4];
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P_STAGES; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    mbar_init(&bar_tmem_full[0], 1); mbar_init(&bar_tmem_full[1], 1);
+    mbar_init(&bar_free_q0, 1);
+    mbar_init(&bar_free_lo, 1);
+    for (int i = 0; i < 4; ++i) mbar_init(&bar_a_ready[i], 2 * P_EPI_WARPS);
+    fence_barrier_init();
+  }
+  if (warp == P_EPI_WARPS + 1) tmem_alloc_pair<512>(&tmem_slot);
+  if (warp == P_EPI_WARPS && lane == 0) { tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmActs); }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int nh = args.num_hidden;
+  const int n_pairs = (args.n_tiles + 1) >> 1;
+  const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
+
+  if (warp == P_EPI_WARPS) {
+    // ================================================================ TMA producer (this CTA's half of every weight block)
+    if (lane == 0) {
+      const uint32_t full_leader = mapa_u32(smem_u32(&bar_full[0]), 0);
+      int stage = 0; uint32_t phase = 0;
+      for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+        for (int l = 0; l < nh; ++l) {
+          const ChainLayer& L = args.prog[l];
+          if (!L.has_mma) continue;
+          for (int h = 0; h < L.n_halves; ++h)
+            for (int kc = 0; kc < L.k_chunks; ++kc) {
+              mbar_wait(&bar_empty[stage], phase ^ 1);
+              if (leader) mbar_arrive_expect_tx(&bar_full[stage], 2 * P_STAGE_BYTES);
+              tma_load_2d_pair(sB + stage * P_STAGE_BYTES, &tmW, full_leader + stage * 8, kc * 64,
+                               L.w_row0 + h * HALF_N + int(rank) * 128);
+              if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+      }
+    }
+  } else if (warp == P_EPI_WARPS + 1) {
+    // ================================================================ MMA issuer (leader CTA only)
+    if (leader) {
+      const uint32_t idesc = umma_idesc_bf16(2 * TILE_M, HALF_N, 0, 0);
+      const uint64_t desc_hi = umma_desc_hi_sw128(16, 1024);
+      const uint32_t sA_u = smem_u32(sA), sB_u = smem_u32(sB);
+      int stage = 0; uint32_t phase = 0; uint32_t a_cons = 0;
+      for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+        for (int l = 0; l < nh; ++l) {
+          const ChainLayer& L = args.prog[l];
+          if (!L.has_mma) continue;
+          const uint32_t apar = a_cons & 1; ++a_cons;
+          const int kc_lo_last = L.k_chunks < 4 ? L.k_chunks - 1 : 3;
+          const int kc_q0_last = L.k_chunks < 2 ? L.k_chunks - 1 : 1;
+          uint32_t waited = 0;     // quarters of the previous layer's output whose a_ready has been consumed
+          auto need = [&](int qd) {
+            if (!((waited >> qd) & 1u)) { mbar_wait_cluster(&bar_a_ready[qd], apar); waited |= 1u << qd; }
+          };
+          for (int h = 0; h < L.n_halves; ++h) {
+            for (int kc = 0; kc < L.k_chunks; ++kc) {
+              // K chunk kc reads quarter kc/2 of the A tile.  Besides, the first MMA of half h overwrites that half's
+              // accumulators, which the previous layer's epilogue reads quarter by quarter: half 0 needs quarters 0,1
+              // drained, half 1 needs quarters 2,3.
+              if (kc == 0) { need(2 * h); need(2 * h + 1); }
+              need(kc >> 1);
+              mbar_wait(&bar_full[stage], phase);
+              tc_fence_after();
+              if (lane == 0) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const uint64_t ad = umma_desc(sA_u + kc * A_CHUNK_BYTES + k * 32, desc_hi);
+                  const uint64_t bd = umma_desc(sB_u + stage * P_STAGE_BYTES + k * 32, desc_hi);
+                  umma_bf16_ss_pair(tmem_base + h * HALF_N, ad, bd, idesc, (kc | k) != 0 ? 1u : 0u);
+                }
+                umma_commit_pair(&bar_empty[stage], 0b11);
+                if (h == L.n_halves - 1 && kc == kc_q0_last) umma_commit_pair(&bar_free_q0, 0b11);
+                if (h == L.n_halves - 1 && kc == kc_lo_last) umma_commit_pair(&bar_free_lo, 0b11);
+              }
+              __syncwarp();
+              if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
+            }
+            if (lane == 0) umma_commit_pair(&bar_tmem_full[h], 0b11);
+            __syncwarp();
+          }
+          if (L.n_halves == 1) {
+            if (lane == 0) umma_commit_pair(&bar_tmem_full[1], 0b11);
+            __syncwarp();
+          }
+          // keep the per-quarter barriers in lock step when this layer's K does not need all of them
+          for (int qd = 0; qd < 4; ++qd) need(qd);
+        }
+      }
+    }
+  } else {
+    // ================================================================ epilogue warps (both CTAs)
+    const int q = warp & 3;            // TMEM lane quadrant
+    const int j = warp >> 2;           // 32-column slice of every 128-column quarter
+    const int tid = threadIdx.x;       // 0..511
+    const uint32_t rt = q * 32 + lane; // row within the tile == TMEM lane
+    const uint32_t tmem_row = tmem_base + (uint32_t(q * 32) << 16);
+    const uint32_t ready_leader = mapa_u32(smem_u32(&bar_a_ready[0]), 0);   // + 8*quarter
+    s_wlast[tid] = __ldg(args.w_last + tid);
+    uint32_t mma_iter = 0;
+    bool stores_pending = false;
+    const int tiles_alloc = int(args.n_rows_pad / TILE_M);
+
+    for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+      const int tile = 2 * tp + int(rank);
+      const bool tile_ok = tile < args.n_tiles;
+      const int tile_c = tile_ok ? tile : args.n_tiles - 1;
+      const bool valid = tile_ok && (int64_t(tile_c) * TILE_M + rt) < args.n_rows;
+      float px = 0.f, py = 0.f, pz = 0.f;
+      if (valid) {
+        const float* pt = args.xyz + (int64_t(tile_c) * TILE_M + rt) * args.xyz_stride;
+        px = __ldg(pt); py = __ldg(pt + 1); pz = __ldg(pt + 2);
+      }
+      const int scene = __ldg(args.tile_scene + tile_c);
+      float ydot = 0.0f;
+
+      for (int l = 0; l < nh; ++l) {
+        const ChainLayer& L = args.prog[l];
+        const bool last = (l == nh - 1);
+        const bool produce_a = !last;
+        const bool drop = kTrain && L.dropout != 0;
+        const bool has_acc = L.has_mma != 0;
+        const float ascale = drop ? args.drop_scale : 1.0f;
+        const float* sb = s_bias + (l & 1) * FH;
+        // ---- before the accumulators are ready: stage this layer's bias (+ xyz weights), draw the first keep words
+        {
+          const float* src = (L.bias_slot >= 0) ? (args.cbias + (size_t(scene) * 2 + L.bias_slot) * FH) : args.bias[l];
+          s_bias[(l & 1) * FH + tid] = __ldg(src + tid) * ascale;
+          if (L.has_xyz) {
+            const float* wsrc = args.wxyz[l];
+            s_wxyz[tid] = __ldg(wsrc + tid) * ascale;
+            s_wxyz[FH + tid] = __ldg(wsrc + FH + tid) * ascale;
+            s_wxyz[2 * FH + tid] = __ldg(wsrc + 2 * FH + tid) * ascale;
+          }
+        }
+        const uint64_t grow = args.row0 + uint64_t(int64_t(tile_c) * TILE_M + rt);
+        uint32_t kwa = 0xFFFFFFFFu, kwb = 0xFFFFFFFFu;
+        if (drop) {
+          kwa = dropout_keep_word(args.seed, uint32_t(l), grow, uint32_t(j), args.drop_thr);
+          kwb = dropout_keep_word(args.seed, uint32_t(l), grow, uint32_t(4 + j), args.drop_thr);
+        }
+        epi_bar();
+        const float* swx = L.has_xyz ? s_wxyz : nullptr;
+        const float* swl = last ? s_wlast : nullptr;
+        uint32_t par = 0;
+        if (has_acc) { par = mma_iter & 1; ++mma_iter; }
+        uint32_t* gdst = nullptr;
+        if (kTrain && args.bitmask != nullptr && tile_ok)
+          gdst = args.bitmask + ((size_t(l) * tiles_alloc + tile) * MASK_WORDS + j) * TILE_M + rt;   // word 4*Q + j at + 4*Q*128
+
+        // One 128-column quarter: two 16-column passes straight from TMEM into the A tile.
+        auto quarter = [&](int Q, uint32_t keep) {
+          const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
+          const uint32_t g0 = epi_pass16<kTrain>(tmem_row + c0, has_acc, ascale, sb + c0, swx ? swx + c0 : nullptr, px, py, pz, keep,
+                                                 swl ? swl + c0 : nullptr, sA, rt, c0, ydot);
+          const uint32_t g1 = epi_pass16<kTrain>(tmem_row + c0 + 16, has_acc, ascale, sb + c0 + 16, swx ? swx + c0 + 16 : nullptr, px, py,
+                                                 pz, keep >> 16, swl ? swl + c0 + 16 : nullptr, sA, rt, c0 + 16, ydot);
+          if (kTrain && gdst != nullptr) gdst[size_t(Q) * 4 * TILE_M] = g0 | (g1 << 16);
+          fence_proxy_async_all();
+          tc_fence_before();
+          __syncwarp();
+          if (produce_a && lane == 0) mbar_arrive_cluster(ready_leader + 8u * uint32_t(Q));
+        };
+
+        // ---- half 0: ready while the tensor cores still compute half 1.  Activation chunks 0,1 may be overwritten once
+        //      half 1's MMAs have passed K chunk 1 (free_q0), chunks 2,3 after K chunk 3 (free_lo); the previous layer's
+        //      stash (TMA store) must have been read out of the tile.
+        if (has_acc) { mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); mbar_wait(&bar_free_q0, par); }
+        if (kTrain && stores_pending) {
+          if (tid == 0) tma_store_wait_read0();
+          epi_bar();
+          stores_pending = false;
+        }
+        quarter(0, kwa);
+        if (has_acc) mbar_wait(&bar_free_lo, par);
+        quarter(1, kwb);
+        // ---- half 1: after all of this layer's MMAs; the next layer starts on the K chunks that are already there
+        if (drop && L.n_halves == 2) {
+          kwa = dropout_keep_word(args.seed, uint32_t(l), grow, uint32_t(8 + j), args.drop_thr);
+          kwb = dropout_keep_word(args.seed, uint32_t(l), grow, uint32_t(12 + j), args.drop_thr);
+        }
+        if (has_acc) { mbar_wait(&bar_tmem_full[1], par); tc_fence_after(); }
+        if (L.n_halves == 2) {
+          quarter(2, kwa);
+          quarter(3, kwb);
+        } else {
+          if (kTrain && gdst != nullptr) { gdst[size_t(2) * 4 * TILE_M] = 0u; gdst[size_t(3) * 4 * TILE_M] = 0u; }
+          tc_fence_before();
+          __syncwarp();
+          if (produce_a && lane == 0) { mbar_arrive_cluster(ready_leader + 16u); mbar_arrive_cluster(ready_leader + 24u); }
+        }
+        // ---- the activation stash for the backward
+        if (kTrain && args.store_acts) {
+          epi_bar();
+          if (tid == 0 && tile_ok) {
+            const int nchunks = L.n_halves * 4;
+            for (int c = 0; c < nchunks; ++c)
+              tma_store_2d(&tmActs, sA + c * A_CHUNK_BYTES, c * 64, int32_t(int64_t(l) * args.n_rows_pad + int64_t(tile) * TILE_M));
+            tma_store_commit();
+          }
+          stores_pending = true;
+        }
+      }
+
+      const int64_t lrow = int64_t(tile_c) * TILE_M + rt;
+      // ---- final layer: combine the four column slices, tanh, loss
+      s_ypart[j * TILE_M + rt] = ydot;
+      epi_bar();
+      if (j == 0) {
+        const float yv = ((s_ypart[rt] + s_ypart[TILE_M + rt]) + (s_ypart[2 * TILE_M + rt] + s_ypart[3 * TILE_M + rt])) + __ldg(args.b_last);
+        const float t1 = tanhf(yv);
+        float t = t1, dt = 1.0f - t1 * t1;
+        if (args.use_tanh) { t = tanhf(t1); dt *= (1.0f - t * t); }
+        if (valid) args.sdf_out[lrow] = t;
+        if (kTrain && args.gt != nullptr) {
+          const float g = valid ? __ldg(args.gt + lrow * args.gt_stride) : 0.0f;
+          float pc = t, gc = g, inside = 1.0f;
+          if (args.clamp > 0.0f) {
+            pc = fminf(fmaxf(t, -args.clamp), args.clamp);
+            gc = fminf(fmaxf(g, -args.clamp), args.clamp);
+            inside = (t >= -args.clamp && t <= args.clamp) ? 1.0f : 0.0f;
+          }
+          const float diff = pc - gc;
+          const float sgn = (diff > 0.0f) ? 1.0f : ((diff < 0.0f) ? -1.0f : 0.0f);
+          if (tile_ok) args.dy_out[lrow] = valid ? sgn * inside * dt * args.inv_n : 0.0f;
+          float a = valid ? fabsf(diff) : 0.0f;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+          if (lane == 0) s_loss[q] = a;
+        }
+      }
+      epi_bar();
+      if (kTrain && args.gt != nullptr && tid == 0 && tile_ok)
+        args.tile_loss[tile] = ((s_loss[0] + s_loss[1]) + s_loss[2]) + s_loss[3];
+    }
+    if (kTrain && stores_pending && tid == 0) tma_store_wait_all0();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == P_EPI_WARPS + 1) tmem_dealloc_pair<512>(tmem_base);
+}
+
+// Number of CTA pairs that can be co-resident (one CTA per SM, both CTAs of a pair on one TPC); cached per kernel.
+template <typename K>
+static int resident_pairs(K kern, int n_sms) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned(n_sms & ~1));
+  cfg.blockDim = dim3(P_THREADS);
+  cfg.dynamicSmemBytes = P_SMEM;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) { cudaGetLastError(); n = n_sms / 2; }
+  return n;
+}
+
+int launch_chain_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, const FwdArgs& args, int n_sms, cudaStream_t stream) {
+  auto kern = args.training ? chain_forward_kernel<true> : chain_forward_kernel<false>;
+  DSDF_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+  static int max_pairs[2] = {0, 0};
+  int& mp = max_pairs[args.training ? 1 : 0];
+  if (mp == 0) mp = resident_pairs(kern, n_sms);
+  const int n_pairs = (args.n_tiles + 1) / 2;
+  int grid_pairs = mp;
+  if (grid_pairs > n_pairs) grid_pairs = n_pairs;
+  if (grid_pairs < 1) grid_pairs = 1;
+  kern<<<2 * grid_pairs, P_THREADS, P_SMEM, stream>>>(tmW, tmActs, args);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int chain_forward_resident_pairs(int n_sms) {
+  cudaFuncSetAttribute(chain_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM);
+  return resident_pairs(chain_forward_kernel<true>, n_sms);
+}
+
+}  // namespace dsdf

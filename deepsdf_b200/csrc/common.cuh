@@ -60,8 +60,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++spins > DSDF_SPIN_LIMIT) {
-      printf("dsdf: mbarrier timeout block %d thread %d bar@%u parity %u\n", blockIdx.x, threadIdx.x,
-             smem_u32(bar), parity);
+#ifdef DSDF_DEBUG_BARRIERS
+      printf("dsdf: mbarrier timeout block %d thread %d bar@%u parity %u\n", blockIdx.x, threadIdx.x, smem_u32(bar), parity);
+#endif
       __trap();
     }
   }
@@ -129,6 +130,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
       : "r"(taddr)
       : "memory");
 }
+// 32 lanes x 16 consecutive fp32 columns
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ------------------------------------------------------------------ clusters / CTA pairs (cta_group::2)
@@ -166,7 +177,9 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
   uint32_t spins = 0;
   while (!mbar_try_wait_cluster(bar, parity)) {
     if (++spins > DSDF_SPIN_LIMIT) {
+#ifdef DSDF_DEBUG_BARRIERS
       printf("dsdf: cluster mbarrier timeout block %d thread %d bar@%u parity %u\n", blockIdx.x, threadIdx.x, smem_u32(bar), parity);
+#endif
       __trap();
     }
   }
@@ -238,15 +251,19 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ float bf16_lo_to_f32(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi_to_f32(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
 
-// ------------------------------------------------------------------ Philox4x32-10 dropout
-// Counter = (row_lo, row_hi, layer, col_block16); key = (seed_lo, seed_hi).  One call yields 16 bytes = the keep
-// decisions of 16 consecutive columns: keep iff byte >= thr, thr = round(p*256) (effective p = thr/256).
+// ------------------------------------------------------------------ Philox dropout (bit-sliced Bernoulli)
+// One dropout decision costs 8 random bits.  For (row, layer) and a group of 32 consecutive columns g32 = col >> 5, two
+// Philox4x32-7 calls with counter (row_lo, row_hi, layer, 2*g32 + k), k = 0,1, key = seed give eight words w0..w7.
+// Column i = col & 31 of the group draws the 8-bit number U_i = sum_b bit_i(w_b) << b, and is KEPT iff U_i >= thr,
+// thr = round(256 p) (effective p = thr/256).  Evaluated bit-sliced, 32 columns per handful of logic ops, the result is
+// a 32-bit keep word - the same format as the gate bits the forward hands to the backward.  Keyed by the GLOBAL row id,
+// so masks do not depend on tiling or on the number of ranks.  7 rounds is the Crush-resistant Philox4x32 variant.
+constexpr int kPhiloxRounds = 7;
 struct Philox4 { uint32_t x, y, z, w; };
-__host__ __device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
-                                                          uint32_t k1) {
+__host__ __device__ __forceinline__ Philox4 philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
-  for (int r = 0; r < 10; ++r) {
+  for (int r = 0; r < kPhiloxRounds; ++r) {
     uint64_t p0 = uint64_t(M0) * c0;
     uint64_t p1 = uint64_t(M1) * c2;
     uint32_t n0 = uint32_t(p1 >> 32) ^ c1 ^ k0;
@@ -258,19 +275,26 @@ __host__ __device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t 
   }
   return Philox4{c0, c1, c2, c3};
 }
-__host__ __device__ __forceinline__ Philox4 dropout_bits16(uint64_t seed, uint32_t layer, uint64_t row, uint32_t col_block16) {
-  return philox4x32_10(uint32_t(row), uint32_t(row >> 32), layer, col_block16, uint32_t(seed), uint32_t(seed >> 32));
-}
 __host__ __device__ __forceinline__ uint32_t dropout_threshold(float p) {
   int t = int(p * 256.0f + 0.5f);
   return uint32_t(t < 0 ? 0 : (t > 255 ? 255 : t));
 }
-// keep decision of a single (row, col): used by the generic path and the tests
+// keep word of columns [32*g32, 32*g32 + 32) of (row, layer): bit i set <=> column 32*g32 + i is kept
+__host__ __device__ __forceinline__ uint32_t dropout_keep_word(uint64_t seed, uint32_t layer, uint64_t row, uint32_t g32, uint32_t thr) {
+  const Philox4 a = philox4x32(uint32_t(row), uint32_t(row >> 32), layer, 2u * g32, uint32_t(seed), uint32_t(seed >> 32));
+  const Philox4 b = philox4x32(uint32_t(row), uint32_t(row >> 32), layer, 2u * g32 + 1u, uint32_t(seed), uint32_t(seed >> 32));
+  const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  uint32_t lt = 0u, eq = 0xFFFFFFFFu;          // bit-sliced U < thr, scanning from the most significant bit
+#pragma unroll
+  for (int bit = 7; bit >= 0; --bit) {
+    if ((thr >> bit) & 1u) { lt |= eq & ~w[bit]; eq &= w[bit]; }
+    else { eq &= ~w[bit]; }
+  }
+  return ~lt;
+}
+// keep decision of a single (row, col): used by the generic path and the mask export
 __host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint32_t layer, uint64_t row, uint32_t col, uint32_t thr) {
-  Philox4 r = dropout_bits16(seed, layer, row, col >> 4);
-  uint32_t word = (col & 8u) ? ((col & 4u) ? r.w : r.z) : ((col & 4u) ? r.y : r.x);
-  uint32_t byte = (word >> ((col & 3u) * 8u)) & 0xFFu;
-  return byte >= thr;
+  return (dropout_keep_word(seed, layer, row, col >> 5, thr) >> (col & 31u)) & 1u;
 }
 
 }  // namespace dsdf

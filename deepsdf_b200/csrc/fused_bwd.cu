@@ -149,7 +149,8 @@ fused_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         const int n_halves = has_mma ? args.prog[t + 1].n_halves : 2;
         const float scale = args.scale[t];
         const bool produce_a = (t > 0);
-        const uint32_t* mrow = args.bitmask + (size_t(t) * args.n_rows_pad + lrow) * MASK_WORDS;
+        // gate bits: [layer][tile][16 words][128 rows]
+        const uint32_t* mrow = args.bitmask + (size_t(t) * (args.n_rows_pad / TILE_M) + tile) * MASK_WORDS * TILE_M + rt;
         uint32_t par = 0;
         if (has_mma) { par = mma_iter & 1; ++mma_iter; }
         uint32_t hold[64];
@@ -157,8 +158,8 @@ fused_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         // ---- half 0 -> registers
         if (has_mma) { mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); }
         {
-          const uint4 mw = __ldg(reinterpret_cast<const uint4*>(mrow + j * 4));
-          const uint32_t mwords[4] = {mw.x, mw.y, mw.z, mw.w};
+          const uint32_t mwords[4] = {__ldg(mrow + (j * 4 + 0) * TILE_M), __ldg(mrow + (j * 4 + 1) * TILE_M),
+                                      __ldg(mrow + (j * 4 + 2) * TILE_M), __ldg(mrow + (j * 4 + 3) * TILE_M)};
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const uint32_t c0 = j * 128 + g * 32;
@@ -196,8 +197,8 @@ fused_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
 
         // ---- half 1
         if (n_halves == 2) {
-          const uint4 mw = __ldg(reinterpret_cast<const uint4*>(mrow + 8 + j * 4));
-          const uint32_t mwords[4] = {mw.x, mw.y, mw.z, mw.w};
+          const uint32_t mwords[4] = {__ldg(mrow + (8 + j * 4 + 0) * TILE_M), __ldg(mrow + (8 + j * 4 + 1) * TILE_M),
+                                      __ldg(mrow + (8 + j * 4 + 2) * TILE_M), __ldg(mrow + (8 + j * 4 + 3) * TILE_M)};
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const uint32_t c0 = HALF_N + j * 128 + g * 32;

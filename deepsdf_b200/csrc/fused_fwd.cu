@@ -62,17 +62,9 @@ __device__ __forceinline__ void epi_group(float (&v)[32], uint32_t c0, const Epi
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.0f);
   if (kTrain && cx.dropout) {
+    const uint32_t keep = dropout_keep_word(cx.seed, cx.layer, cx.grow, c0 >> 5, cx.thr);
 #pragma unroll
-    for (int hb = 0; hb < 2; ++hb) {
-      Philox4 r = dropout_bits16(cx.seed, cx.layer, cx.grow, (c0 >> 4) + hb);
-      uint32_t w[4] = {r.x, r.y, r.z, r.w};
-#pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        uint32_t byte = (w[i >> 2] >> ((i & 3) * 8)) & 0xFFu;
-        float s = (byte >= cx.thr) ? cx.scale : 0.0f;
-        v[hb * 16 + i] *= s;
-      }
-    }
+    for (int i = 0; i < 32; ++i) v[i] = ((keep >> i) & 1u) ? v[i] * cx.scale : 0.0f;
   }
   bits = 0;
 #pragma unroll
@@ -243,8 +235,9 @@ fused_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           for (int i = 0; i < 16; ++i) hold[g * 16 + i] = p[i];
         }
         if (kTrain && args.bitmask != nullptr) {
-          uint4* dst = reinterpret_cast<uint4*>(args.bitmask + (size_t(l) * args.n_rows_pad + lrow) * MASK_WORDS + j * 4);
-          *dst = make_uint4(mask_words[0], mask_words[1], mask_words[2], mask_words[3]);
+          uint32_t* dst = args.bitmask + ((size_t(l) * (args.n_rows_pad / TILE_M) + tile) * MASK_WORDS + j * 4) * TILE_M + rt;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) dst[size_t(g) * TILE_M] = mask_words[g];
         }
         // ---- all MMAs of this layer retired -> the A tile may be overwritten
         if (L.has_mma) { mbar_wait(&bar_tmem_full[1], par); tc_fence_after(); }
@@ -281,13 +274,15 @@ fused_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
             store_group(sA, rt, c0, p);
           }
           if (kTrain && args.bitmask != nullptr) {
-            uint4* dst = reinterpret_cast<uint4*>(args.bitmask + (size_t(l) * args.n_rows_pad + lrow) * MASK_WORDS + 8 + j * 4);
-            *dst = make_uint4(mask_words[0], mask_words[1], mask_words[2], mask_words[3]);
+            uint32_t* dst = args.bitmask + ((size_t(l) * (args.n_rows_pad / TILE_M) + tile) * MASK_WORDS + 8 + j * 4) * TILE_M + rt;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) dst[size_t(g) * TILE_M] = mask_words[g];
           }
           fence_proxy_async_smem();
         } else if (kTrain && args.bitmask != nullptr) {
-          uint4* dst = reinterpret_cast<uint4*>(args.bitmask + (size_t(l) * args.n_rows_pad + lrow) * MASK_WORDS + 8 + j * 4);
-          *dst = make_uint4(0u, 0u, 0u, 0u);
+          uint32_t* dst = args.bitmask + ((size_t(l) * (args.n_rows_pad / TILE_M) + tile) * MASK_WORDS + 8 + j * 4) * TILE_M + rt;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) dst[size_t(g) * TILE_M] = 0u;
         }
         tc_fence_before();
         __syncwarp();

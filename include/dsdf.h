@@ -72,7 +72,8 @@ const char* dsdf_last_error(void);
 int dsdf_check_device(void);
 
 /* ------------------------------------------------------------------------------------------------
- * Dropout: Philox4x32-10, counter (row, layer, col/16), key seed; keep iff byte >= round(p*256).
+ * Dropout: Philox4x32-7, counter (row, layer, 2*(col/32)+k), key seed; 8 random bits per decision, bit-sliced over 32
+ * columns; keep iff the 8-bit draw >= round(p*256) (csrc/common.cuh).
  * Writes the {0,1} keep mask of one hidden layer as uint8 [n_rows, width] (tests / oracle hand-over). */
 int dsdf_dropout_mask(uint64_t seed, uint32_t layer, uint64_t row0, int64_t n_rows, int32_t width, float p,
                       uint8_t* mask_out, void* stream);

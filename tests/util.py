@@ -86,10 +86,12 @@ def emulate_fused_forward(ospec, params, table, row_scene, xyz, masks=None):
 
 
 def unpack_gate_bits(bitmask: torch.Tensor, ospec, n_rows: int):
-    """The fused forward's 1-bit relu*dropout gates (dsdf_train_io.bitmask: uint32 [num_hidden][n_rows_pad][16], word w bit i
-    = column 32*w + i) -> {layer: float {0,1} [n_rows, out_dim]} on the CPU."""
+    """The fused forward's 1-bit relu*dropout gates (dsdf_train_io.bitmask: uint32 [num_hidden][n_tiles][16 words][128 rows],
+    word w bit i = column 32*w + i) -> {layer: float {0,1} [n_rows, out_dim]} on the CPU."""
     nh = ospec.num_linear - 1
-    words = bitmask.view(torch.int32).reshape(nh, -1, 16)[:, :n_rows].cpu().numpy().astype(np.uint32)
+    n_tiles = (n_rows + 127) // 128
+    words = bitmask.view(torch.int32)[:nh * n_tiles * 16 * 128].reshape(nh, n_tiles, 16, 128).permute(0, 1, 3, 2)
+    words = words.reshape(nh, n_tiles * 128, 16)[:, :n_rows].cpu().numpy().astype(np.uint32)
     out = {}
     for l in range(nh):
         bits = ((words[l][:, :, None] >> np.arange(32, dtype=np.uint32)[None, None, :]) & 1).reshape(n_rows, 512)
