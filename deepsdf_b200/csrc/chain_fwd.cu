@@ -153,74 +153,96 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
 
   if (warp == P_EPI_WARPS) {
     // ================================================================ TMA producer (this CTA's half of every weight block)
-    if (lane == 0) {
+    {
+      // the whole warp walks the loop (warp-uniform values stay in uniform registers); one elected lane issues
       const uint32_t full_leader = mapa_u32(smem_u32(&bar_full[0]), 0);
-      int stage = 0; uint32_t phase = 0;
+      const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]), sB_u = smem_u32(sB);
+      uint32_t stage = 0, phase = 0;
       for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
         for (int l = 0; l < nh; ++l) {
-          const ChainLayer& L = args.prog[l];
-          if (!L.has_mma) continue;
-          for (int h = 0; h < L.n_halves; ++h)
-            for (int kc = 0; kc < L.k_chunks; ++kc) {
-              mbar_wait(&bar_empty[stage], phase ^ 1);
-              if (leader) mbar_arrive_expect_tx(&bar_full[stage], 2 * P_STAGE_BYTES);
-              tma_load_2d_pair(sB + stage * P_STAGE_BYTES, &tmW, full_leader + stage * 8, kc * 64,
-                               L.w_row0 + h * HALF_N + int(rank) * 128);
+          if (!args.prog[l].has_mma) continue;
+          const int n_halves = args.prog[l].n_halves, k_chunks = args.prog[l].k_chunks;
+          const int row_base = args.prog[l].w_row0 + int(rank) * 128;
+          for (int h = 0; h < n_halves; ++h)
+            for (int kc = 0; kc < k_chunks; ++kc) {
+              mbar_wait_a(empty0 + stage * 8, phase ^ 1);
+              if (elect_one()) {
+                if (leader) mbar_arrive_expect_tx_a(full0 + stage * 8, 2 * P_STAGE_BYTES);
+                tma_load_2d_pair_a(sB_u + stage * P_STAGE_BYTES, &tmW, full_leader + stage * 8, kc * 64, row_base + h * HALF_N);
+              }
+              __syncwarp();
               if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
             }
         }
       }
     }
   } else if (warp == P_EPI_WARPS + 1) {
-    // ================================================================ MMA issuer (leader CTA only)
+    // ================================================================ MMA issuer (leader CTA).  The whole warp walks the
+    // loop so that every operand is warp-uniform (uniform registers feed UTCHMMA directly; issuing from a divergent
+    // `lane == 0` branch makes the compiler wrap each MMA in an ELECT / R2UR waterfall that costs more than the 128
+    // tensor-core cycles the MMA itself takes); one elected lane issues.  Barrier addresses, descriptor bases and the
+    // layer fields are precomputed: the warp must issue four MMAs (= 512 tensor cycles) per stage without being the bottleneck.
     if (leader) {
       const uint32_t idesc = umma_idesc_bf16(2 * TILE_M, HALF_N, 0, 0);
       const uint64_t desc_hi = umma_desc_hi_sw128(16, 1024);
-      const uint32_t sA_u = smem_u32(sA), sB_u = smem_u32(sB);
-      int stage = 0; uint32_t phase = 0; uint32_t a_cons = 0;
+      const uint64_t a_base = desc_hi | uint64_t((smem_u32(sA) >> 4) & 0x3FFF);
+      const uint64_t b_base = desc_hi | uint64_t((smem_u32(sB) >> 4) & 0x3FFF);
+      const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]);
+      const uint32_t tfull0 = smem_u32(&bar_tmem_full[0]), fq0 = smem_u32(&bar_free_q0), flo = smem_u32(&bar_free_lo);
+      const uint32_t ready0 = smem_u32(&bar_a_ready[0]);
+      uint32_t stage = 0, phase = 0, a_cons = 0;
       for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
         for (int l = 0; l < nh; ++l) {
-          const ChainLayer& L = args.prog[l];
-          if (!L.has_mma) continue;
+          if (!args.prog[l].has_mma) continue;
+          const int n_halves = args.prog[l].n_halves, k_chunks = args.prog[l].k_chunks;
           const uint32_t apar = a_cons & 1; ++a_cons;
-          const int kc_lo_last = L.k_chunks < 4 ? L.k_chunks - 1 : 3;
-          const int kc_q0_last = L.k_chunks < 2 ? L.k_chunks - 1 : 1;
+          const int kc_lo_last = k_chunks < 4 ? k_chunks - 1 : 3;
+          const int kc_q0_last = k_chunks < 2 ? k_chunks - 1 : 1;
           uint32_t waited = 0;     // quarters of the previous layer's output whose a_ready has been consumed
-          auto need = [&](int qd) {
-            if (!((waited >> qd) & 1u)) { mbar_wait_cluster(&bar_a_ready[qd], apar); waited |= 1u << qd; }
-          };
-          for (int h = 0; h < L.n_halves; ++h) {
-            for (int kc = 0; kc < L.k_chunks; ++kc) {
+          for (int h = 0; h < n_halves; ++h) {
+            const bool last_half = (h == n_halves - 1);
+            for (int kc = 0; kc < k_chunks; ++kc) {
               // K chunk kc reads quarter kc/2 of the A tile.  Besides, the first MMA of half h overwrites that half's
               // accumulators, which the previous layer's epilogue reads quarter by quarter: half 0 needs quarters 0,1
               // drained, half 1 needs quarters 2,3.
-              if (kc == 0) { need(2 * h); need(2 * h + 1); }
-              need(kc >> 1);
-              mbar_wait(&bar_full[stage], phase);
+              uint32_t needm = 1u << (kc >> 1);
+              if (kc == 0) needm |= 3u << (2 * h);
+              needm &= ~waited;
+              while (needm) {
+                const int qd = __ffs(int(needm)) - 1;
+                mbar_wait_a(ready0 + qd * 8, apar);
+                needm &= needm - 1;
+                waited |= 1u << qd;
+              }
+              mbar_wait_a(full0 + stage * 8, phase);
               tc_fence_after();
-              if (lane == 0) {
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  const uint64_t ad = umma_desc(sA_u + kc * A_CHUNK_BYTES + k * 32, desc_hi);
-                  const uint64_t bd = umma_desc(sB_u + stage * P_STAGE_BYTES + k * 32, desc_hi);
-                  umma_bf16_ss_pair(tmem_base + h * HALF_N, ad, bd, idesc, (kc | k) != 0 ? 1u : 0u);
+              const uint64_t ad = a_base + uint64_t(kc * (A_CHUNK_BYTES >> 4));
+              const uint64_t bd = b_base + uint64_t(stage * (P_STAGE_BYTES >> 4));
+              const uint32_t d = tmem_base + h * HALF_N;
+              if (elect_one()) {
+                umma_bf16_ss_pair(d, ad, bd, idesc, kc != 0 ? 1u : 0u);
+                umma_bf16_ss_pair(d, ad + 2, bd + 2, idesc, 1u);
+                umma_bf16_ss_pair(d, ad + 4, bd + 4, idesc, 1u);
+                umma_bf16_ss_pair(d, ad + 6, bd + 6, idesc, 1u);
+                umma_commit_pair_a(empty0 + stage * 8, 0b11);
+                if (last_half && kc == kc_q0_last) umma_commit_pair_a(fq0, 0b11);
+                if (last_half && kc == kc_lo_last) umma_commit_pair_a(flo, 0b11);
+                if (kc == k_chunks - 1) {
+                  umma_commit_pair_a(tfull0 + h * 8, 0b11);
+                  if (n_halves == 1) umma_commit_pair_a(tfull0 + 8, 0b11);
                 }
-                umma_commit_pair(&bar_empty[stage], 0b11);
-                if (h == L.n_halves - 1 && kc == kc_q0_last) umma_commit_pair(&bar_free_q0, 0b11);
-                if (h == L.n_halves - 1 && kc == kc_lo_last) umma_commit_pair(&bar_free_lo, 0b11);
               }
               __syncwarp();
               if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
             }
-            if (lane == 0) umma_commit_pair(&bar_tmem_full[h], 0b11);
-            __syncwarp();
           }
-          if (L.n_halves == 1) {
-            if (lane == 0) umma_commit_pair(&bar_tmem_full[1], 0b11);
-            __syncwarp();
+          // keep the per-quarter barriers in lock step when this layer's K did not need all of them
+          uint32_t rest = 0xFu & ~waited;
+          while (rest) {
+            const int qd = __ffs(int(rest)) - 1;
+            mbar_wait_a(ready0 + qd * 8, apar);
+            rest &= rest - 1;
           }
-          // keep the per-quarter barriers in lock step when this layer's K does not need all of them
-          for (int qd = 0; qd < 4; ++qd) need(qd);
         }
       }
     }
@@ -292,10 +314,10 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           const uint32_t g1 = epi_pass16<kTrain>(tmem_row + c0 + 16, has_acc, ascale, sb + c0 + 16, swx ? swx + c0 + 16 : nullptr, px, py,
                                                  pz, keep >> 16, swl ? swl + c0 + 16 : nullptr, sA, rt, c0 + 16, ydot);
           if (kTrain && gdst != nullptr) gdst[size_t(Q) * 4 * TILE_M] = g0 | (g1 << 16);
-          fence_proxy_async_all();
+          fence_proxy_async_smem();
           tc_fence_before();
           __syncwarp();
-          if (produce_a && lane == 0) mbar_arrive_cluster(ready_leader + 8u * uint32_t(Q));
+          if (produce_a && lane == 0) mbar_arrive_remote(ready_leader + 8u * uint32_t(Q));
         };
 
         // ---- half 0: ready while the tensor cores still compute half 1.  Activation chunks 0,1 may be overwritten once
@@ -323,7 +345,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           if (kTrain && gdst != nullptr) { gdst[size_t(2) * 4 * TILE_M] = 0u; gdst[size_t(3) * 4 * TILE_M] = 0u; }
           tc_fence_before();
           __syncwarp();
-          if (produce_a && lane == 0) { mbar_arrive_cluster(ready_leader + 16u); mbar_arrive_cluster(ready_leader + 24u); }
+          if (produce_a && lane == 0) { mbar_arrive_remote(ready_leader + 16u); mbar_arrive_remote(ready_leader + 24u); }
         }
         // ---- the activation stash for the backward
         if (kTrain && args.store_acts) {
