@@ -1,0 +1,347 @@
+// Fused DeepSDF decoder backward, data-gradient chain, CTA-pair version (sm_100a: tcgen05 cta_group::2 + TMEM + TMA).
+//
+// Mirror image of chain_fwd.cu (same pair / pipeline structure, see there).  Per 128-row tile, for t = last hidden layer
+// .. 0 the kernel produces
+//   dY_t = dX_{t+1} (.) gate_t        dX_{t+1} = dY_{t+1} . W_{t+1}   (tensor cores, W^T streamed through the TMA ring)
+// with dY of the last hidden layer seeded by the rank-1 product dL/dy * w_last.  The dY tile lives in shared memory as
+// bf16 (SW128: the A operand of the next chain link), the gates are the 1-bit relu*dropout words written by the forward,
+// and the dropout scale is applied with the gate.  Once a tile of dY_t is complete the 16 epilogue warps also emit
+//   * its column sums (bias gradients; the per-scene sums of dY_0 / dY_skip ARE the latent-code gradient up to a tiny
+//     [S x 512] x [512 x L] product, so the latent-gradient reduction is a fixed-order sum of per-tile partials),
+//   * the xyz-weighted column sums of dY_0 / dY_skip (gradients of the xyz weight columns),
+//   * the bf16 dY tile itself (TMA store) that wgrad.cu contracts with the stashed activations.
+// The data gradient w.r.t. lin0's input is never formed: training only needs it reduced per scene.
+// Replaces the autograd graph of train_deep_sdf.py:533 (data-gradient part).
+#include "common.cuh"
+#include "fused.cuh"
+#include "host_util.h"
+
+namespace dsdf {
+
+namespace {
+
+constexpr int B_EPI_WARPS = 16;
+constexpr int B_EPI_THREADS = B_EPI_WARPS * 32;
+constexpr int B_THREADS = (B_EPI_WARPS + 2) * 32;
+constexpr int B_STAGES = 5;
+constexpr int B_STAGE_BYTES = 128 * 128;
+constexpr int B_OFF_B = A_BYTES;
+constexpr int B_OFF_WLAST = B_OFF_B + B_STAGES * B_STAGE_BYTES;   // f32 [512]
+constexpr int B_OFF_XYZ = B_OFF_WLAST + FH * 4;                   // f32 [3][128]
+constexpr int B_SMEM = B_OFF_XYZ + 3 * TILE_M * 4 + 1024;
+
+__device__ __forceinline__ void bwd_bar() { asm volatile("bar.sync 1, %0;" ::"n"(B_EPI_THREADS) : "memory"); }
+
+// 16 columns [c0, c0+16) of one row: v = accumulators (or dy * w_last), gated and scaled, packed to bf16 into the A tile
+__device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float dyv, const float* swl, uint32_t gate16, float scale,
+                                           uint8_t* sA, uint32_t row, uint32_t c0) {
+  float v[16];
+  if (has_acc) {
+    uint32_t r[16];
+    tmem_ld16(taddr, r);
+    tmem_ld_wait();
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]) * scale;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float4 w = *reinterpret_cast<const float4*>(swl + 4 * k);
+      const float d = dyv * scale;
+      v[4 * k + 0] = d * w.x; v[4 * k + 1] = d * w.y; v[4 * k + 2] = d * w.z; v[4 * k + 3] = d * w.w;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = (gate16 & (1u << i)) ? v[i] : 0.0f;
+  uint8_t* base = sA + (c0 >> 6) * A_CHUNK_BYTES + row * 128u;
+  const uint32_t piece0 = (c0 & 63u) >> 3;
+  *reinterpret_cast<uint4*>(base + ((piece0 ^ (row & 7u)) << 4)) =
+      make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  *reinterpret_cast<uint4*>(base + (((piece0 + 1) ^ (row & 7u)) << 4)) =
+      make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+}
+
+}  // namespace
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(B_THREADS, 1)
+chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmDys,
+                   const __grid_constant__ BwdArgs args) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + B_OFF_B;
+  float* s_wlast = reinterpret_cast<float*>(smem + B_OFF_WLAST);
+  float* s_xyz = reinterpret_cast<float*>(smem + B_OFF_XYZ);
+  __shared__ uint64_t bar_full[B_STAGES], bar_empty[B_STAGES], bar_tmem_full[2], bar_free_q0, bar_free_lo, bar_a_ready[4];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < B_STAGES; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    mbar_init(&bar_tmem_full[0], 1); mbar_init(&bar_tmem_full[1], 1);
+    mbar_init(&bar_free_q0, 1);
+    mbar_init(&bar_free_lo, 1);
+    for (int i = 0; i < 4; ++i) mbar_init(&bar_a_ready[i], 2 * B_EPI_WARPS);
+    fence_barrier_init();
+  }
+  if (warp == B_EPI_WARPS + 1) tmem_alloc_pair<512>(&tmem_slot);
+  if (warp == B_EPI_WARPS && lane == 0) { tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmDys); }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int nh = args.num_hidden;
+  const int n_pairs = (args.n_tiles + 1) >> 1;
+  const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
+
+  if (warp == B_EPI_WARPS) {
+    // ================================================================ TMA producer (this CTA's half of every W^T block)
+    const uint32_t full_leader = mapa_u32(smem_u32(&bar_full[0]), 0);
+    const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]), sB_u = smem_u32(sB);
+    uint32_t stage = 0, phase = 0;
+    for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+      for (int t = nh - 2; t >= 0; --t) {
+        const int n_halves = args.prog[t + 1].n_halves, k_chunks = args.prog[t + 1].k_chunks;
+        const int row_base = args.prog[t + 1].w_row0 + int(rank) * 128;
+        for (int h = 0; h < n_halves; ++h)
+          for (int kc = 0; kc < k_chunks; ++kc) {
+            mbar_wait_a(empty0 + stage * 8, phase ^ 1);
+            if (elect_one()) {
+              if (leader) mbar_arrive_expect_tx_a(full0 + stage * 8, 2 * B_STAGE_BYTES);
+              tma_load_2d_pair_a(sB_u + stage * B_STAGE_BYTES, &tmW, full_leader + stage * 8, kc * 64, row_base + h * HALF_N);
+            }
+            __syncwarp();
+            if (++stage == B_STAGES) { stage = 0; phase ^= 1; }
+          }
+      }
+    }
+  } else if (warp == B_EPI_WARPS + 1) {
+    // ================================================================ MMA issuer (leader CTA; whole warp, elected issue)
+    if (leader) {
+      const uint32_t idesc = umma_idesc_bf16(2 * TILE_M, HALF_N, 0, 0);
+      const uint64_t desc_hi = umma_desc_hi_sw128(16, 1024);
+      const uint64_t a_base = desc_hi | uint64_t((smem_u32(sA) >> 4) & 0x3FFF);
+      const uint64_t b_base = desc_hi | uint64_t((smem_u32(sB) >> 4) & 0x3FFF);
+      const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]);
+      const uint32_t tfull0 = smem_u32(&bar_tmem_full[0]), fq0 = smem_u32(&bar_free_q0), flo = smem_u32(&bar_free_lo);
+      const uint32_t ready0 = smem_u32(&bar_a_ready[0]);
+      uint32_t stage = 0, phase = 0, a_cons = 0;
+      for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+        for (int t = nh - 2; t >= 0; --t) {
+          const int n_halves = args.prog[t + 1].n_halves, k_chunks = args.prog[t + 1].k_chunks;
+          const uint32_t apar = a_cons & 1; ++a_cons;
+          const int kc_lo_last = k_chunks < 4 ? k_chunks - 1 : 3;
+          const int kc_q0_last = k_chunks < 2 ? k_chunks - 1 : 1;
+          uint32_t waited = 0;
+          for (int h = 0; h < n_halves; ++h) {
+            const bool last_half = (h == n_halves - 1);
+            for (int kc = 0; kc < k_chunks; ++kc) {
+              uint32_t needm = 1u << (kc >> 1);
+              if (kc == 0) needm |= 3u << (2 * h);      // the first MMA of a half overwrites accumulators the epilogue reads
+              needm &= ~waited;
+              while (needm) {
+                const int qd = __ffs(int(needm)) - 1;
+                mbar_wait_a(ready0 + qd * 8, apar);
+                needm &= needm - 1;
+                waited |= 1u << qd;
+              }
+              mbar_wait_a(full0 + stage * 8, phase);
+              tc_fence_after();
+              const uint64_t ad = a_base + uint64_t(kc * (A_CHUNK_BYTES >> 4));
+              const uint64_t bd = b_base + uint64_t(stage * (B_STAGE_BYTES >> 4));
+              const uint32_t d = tmem_base + h * HALF_N;
+              if (elect_one()) {
+                umma_bf16_ss_pair(d, ad, bd, idesc, kc != 0 ? 1u : 0u);
+                umma_bf16_ss_pair(d, ad + 2, bd + 2, idesc, 1u);
+                umma_bf16_ss_pair(d, ad + 4, bd + 4, idesc, 1u);
+                umma_bf16_ss_pair(d, ad + 6, bd + 6, idesc, 1u);
+                umma_commit_pair_a(empty0 + stage * 8, 0b11);
+                if (last_half && kc == kc_q0_last) umma_commit_pair_a(fq0, 0b11);
+                if (last_half && kc == kc_lo_last) umma_commit_pair_a(flo, 0b11);
+                if (kc == k_chunks - 1) {
+                  umma_commit_pair_a(tfull0 + h * 8, 0b11);
+                  if (n_halves == 1) umma_commit_pair_a(tfull0 + 8, 0b11);
+                }
+              }
+              __syncwarp();
+              if (++stage == B_STAGES) { stage = 0; phase ^= 1; }
+            }
+          }
+          uint32_t rest = 0xFu & ~waited;
+          while (rest) {
+            const int qd = __ffs(int(rest)) - 1;
+            mbar_wait_a(ready0 + qd * 8, apar);
+            rest &= rest - 1;
+          }
+        }
+      }
+    }
+  } else {
+    // ================================================================ epilogue warps (both CTAs)
+    const int q = warp & 3;
+    const int j = warp >> 2;
+    const int tid = threadIdx.x;
+    const uint32_t rt = q * 32 + lane;
+    const uint32_t tmem_row = tmem_base + (uint32_t(q * 32) << 16);
+    const uint32_t ready_leader = mapa_u32(smem_u32(&bar_a_ready[0]), 0);
+    s_wlast[tid] = __ldg(args.w_last + tid);
+    uint32_t mma_iter = 0;
+    bool stores_pending = false;
+    const int tiles_alloc = int(args.n_rows_pad / TILE_M);
+
+    for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+      const int tile = 2 * tp + int(rank);
+      const bool tile_ok = tile < args.n_tiles;
+      const int tile_c = tile_ok ? tile : args.n_tiles - 1;
+      const int64_t lrow = int64_t(tile_c) * TILE_M + rt;
+      const bool valid = tile_ok && lrow < args.n_rows;
+      const float dyv = valid ? __ldg(args.dy + lrow) : 0.0f;
+      if (j == 0) {
+        const float* pt = args.xyz + lrow * args.xyz_stride;
+        s_xyz[rt] = valid ? __ldg(pt + 0) : 0.0f;
+        s_xyz[TILE_M + rt] = valid ? __ldg(pt + 1) : 0.0f;
+        s_xyz[2 * TILE_M + rt] = valid ? __ldg(pt + 2) : 0.0f;
+      }
+
+      for (int t = nh - 1; t >= 0; --t) {
+        const bool has_acc = (t < nh - 1);
+        const int n_halves = has_acc ? args.prog[t + 1].n_halves : 2;
+        const float scale = args.scale[t];
+        const bool produce_a = (t > 0);
+        // gate words of this row: word 4*Q + j of [layer][tile][16][128]
+        const uint32_t* mrow = args.bitmask + ((size_t(t) * tiles_alloc + tile_c) * MASK_WORDS + j) * TILE_M + rt;
+        uint32_t gw0 = 0, gw1 = 0, gw2 = 0, gw3 = 0;
+        if (tile_ok) {
+          gw0 = __ldg(mrow); gw1 = __ldg(mrow + 4 * TILE_M);
+          if (n_halves == 2) { gw2 = __ldg(mrow + 8 * TILE_M); gw3 = __ldg(mrow + 12 * TILE_M); }
+        }
+        // every warp has finished the column-sum pass over the previous dY tile before anyone overwrites it
+        bwd_bar();
+        uint32_t par = 0;
+        if (has_acc) { par = mma_iter & 1; ++mma_iter; }
+
+        auto quarter = [&](int Q, uint32_t gate) {
+          const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
+          bwd_pass16(tmem_row + c0, has_acc, dyv, s_wlast + c0, gate, scale, sA, rt, c0);
+          bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, s_wlast + c0 + 16, gate >> 16, scale, sA, rt, c0 + 16);
+          fence_proxy_async_smem();
+          tc_fence_before();
+          __syncwarp();
+          if (produce_a && lane == 0) mbar_arrive_remote(ready_leader + 8u * uint32_t(Q));
+        };
+
+        if (has_acc) { mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); mbar_wait(&bar_free_q0, par); }
+        if (stores_pending) {
+          if (tid == 0) tma_store_wait_read0();
+          bwd_bar();
+          stores_pending = false;
+        }
+        quarter(0, gw0);
+        if (has_acc) mbar_wait(&bar_free_lo, par);
+        quarter(1, gw1);
+        if (has_acc) { mbar_wait(&bar_tmem_full[1], par); tc_fence_after(); }
+        if (n_halves == 2) {
+          quarter(2, gw2);
+          quarter(3, gw3);
+        } else {
+          tc_fence_before();
+          __syncwarp();
+          if (produce_a && lane == 0) { mbar_arrive_remote(ready_leader + 16u); mbar_arrive_remote(ready_leader + 24u); }
+        }
+
+        // ---- tile of dY_t complete in shared memory: stash + column sums
+        bwd_bar();
+        if (args.store_dys && t > 0) {
+          if (tid == 0 && tile_ok) {
+            const int nchunks = n_halves * 4;
+            for (int c = 0; c < nchunks; ++c)
+              tma_store_2d(&tmDys, sA + c * A_CHUNK_BYTES, c * 64, int32_t(int64_t(t) * args.n_rows_pad + int64_t(tile) * TILE_M));
+            tma_store_commit();
+          }
+          stores_pending = true;
+        }
+        {
+          // warp w owns columns [32w, 32w+32): lane = (row parity, bf16x2 word); rows 2i + parity, i = 0..63
+          const int cw = warp * 32;
+          const bool cols_valid = cw < n_halves * 256;
+          const bool want_xyz = args.xyzsum_slot[t] >= 0;
+          const int word = lane & 15, rpar = lane >> 4;
+          float s0 = 0.f, s1 = 0.f, sx0 = 0.f, sx1 = 0.f, sy0 = 0.f, sy1 = 0.f, sz0 = 0.f, sz1 = 0.f;
+          if (cols_valid) {
+            const uint8_t* cb = sA + (cw >> 6) * A_CHUNK_BYTES;
+            const uint32_t colw = uint32_t(cw & 63) / 2 + word;            // bf16x2 word index within the 64-column chunk row
+#pragma unroll 4
+            for (int i = 0; i < TILE_M / 2; ++i) {
+              const int r = 2 * i + rpar;
+              const uint32_t w = *reinterpret_cast<const uint32_t*>(cb + r * 128 + ((((colw >> 2) ^ (r & 7)) << 4) | ((colw & 3) << 2)));
+              const float lo = bf16_lo_to_f32(w), hi = bf16_hi_to_f32(w);
+              s0 += lo; s1 += hi;
+              if (want_xyz) {
+                const float x = s_xyz[r], y = s_xyz[TILE_M + r], z = s_xyz[2 * TILE_M + r];
+                sx0 += x * lo; sx1 += x * hi; sy0 += y * lo; sy1 += y * hi; sz0 += z * lo; sz1 += z * hi;
+              }
+            }
+          }
+          // combine the two row parities (fixed order: even rows + odd rows)
+          s0 += __shfl_down_sync(0xffffffffu, s0, 16); s1 += __shfl_down_sync(0xffffffffu, s1, 16);
+          if (want_xyz) {
+            sx0 += __shfl_down_sync(0xffffffffu, sx0, 16); sx1 += __shfl_down_sync(0xffffffffu, sx1, 16);
+            sy0 += __shfl_down_sync(0xffffffffu, sy0, 16); sy1 += __shfl_down_sync(0xffffffffu, sy1, 16);
+            sz0 += __shfl_down_sync(0xffffffffu, sz0, 16); sz1 += __shfl_down_sync(0xffffffffu, sz1, 16);
+          }
+          if (tile_ok && rpar == 0) {
+            float* part = args.tile_part + size_t(tile) * args.part_stride;
+            const int col = cw + word * 2;
+            if (args.colsum_slot[t] >= 0)
+              *reinterpret_cast<float2*>(part + args.colsum_slot[t] * FH + col) = make_float2(s0, s1);
+            if (want_xyz) {
+              const int sl = args.xyzsum_slot[t];
+              *reinterpret_cast<float2*>(part + (sl + 0) * FH + col) = make_float2(sx0, sx1);
+              *reinterpret_cast<float2*>(part + (sl + 1) * FH + col) = make_float2(sy0, sy1);
+              *reinterpret_cast<float2*>(part + (sl + 2) * FH + col) = make_float2(sz0, sz1);
+            }
+          }
+        }
+      }
+      // s_xyz of this tile must not be overwritten while a slower warp is still in the last column-sum pass
+      bwd_bar();
+    }
+    if (stores_pending && tid == 0) tma_store_wait_all0();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == B_EPI_WARPS + 1) tmem_dealloc_pair<512>(tmem_base);
+}
+
+int launch_chain_dgrad(const CUtensorMap& tmW, const CUtensorMap& tmDys, const BwdArgs& args, int n_sms, cudaStream_t stream) {
+  DSDF_CHECK_CUDA(cudaFuncSetAttribute(chain_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM));
+  static int max_pairs = 0;
+  if (max_pairs == 0) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(unsigned(n_sms & ~1));
+    cfg.blockDim = dim3(B_THREADS);
+    cfg.dynamicSmemBytes = B_SMEM;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, chain_dgrad_kernel, &cfg) != cudaSuccess || n <= 0) { cudaGetLastError(); n = n_sms / 2; }
+    max_pairs = n;
+  }
+  const int n_pairs = (args.n_tiles + 1) / 2;
+  int grid_pairs = max_pairs < n_pairs ? max_pairs : n_pairs;
+  if (grid_pairs < 1) grid_pairs = 1;
+  chain_dgrad_kernel<<<2 * grid_pairs, B_THREADS, B_SMEM, stream>>>(tmW, tmDys, args);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace dsdf

@@ -1,11 +1,13 @@
 // C-ABI wrappers of the fused training step: buffer sizing, dgrad chain, wgrad, finish (reductions + weight-norm
 // backward + latent gradient + loss) and Adam.
+#include <stdlib.h>
 #include "train_kernels.cuh"
 #include "host_util.h"
 
 namespace dsdf {
 
 int launch_fused_dgrad(const CUtensorMap& tmW, const CUtensorMap& tmDys, const BwdArgs& args, int grid, cudaStream_t stream);
+int launch_chain_dgrad(const CUtensorMap& tmW, const CUtensorMap& tmDys, const BwdArgs& args, int n_sms, cudaStream_t stream);
 int launch_wgrad(const CUtensorMap& tmDys, const CUtensorMap& tmActs, const WgradArgs& args, int grid, cudaStream_t stream);
 int launch_wgrad_last(const void* x_last, const float* dy, int64_t n_rows_pad, float* part, int n_blocks, cudaStream_t stream);
 
@@ -121,8 +123,10 @@ extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, con
   a.part_stride = n_slots(lo) * FH;
   a.store_dys = 1;
   CUtensorMap tmW, tmDys;
-  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wpt, FH, lo.bwd_rows, FH * 2, 64, HALF_N)) return e;
+  static const bool use_v1 = getenv("DSDF_CHAIN_V1") != nullptr;   // debugging aid: the single-CTA first-generation kernel
+  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wpt, FH, lo.bwd_rows, FH * 2, 64, use_v1 ? HALF_N : 128)) return e;
   if (int e = make_tmap_bf16_2d(&tmDys, bufs->dys, FH, uint64_t(lo.num_hidden) * n_rows, FH * 2, 64, TILE_M)) return e;
+  if (!use_v1) return launch_chain_dgrad(tmW, tmDys, a, sm_count(), static_cast<cudaStream_t>(stream));
   int grid = sm_count();
   if (grid > a.n_tiles) grid = a.n_tiles;
   return launch_fused_dgrad(tmW, tmDys, a, grid, static_cast<cudaStream_t>(stream));
