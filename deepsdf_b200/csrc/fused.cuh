@@ -81,21 +81,31 @@ struct BwdArgs {
   int32_t store_dys;
 };
 
-constexpr int WG_MAX_SLABS = 64;
-struct WgradSlab {
-  int32_t dy_layer;     // region of the dY stash (hidden layer index l)
-  int32_t x_layer;      // region of the activation stash (= l-1: the input of lin{l})
-  int32_t m0;           // first output feature of the 128-row slab
+// wgrad work plan.  The row axis of every layer is cut into contiguous segments, one per CLUSTER of four CTAs (the four
+// 128-feature output blocks of the layer share every activation box through TMA multicast).  The plan depends only on
+// the network and the row count - never on the device - so the split-K summation order, and with it every gradient
+// bit, is reproducible.
+constexpr int WG_CLUSTERS = 32;      // 32 clusters x 4 CTAs = 128 SMs: a 4-CTA cluster must sit inside one GPC, and the
+                                     // B200's GPCs (18-20 SMs) leave SMs over; wgrad is HBM-bound, 128 SMs saturate it
+constexpr int WG_MAX_SEGS = 64;
+struct WgradSeg {
+  int32_t layer;        // hidden layer l: dW_l = dY_l^T . X_{l-1}
   int32_t n;            // input features covered (256 or 512)
-  int32_t splits;       // row-range splits (CTAs) of this slab
-  int32_t first_cta;
-  int64_t part_offset;  // float offset of this slab's partials [splits][128][n]
+  int32_t step_beg;     // 32-row steps [step_beg, step_end)
+  int32_t step_end;
+  int64_t part_offset;  // float offset of this segment's partial [4 x 128 output features][n]
+};
+struct WgradPlan {
+  int32_t n_segs;
+  int32_t cluster_seg0[WG_CLUSTERS + 1];       // segments of cluster c: [cluster_seg0[c], cluster_seg0[c+1])
+  int32_t layer_seg0[DSDF_MAX_LAYERS + 1];     // segments of layer l:   [layer_seg0[l], layer_seg0[l+1])
+  WgradSeg seg[WG_MAX_SEGS];
+  int64_t total_floats;
 };
 struct WgradArgs {
-  int32_t n_slabs;
+  WgradPlan plan;
   int64_t n_rows_pad;
   float* partials;
-  WgradSlab slab[WG_MAX_SLABS];
 };
 
 }  // namespace dsdf

@@ -8,49 +8,54 @@ namespace dsdf {
 
 int launch_fused_dgrad(const CUtensorMap& tmW, const CUtensorMap& tmDys, const BwdArgs& args, int grid, cudaStream_t stream);
 int launch_chain_dgrad(const CUtensorMap& tmW, const CUtensorMap& tmDys, const BwdArgs& args, int n_sms, cudaStream_t stream);
-int launch_wgrad(const CUtensorMap& tmDys, const CUtensorMap& tmActs, const WgradArgs& args, int grid, cudaStream_t stream);
+int launch_wgrad(const CUtensorMap& tmDys, const CUtensorMap& tmActs, const WgradArgs& args, cudaStream_t stream);
+int wgrad_max_active_clusters();
 int launch_wgrad_last(const void* x_last, const float* dy, int64_t n_rows_pad, float* part, int n_blocks, cudaStream_t stream);
 
 namespace {
 
-constexpr int kPlanCtas = 148;        // the split plan is fixed (not device dependent) so results are reproducible
 constexpr int kLastBlocks = 1184;   // fixed (not device dependent): 8 x 148
 
-struct WgradPlan {
-  int n_slabs;
-  int n_ctas;
-  WgradSlab slab[WG_MAX_SLABS];
-  int32_t slab_of[DSDF_MAX_LAYERS][4];
-  size_t total_floats;
-};
-
-int build_plan(const dsdf_net_desc* d, const FusedLayout& lo, WgradPlan* p) {
+// Cut the (layer, 32-row step) space into WG_CLUSTERS contiguous pieces of equal tensor-core cost (a 512-wide layer costs
+// two units per step, a 256-wide one a single unit).  A cluster gets one piece = at most a few segments.
+int build_plan(const dsdf_net_desc* d, const FusedLayout& lo, int64_t n_rows, WgradPlan* p) {
   memset(p, 0, sizeof(*p));
-  for (int l = 0; l < DSDF_MAX_LAYERS; ++l) for (int m = 0; m < 4; ++m) p->slab_of[l][m] = -1;
-  // cost units: a 512-wide slab = 2, a 256-wide slab = 1
-  int units = 0, n = 0;
-  for (int l = 1; l < lo.num_hidden; ++l) {
-    const int mblocks = (d->out_dim[l] + 127) / 128;
-    for (int mb = 0; mb < mblocks; ++mb) {
-      if (n >= WG_MAX_SLABS) return set_error("too many wgrad slabs");
-      WgradSlab& s = p->slab[n];
-      s.dy_layer = l; s.x_layer = l - 1; s.m0 = mb * 128; s.n = lo.bwd_halves[l] * HALF_N;
-      units += s.n / 256;
-      p->slab_of[l][mb] = n++;
+  (void)d;
+  const int64_t n_steps = n_rows / 32;
+  int64_t total = 0;
+  for (int l = 1; l < lo.num_hidden; ++l) total += n_steps * lo.bwd_halves[l];
+  const int64_t share = (total + WG_CLUSTERS - 1) / WG_CLUSTERS;
+  int l = 1, nseg = 0;
+  int64_t step = 0, off = 0;
+  for (int l2 = 0; l2 <= DSDF_MAX_LAYERS; ++l2) p->layer_seg0[l2] = -1;
+  for (int c = 0; c < WG_CLUSTERS; ++c) {
+    p->cluster_seg0[c] = nseg;
+    int64_t remaining = share;
+    while (remaining > 0 && l < lo.num_hidden) {
+      const int u = lo.bwd_halves[l];
+      int64_t take = (remaining + u - 1) / u;
+      if (take > n_steps - step) take = n_steps - step;
+      if (take > 0) {
+        if (nseg >= WG_MAX_SEGS) return set_error("too many wgrad segments");
+        WgradSeg& s = p->seg[nseg];
+        s.layer = l; s.n = u * HALF_N; s.step_beg = int32_t(step); s.step_end = int32_t(step + take);
+        s.part_offset = off;
+        off += int64_t(4) * 128 * s.n;
+        if (p->layer_seg0[l] < 0) p->layer_seg0[l] = nseg;
+        ++nseg;
+        step += take;
+        remaining -= take * u;
+      }
+      if (step >= n_steps) { ++l; step = 0; }
     }
   }
-  p->n_slabs = n;
-  int per_unit = units > 0 ? kPlanCtas / units : 1;
-  if (per_unit < 1) per_unit = 1;
-  int cta = 0; size_t off = 0;
-  for (int i = 0; i < n; ++i) {
-    WgradSlab& s = p->slab[i];
-    s.splits = per_unit * (s.n / 256);
-    s.first_cta = cta; cta += s.splits;
-    s.part_offset = int64_t(off);
-    off += size_t(s.splits) * 128 * s.n;
+  p->cluster_seg0[WG_CLUSTERS] = nseg;
+  p->n_segs = nseg;
+  // close the per-layer ranges: layer_seg0[l+1] = first segment of the next layer that has one (or n_segs)
+  int next = nseg;
+  for (int l2 = DSDF_MAX_LAYERS; l2 >= 0; --l2) {
+    if (p->layer_seg0[l2] < 0) p->layer_seg0[l2] = next; else next = p->layer_seg0[l2];
   }
-  p->n_ctas = cta;
   p->total_floats = off;
   return 0;
 }
@@ -66,9 +71,9 @@ using namespace dsdf;
 extern "C" int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, int32_t n_scenes, size_t* sizes) {
   FusedLayout lo;
   if (int e = fused_layout(desc, &lo)) return e;
-  WgradPlan plan;
-  if (int e = build_plan(desc, lo, &plan)) return e;
   const int64_t n_tiles = (n_rows + TILE_M - 1) / TILE_M, n_pad = n_tiles * TILE_M;
+  WgradPlan plan;
+  if (int e = build_plan(desc, lo, n_pad, &plan)) return e;
   const size_t nh = lo.num_hidden;
   sizes[0] = nh * n_pad * FH * 2;
   sizes[1] = nh * n_pad * FH * 2;
@@ -137,20 +142,17 @@ extern "C" int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs
   FusedLayout lo;
   if (int e = fused_layout(desc, &lo)) return e;
   DSDF_REQUIRE(n_rows > 0 && n_rows % TILE_M == 0, "fused training needs n_rows to be a positive multiple of 128");
-  WgradPlan plan;
-  if (int e = build_plan(desc, lo, &plan)) return e;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   WgradArgs a;
   memset(&a, 0, sizeof(a));
-  a.n_slabs = plan.n_slabs;
+  if (int e = build_plan(desc, lo, n_rows, &a.plan)) return e;
   a.n_rows_pad = n_rows;
   a.partials = bufs->wg_part;
-  memcpy(a.slab, plan.slab, sizeof(plan.slab));
   CUtensorMap tmDys, tmActs;
   const uint64_t rows = uint64_t(lo.num_hidden) * n_rows;
   if (int e = make_tmap_bf16_2d(&tmDys, bufs->dys, FH, rows, FH * 2, 64, 32)) return e;
   if (int e = make_tmap_bf16_2d(&tmActs, bufs->acts, FH, rows, FH * 2, 64, 32)) return e;
-  if (int e = launch_wgrad(tmDys, tmActs, a, plan.n_ctas, st)) return e;
+  if (int e = launch_wgrad(tmDys, tmActs, a, st)) return e;
   const uint8_t* x_last = static_cast<const uint8_t*>(bufs->acts) + size_t(lo.num_hidden - 1) * n_rows * FH * 2;
   return launch_wgrad_last(x_last, bufs->dy, n_rows, bufs->last_part, kLastBlocks, st);
 }
@@ -164,8 +166,7 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
   FinishArgs a;
   memset(&a, 0, sizeof(a));
   if (int e = fused_layout(desc, &a.lo)) return e;
-  WgradPlan plan;
-  if (int e = build_plan(desc, a.lo, &plan)) return e;
+  if (int e = build_plan(desc, a.lo, n_rows, &a.plan)) return e;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   a.desc = *desc;
   a.params = *params;
@@ -179,8 +180,6 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
   a.scene_sums = bufs->scene_sums;
   a.scene_reg = bufs->scene_sums + size_t(n_scenes) * a.n_slots * FH;
   a.wg_part = bufs->wg_part;
-  memcpy(a.slab_of, plan.slab_of, sizeof(plan.slab_of));
-  memcpy(a.slab, plan.slab, sizeof(plan.slab));
   a.last_part = bufs->last_part;
   a.n_last_blocks = kLastBlocks;
   a.lat_table = lat_table;
@@ -210,6 +209,8 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+extern "C" int dsdf_debug_wgrad_clusters(void) { return wgrad_max_active_clusters(); }
 
 extern "C" int dsdf_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
                          int32_t step, float grad_scale, const float* grad_scale_dev, void* stream) {

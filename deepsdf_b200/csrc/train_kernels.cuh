@@ -20,8 +20,7 @@ struct FinishArgs {
   float* scene_sums;            // [S][n_slots][512]
   float* scene_reg;             // [S] rows_s * ||z_s|| (written by latent_grad_kernel)
   const float* wg_part;         // wgrad partials
-  int32_t slab_of[DSDF_MAX_LAYERS][4];     // slab index of (layer, m-block) or -1
-  WgradSlab slab[WG_MAX_SLABS];
+  WgradPlan plan;               // wgrad segments: partial [4 x 128 outputs][n] per segment
   const float* last_part;       // [n_last_blocks][513]
   int32_t n_last_blocks;
   const float* lat_table;       // [S_total][L]
@@ -76,9 +75,8 @@ __global__ void __launch_bounds__(128) assemble_grads_kernel(const __grid_consta
     if (l == nh) {
       for (int b = 0; b < a.n_last_blocks; ++b) g += a.last_part[size_t(b) * (FH + 1) + k];
     } else if (k < a.lo.xw[l]) {
-      const WgradSlab& sl = a.slab[a.slab_of[l][o >> 7]];
-      const float* p = a.wg_part + sl.part_offset + size_t(o & 127) * sl.n + k;
-      for (int sp = 0; sp < sl.splits; ++sp) g += p[size_t(sp) * 128 * sl.n];
+      for (int sg = a.plan.layer_seg0[l]; sg < a.plan.layer_seg0[l + 1]; ++sg)
+        g += a.wg_part[a.plan.seg[sg].part_offset + size_t(o) * a.plan.seg[sg].n + k];
     } else if (a.lo.lat_col0[l] >= 0 && k < a.lo.lat_col0[l] + L) {
       const int kk = k - a.lo.lat_col0[l];
       for (int s = 0; s < S; ++s)

@@ -1,12 +1,15 @@
-// Weight-gradient contraction over the point axis (sm_100a, tcgen05 + TMEM + TMA):
-//   dW_l[o, i] = sum_rows dY_l[row, o] * X_l[row, i]        X_l = stashed bf16 activations, dY_l = stashed bf16 dY
+// Weight-gradient contraction over the point axis (sm_100a, tcgen05 + TMEM + TMA multicast, 4-CTA clusters):
+//   dW_l[o, i] = sum_rows dY_l[row, o] * X_{l-1}[row, i]     X = stashed bf16 activations, dY = stashed bf16 dY
 // Both operands are row-major [rows][512] in HBM, i.e. MN-major for this GEMM (the contraction index is the row), so the
 // same SW128 TMA boxes {64 features x 32 rows} serve as UMMA operands through MN-major descriptors
 // (LBO = 4096 between 64-feature groups, SBO = 1024 between 8-row groups).
-// Work unit = slab (layer, 128 output features) x split of the row range; one CTA per unit keeps the slab's
-// [128 x N<=512] fp32 accumulator in TMEM for its whole row range and writes one partial, which dsdf_fused_finish
-// reduces in a fixed order (deterministic split-K).
-// Replaces the weight-gradient part of chunk_loss.backward() (train_deep_sdf.py:533).
+// A cluster of four CTAs owns a row segment of one layer; CTA r computes output features [128 r, 128 r + 128) into a
+// [128 x n<=512] fp32 TMEM accumulator.  Every CTA needs the whole X box row (n features) but only its own 128 dY
+// features: each CTA TMA-loads a quarter of the X boxes and MULTICASTS it to all four, so X is read from L2 once per
+// cluster instead of once per CTA (the first version re-read it per CTA and was L2 -> SM bound at 7.7 TB/s).
+// A stage may be refilled only when all four CTAs have consumed it: every CTA's MMA commit arrives (multicast) on the
+// empty barrier of all four.  One partial per (segment, CTA), reduced by dsdf_fused_finish in plan order
+// (deterministic split-K).  Replaces the weight-gradient part of chunk_loss.backward() (train_deep_sdf.py:533).
 #include "common.cuh"
 #include "fused.cuh"
 #include "host_util.h"
@@ -22,94 +25,100 @@ constexpr int WG_THREADS = 192;                   // warp 0 TMA, warp 1 MMA + TM
 constexpr int WG_SMEM = WG_STAGES * WG_STAGE_BYTES + 1024;
 }  // namespace
 
-__global__ void __launch_bounds__(WG_THREADS, 1)
+__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(WG_THREADS, 1)
 wgrad_kernel(const __grid_constant__ CUtensorMap tmDys, const __grid_constant__ CUtensorMap tmActs,
              const __grid_constant__ WgradArgs args) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  __shared__ uint64_t bar_full[WG_STAGES], bar_empty[WG_STAGES], bar_done;
+  __shared__ uint64_t bar_full[WG_STAGES], bar_empty[WG_STAGES], bar_done, bar_epi_free;
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-  // ---- which unit is mine
-  int slab = -1, split = 0;
-  for (int s = 0; s < args.n_slabs; ++s) {
-    const int first = args.slab[s].first_cta;
-    if (int(blockIdx.x) >= first && int(blockIdx.x) < first + args.slab[s].splits) { slab = s; split = blockIdx.x - first; }
-  }
-  if (slab < 0) return;
-  const WgradSlab S = args.slab[slab];
-  const int64_t total_steps = args.n_rows_pad / WG_ROWS;
-  const int64_t step_beg = total_steps * split / S.splits;
-  const int64_t step_end = total_steps * (split + 1) / S.splits;
-  const int n_boxes_b = S.n / 64;
-  const uint32_t stage_tx = uint32_t(2 + n_boxes_b) * WG_BOX_BYTES;
+  const uint32_t rank = cluster_ctarank();          // = 128-feature output block of the layer
+  const int cluster = blockIdx.x >> 2;
+  const int seg0 = args.plan.cluster_seg0[cluster], seg1 = args.plan.cluster_seg0[cluster + 1];
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < WG_STAGES; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    for (int s = 0; s < WG_STAGES; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 4); }
     mbar_init(&bar_done, 1);
+    mbar_init(&bar_epi_free, 4);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_slot);
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmDys); tma_prefetch_desc(&tmActs); }
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      const int64_t dy_row0 = int64_t(S.dy_layer) * args.n_rows_pad;
-      const int64_t x_row0 = int64_t(S.x_layer) * args.n_rows_pad;
-      for (int64_t st = step_beg; st < step_end; ++st) {
-        mbar_wait(&bar_empty[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&bar_full[stage], stage_tx);
-        uint8_t* base = smem + stage * WG_STAGE_BYTES;
-        const int32_t r = int32_t(st * WG_ROWS);
-        tma_load_2d(base, &tmDys, &bar_full[stage], S.m0, int32_t(dy_row0) + r);
-        tma_load_2d(base + WG_BOX_BYTES, &tmDys, &bar_full[stage], S.m0 + 64, int32_t(dy_row0) + r);
-        for (int b = 0; b < n_boxes_b; ++b)
-          tma_load_2d(base + (2 + b) * WG_BOX_BYTES, &tmActs, &bar_full[stage], b * 64, int32_t(x_row0) + r);
+    // ================================================================ TMA producer (whole warp walks, one lane issues)
+    const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]), s_u = smem_u32(smem);
+    uint32_t stage = 0, phase = 0;
+    for (int sg = seg0; sg < seg1; ++sg) {
+      const int layer = args.plan.seg[sg].layer, n = args.plan.seg[sg].n;
+      const int st_beg = args.plan.seg[sg].step_beg, st_end = args.plan.seg[sg].step_end;
+      const int n_boxes_b = n >> 6, share = n_boxes_b >> 2;       // X boxes per stage; boxes this CTA fetches for everybody
+      const uint32_t stage_tx = uint32_t(2 + n_boxes_b) * WG_BOX_BYTES;
+      const int32_t dy_row0 = int32_t(int64_t(layer) * args.n_rows_pad);
+      const int32_t x_row0 = int32_t(int64_t(layer - 1) * args.n_rows_pad);
+      for (int st = st_beg; st < st_end; ++st) {
+        mbar_wait_a(empty0 + stage * 8, phase ^ 1);
+        if (elect_one()) {
+          const uint32_t base = s_u + stage * WG_STAGE_BYTES, bar = full0 + stage * 8;
+          const int32_t r = st * WG_ROWS;
+          mbar_arrive_expect_tx_a(bar, stage_tx);
+          tma_load_2d_a(base, &tmDys, bar, int32_t(rank) * 128, dy_row0 + r);
+          tma_load_2d_a(base + WG_BOX_BYTES, &tmDys, bar, int32_t(rank) * 128 + 64, dy_row0 + r);
+          for (int b = int(rank) * share; b < int(rank + 1) * share; ++b)
+            tma_load_2d_mcast_a(base + (2 + b) * WG_BOX_BYTES, &tmActs, bar, b * 64, x_row0 + r, 0xF);
+        }
+        __syncwarp();
         if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
+    // ================================================================ MMA issuer (warp-uniform loop, elected issue)
     const uint32_t idesc = umma_idesc_bf16(128, 256, 1, 1);            // both operands MN-major
     const uint64_t desc_hi = umma_desc_hi_sw128(WG_BOX_BYTES, 1024);   // LBO = next 64-feature group, SBO = next 8 rows
-    const uint32_t s_u = smem_u32(smem);
-    int stage = 0; uint32_t phase = 0;
-    const int n_halves = S.n / 256;
-    for (int64_t st = step_beg; st < step_end; ++st) {
-      mbar_wait(&bar_full[stage], phase);
-      tc_fence_after();
-      if (lane == 0) {
-        const uint32_t a0 = s_u + stage * WG_STAGE_BYTES;
-        const uint32_t b0 = a0 + 2 * WG_BOX_BYTES;
+    const uint64_t d_base = desc_hi | uint64_t((smem_u32(smem) >> 4) & 0x3FFF);
+    const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]);
+    const uint32_t done_a = smem_u32(&bar_done), free_a = smem_u32(&bar_epi_free);
+    uint32_t stage = 0, phase = 0;
+    for (int sg = seg0; sg < seg1; ++sg) {
+      const int n_halves = args.plan.seg[sg].n >> 8;
+      const int st_beg = args.plan.seg[sg].step_beg, st_end = args.plan.seg[sg].step_end;
+      if (sg > seg0) { mbar_wait_a(free_a, uint32_t(sg - seg0 - 1) & 1u); tc_fence_after(); }   // accumulator drained
+      for (int st = st_beg; st < st_end; ++st) {
+        mbar_wait_a(full0 + stage * 8, phase);
+        tc_fence_after();
+        const uint64_t a0 = d_base + uint64_t(stage * (WG_STAGE_BYTES >> 4));
+        const uint64_t b0 = a0 + uint64_t((2 * WG_BOX_BYTES) >> 4);
+        if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < WG_ROWS / 16; ++ks) {
-          const uint64_t ad = umma_desc(a0 + ks * 2048, desc_hi);
-          for (int h = 0; h < n_halves; ++h) {
-            const uint64_t bd = umma_desc(b0 + h * 4 * WG_BOX_BYTES + ks * 2048, desc_hi);
-            umma_bf16_ss(tmem_base + h * 256, ad, bd, idesc, (st > step_beg || ks > 0) ? 1u : 0u);
+          for (int ks = 0; ks < WG_ROWS / 16; ++ks) {
+            const uint32_t acc = (st > st_beg || ks > 0) ? 1u : 0u;
+            umma_bf16_ss(tmem_base, a0 + ks * 128, b0 + ks * 128, idesc, acc);
+            if (n_halves == 2) umma_bf16_ss(tmem_base + 256, a0 + ks * 128, b0 + uint64_t((4 * WG_BOX_BYTES) >> 4) + ks * 128, idesc, acc);
           }
+          umma_commit_mcast_a(empty0 + stage * 8, 0xF);
+          if (st == st_end - 1) umma_commit_a(done_a);
         }
-        umma_commit(&bar_empty[stage]);
+        __syncwarp();
+        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
-      if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
     }
-    if (lane == 0) umma_commit(&bar_done);
-    __syncwarp();
   } else {
-    // epilogue: TMEM -> fp32 partial [128][n]
+    // ================================================================ epilogue: TMEM -> fp32 partial [128][n]
     const int q = warp & 3;
     const int row = q * 32 + lane;
-    float* out = args.partials + S.part_offset + size_t(split) * 128 * S.n + size_t(row) * S.n;
-    if (step_end > step_beg) {
-      mbar_wait(&bar_done, 0);
+    const uint32_t free_a = smem_u32(&bar_epi_free);
+    for (int sg = seg0; sg < seg1; ++sg) {
+      const int n = args.plan.seg[sg].n;
+      float* out = args.partials + args.plan.seg[sg].part_offset + (size_t(rank) * 128 + row) * n;
+      mbar_wait(&bar_done, uint32_t(sg - seg0) & 1u);
       tc_fence_after();
-      for (int c0 = 0; c0 < S.n; c0 += 32) {
+      for (int c0 = 0; c0 < n; c0 += 32) {
         uint32_t v[32];
         tmem_ld32(tmem_base + (uint32_t(q * 32) << 16) + c0, v);
         tmem_ld_wait();
@@ -118,12 +127,14 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDys, const __grid_constant__ 
           reinterpret_cast<float4*>(out + c0)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
                                                                  __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
       }
-    } else {
-      for (int c0 = 0; c0 < S.n; c0 += 4) *reinterpret_cast<float4*>(out + c0) = make_float4(0.f, 0.f, 0.f, 0.f);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(free_a);
     }
-    tc_fence_before();
   }
+  tc_fence_before();
   __syncthreads();
+  cluster_sync_all();
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
@@ -150,11 +161,27 @@ __global__ void __launch_bounds__(256) wgrad_last_kernel(const __nv_bfloat16* __
   if (threadIdx.x == 0) o[FH] = sd;
 }
 
-int launch_wgrad(const CUtensorMap& tmDys, const CUtensorMap& tmActs, const WgradArgs& args, int grid, cudaStream_t stream) {
+int launch_wgrad(const CUtensorMap& tmDys, const CUtensorMap& tmActs, const WgradArgs& args, cudaStream_t stream) {
   DSDF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
-  wgrad_kernel<<<grid, WG_THREADS, WG_SMEM, stream>>>(tmDys, tmActs, args);
+  wgrad_kernel<<<4 * WG_CLUSTERS, WG_THREADS, WG_SMEM, stream>>>(tmDys, tmActs, args);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+int wgrad_max_active_clusters() {
+  cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(4 * WG_CLUSTERS);
+  cfg.blockDim = dim3(WG_THREADS);
+  cfg.dynamicSmemBytes = WG_SMEM;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 4; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, wgrad_kernel, &cfg) != cudaSuccess) { cudaGetLastError(); n = -1; }
+  return n;
 }
 
 int launch_wgrad_last(const void* x_last, const float* dy, int64_t n_rows_pad, float* part, int n_blocks, cudaStream_t stream) {

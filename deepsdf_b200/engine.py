@@ -127,7 +127,9 @@ class FusedEngine:
         names = ["acts", "dys", "bitmask", "dy", "tile_loss", "tile_part", "wg_part", "last_part", "scene_sums", "cbias"]
         self._bufs = {}
         for n, s in zip(names, sizes):
-            self._bufs[n] = torch.empty(max(int(s), 16), dtype=torch.uint8, device=self.device)
+            # zero-filled once: wgrad pads layers narrower than 512 outputs to four 128-feature blocks and reads the
+            # never-written columns of their dY stash
+            self._bufs[n] = torch.zeros(max(int(s), 16), dtype=torch.uint8, device=self.device)
         self._bufs["sdf"] = torch.empty(n_rows, device=self.device)
         self._bufs["loss"] = torch.zeros(2, device=self.device)
         tb = TrainBufs()

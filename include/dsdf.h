@@ -178,6 +178,8 @@ int dsdf_clip_coef(const float* g, int64_t n, float max_norm, float* scratch, fl
 int dsdf_selftest_umma(int mode, const void* A, const void* B, float* C, void* A_store_out, int K, int N,
                        unsigned a_lbo, unsigned a_sbo, unsigned b_lbo, unsigned b_sbo, void* stream);
 
+/* diagnostics: how many 4-CTA wgrad clusters can be co-resident on the current device (-1: query failed) */
+int dsdf_debug_wgrad_clusters(void);
 /* CTA-pair (cta_group::2) bring-up: C[256,256] = A[256,K] * B[256,K]^T on one 2-CTA cluster; mode bit2 = A written by
  * threads and handed over with a remote mbarrier arrive (see csrc/selftest.cu). */
 int dsdf_selftest_umma_pair(int mode, const void* A, const void* B, float* C, int K, void* stream);
