@@ -265,28 +265,37 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           stores_pending = true;
         }
         {
-          // warp w owns columns [32w, 32w+32): lane = (row parity, bf16x2 word); rows 2i + parity, i = 0..63
+          // warp w owns columns [32w, 32w+32): lane = (row set, bf16x2 word).  Lanes 0-15 walk the rows with bit 2
+          // clear, lanes 16-31 the same rows ^ 4: the SW128 XOR then puts the two half-warps on disjoint bank groups.
           const int cw = warp * 32;
           const bool cols_valid = cw < n_halves * 256;
           const bool want_xyz = args.xyzsum_slot[t] >= 0;
           const int word = lane & 15, rpar = lane >> 4;
           float s0 = 0.f, s1 = 0.f, sx0 = 0.f, sx1 = 0.f, sy0 = 0.f, sy1 = 0.f, sz0 = 0.f, sz1 = 0.f;
           if (cols_valid) {
-            const uint8_t* cb = sA + (cw >> 6) * A_CHUNK_BYTES;
+            const uint32_t cb = smem_u32(sA) + uint32_t(cw >> 6) * A_CHUNK_BYTES;
+            const uint32_t xb = smem_u32(s_xyz);
             const uint32_t colw = uint32_t(cw & 63) / 2 + word;            // bf16x2 word index within the 64-column chunk row
+            if (!want_xyz) {
+#pragma unroll 8
+              for (int i = 0; i < TILE_M / 2; ++i) {
+                const uint32_t r = (uint32_t(i & 3) | (uint32_t(i >> 2) << 3)) ^ (uint32_t(rpar) << 2);
+                const uint32_t w = lds_u32(cb + r * 128u + ((((colw >> 2) ^ (r & 7u)) << 4) | ((colw & 3u) << 2)));
+                s0 += bf16_lo_to_f32(w); s1 += bf16_hi_to_f32(w);
+              }
+            } else {
 #pragma unroll 4
-            for (int i = 0; i < TILE_M / 2; ++i) {
-              const int r = 2 * i + rpar;
-              const uint32_t w = *reinterpret_cast<const uint32_t*>(cb + r * 128 + ((((colw >> 2) ^ (r & 7)) << 4) | ((colw & 3) << 2)));
-              const float lo = bf16_lo_to_f32(w), hi = bf16_hi_to_f32(w);
-              s0 += lo; s1 += hi;
-              if (want_xyz) {
-                const float x = s_xyz[r], y = s_xyz[TILE_M + r], z = s_xyz[2 * TILE_M + r];
+              for (int i = 0; i < TILE_M / 2; ++i) {
+                const uint32_t r = (uint32_t(i & 3) | (uint32_t(i >> 2) << 3)) ^ (uint32_t(rpar) << 2);
+                const uint32_t w = lds_u32(cb + r * 128u + ((((colw >> 2) ^ (r & 7u)) << 4) | ((colw & 3u) << 2)));
+                const float lo = bf16_lo_to_f32(w), hi = bf16_hi_to_f32(w);
+                const float x = lds_f32(xb + r * 4u), y = lds_f32(xb + (TILE_M + r) * 4u), z = lds_f32(xb + (2 * TILE_M + r) * 4u);
+                s0 += lo; s1 += hi;
                 sx0 += x * lo; sx1 += x * hi; sy0 += y * lo; sy1 += y * hi; sz0 += z * lo; sz1 += z * hi;
               }
             }
           }
-          // combine the two row parities (fixed order: even rows + odd rows)
+          // combine the two row sets (fixed order)
           s0 += __shfl_down_sync(0xffffffffu, s0, 16); s1 += __shfl_down_sync(0xffffffffu, s1, 16);
           if (want_xyz) {
             sx0 += __shfl_down_sync(0xffffffffu, sx0, 16); sx1 += __shfl_down_sync(0xffffffffu, sx1, 16);

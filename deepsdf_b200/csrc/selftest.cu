@@ -14,6 +14,8 @@ namespace dsdf {
 
 struct SelftestArgs {
   int K, N, mode;
+  int reps;                     // > 1: repeat the whole K loop (throughput measurement; C is then reps x the product)
+  long long* cycles;            // [1] clock64 ticks from the first MMA issue to the completion of the last, or null
   uint32_t a_lbo, a_sbo, b_lbo, b_sbo;
   const __nv_bfloat16* a_raw;   // for manual writes: K-major [128][K]
   float* C;                     // [128][N]
@@ -80,13 +82,17 @@ umma_selftest_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       const uint32_t idesc = umma_idesc_bf16(128, N, a_mn ? 1 : 0, b_mn ? 1 : 0);
       const uint64_t a_hi = umma_desc_hi_sw128(args.a_lbo, args.a_sbo);
       const uint64_t b_hi = umma_desc_hi_sw128(args.b_lbo, args.b_sbo);
-      for (int ks = 0; ks < K / 16; ++ks) {
-        uint32_t a_off = a_mn ? ks * 2048u : (ks >> 2) * 16384u + (ks & 3) * 32u;
-        uint32_t b_off = b_mn ? ks * 2048u : (ks >> 2) * (uint32_t(N) * 128u) + (ks & 3) * 32u;
-        umma_bf16_ss(tmem_base, umma_desc(smem_u32(sA) + a_off, a_hi), umma_desc(smem_u32(sB) + b_off, b_hi), idesc,
-                     ks > 0 ? 1u : 0u);
-      }
+      const long long t0 = clock64();
+      for (int rep = 0; rep < args.reps; ++rep)
+        for (int ks = 0; ks < K / 16; ++ks) {
+          uint32_t a_off = a_mn ? ks * 2048u : (ks >> 2) * 16384u + (ks & 3) * 32u;
+          uint32_t b_off = b_mn ? ks * 2048u : (ks >> 2) * (uint32_t(N) * 128u) + (ks & 3) * 32u;
+          umma_bf16_ss(tmem_base, umma_desc(smem_u32(sA) + a_off, a_hi), umma_desc(smem_u32(sB) + b_off, b_hi), idesc,
+                       (ks > 0 || rep > 0) ? 1u : 0u);
+        }
       umma_commit(&bar_done);
+      mbar_wait(&bar_done, 0);
+      if (args.cycles) args.cycles[0] = clock64() - t0;
     }
     __syncwarp();
   }
@@ -123,6 +129,7 @@ extern "C" int dsdf_selftest_umma(int mode, const void* A, const void* B, float*
   DSDF_REQUIRE(K % 64 == 0 && K >= 64 && K <= 256, "selftest: K must be 64..256, multiple of 64");
   DSDF_REQUIRE(N % 64 == 0 && N >= 64 && N <= 256, "selftest: N must be 64..256, multiple of 64");
   const bool a_mn = mode & 1, b_mn = mode & 2;
+  const bool timing = (mode >> 8) > 0;
   CUtensorMap tmA, tmB, tmS;
   int e;
   if (!a_mn) e = make_tmap_bf16_2d(&tmA, A, K, 128, uint64_t(K) * 2, 64, 128);
@@ -131,11 +138,13 @@ extern "C" int dsdf_selftest_umma(int mode, const void* A, const void* B, float*
   if (!b_mn) e = make_tmap_bf16_2d(&tmB, B, K, N, uint64_t(K) * 2, 64, N);
   else       e = make_tmap_bf16_2d(&tmB, B, N, K, uint64_t(N) * 2, 64, K);
   if (e) return e;
-  const void* store_ptr = A_store_out ? A_store_out : A;
+  const void* store_ptr = (A_store_out && !timing) ? A_store_out : A;
   e = make_tmap_bf16_2d(&tmS, store_ptr, K, 128, uint64_t(K) * 2, 64, 128);
   if (e) return e;
-  if ((mode & 8) && !A_store_out) return set_error("selftest: store mode needs an output buffer");
-  SelftestArgs args{K, N, mode, a_lbo, a_sbo, b_lbo, b_sbo, reinterpret_cast<const __nv_bfloat16*>(A), C};
+  if (!timing && (mode & 8) && !A_store_out) return set_error("selftest: store mode needs an output buffer");
+  SelftestArgs args{K, N, mode & 15, (mode >> 8) > 0 ? (mode >> 8) : 1, reinterpret_cast<long long*>((mode >> 8) > 0 ? A_store_out : nullptr),
+                    a_lbo, a_sbo, b_lbo, b_sbo, reinterpret_cast<const __nv_bfloat16*>(A), C};
+  if ((mode >> 8) > 0) { mode &= 7; args.mode = mode; }   // throughput runs: A_store_out receives the cycle count instead
   const size_t smem = 65536 + 131072 + 1024;
   DSDF_CHECK_CUDA(cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
   umma_selftest_kernel<<<1, ST_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB, tmS, args);

@@ -116,7 +116,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap tmDys, const __grid_constant__ 
     for (int sg = seg0; sg < seg1; ++sg) {
       const int n = args.plan.seg[sg].n;
       float* out = args.partials + args.plan.seg[sg].part_offset + (size_t(rank) * 128 + row) * n;
-      mbar_wait(&bar_done, uint32_t(sg - seg0) & 1u);
+      mbar_wait_sleep(&bar_done, uint32_t(sg - seg0) & 1u, 2000);
       tc_fence_after();
       for (int c0 = 0; c0 < n; c0 += 32) {
         uint32_t v[32];
