@@ -28,7 +28,7 @@ namespace {
 
 constexpr int P_EPI_WARPS = 16;
 constexpr int P_EPI_THREADS = P_EPI_WARPS * 32;        // 512
-constexpr int P_THREADS = (P_EPI_WARPS + 2) * 32;      // + TMA warp + MMA warp
+constexpr int P_THREADS = (P_EPI_WARPS + 3) * 32;      // + TMA warp + MMA warp + stash warp
 constexpr int P_STAGES = 5;
 constexpr int P_STAGE_BYTES = 128 * 128;               // this CTA's half ([128 out rows][64 K] bf16) of a weight block
 constexpr int P_OFF_B = A_BYTES;
@@ -124,6 +124,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   float* s_wlast = reinterpret_cast<float*>(smem + P_OFF_WLAST);
   float* s_ypart = reinterpret_cast<float*>(smem + P_OFF_YPART);
   __shared__ uint64_t bar_full[P_STAGES], bar_empty[P_STAGES], bar_tmem_full[2], bar_free_q0, bar_free_lo, bar_a_ready[4];
+  __shared__ uint64_t bar_q_written[4], bar_q_stashed[4];   // activation stash hand-over (training), per 128-column quarter
   __shared__ uint32_t tmem_slot;
   __shared__ float s_loss[4];
 
@@ -138,6 +139,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     mbar_init(&bar_free_q0, 1);
     mbar_init(&bar_free_lo, 1);
     for (int i = 0; i < 4; ++i) mbar_init(&bar_a_ready[i], 2 * P_EPI_WARPS);
+    for (int i = 0; i < 4; ++i) { mbar_init(&bar_q_written[i], P_EPI_WARPS); mbar_init(&bar_q_stashed[i], 1); }
     fence_barrier_init();
   }
   if (warp == P_EPI_WARPS + 1) tmem_alloc_pair<512>(&tmem_slot);
@@ -246,6 +248,51 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         }
       }
     }
+  } else if (warp == P_EPI_WARPS + 2) {
+    // ================================================================ stash warp (training): as soon as all 16 epilogue
+    // warps have written a 128-column quarter of the activation tile, TMA-store its two 64-column chunks (bf16) for
+    // wgrad and tell the epilogue when the store has read the shared memory, so that the quarter may be overwritten by
+    // the next layer.  No CTA-wide barrier is involved: the epilogue warps never wait for each other because of the stash.
+    if (kTrain && args.store_acts) {
+      const uint32_t wr0 = smem_u32(&bar_q_written[0]), st0 = smem_u32(&bar_q_stashed[0]), sA_u = smem_u32(sA);
+      uint32_t cnt = 0;            // bit Q: parity of the number of quarter-Q hand-overs so far
+      int pending = -1;            // quarter whose store is still in flight (its q_stashed arrive is owed)
+      for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+        const int tile = 2 * tp + int(rank);
+        const bool tile_ok = tile < args.n_tiles;
+        for (int l = 0; l < nh; ++l) {
+          const int nq = args.prog[l].n_halves * 2;
+          const int32_t grow0 = int32_t(int64_t(l) * args.n_rows_pad + int64_t(tile) * TILE_M);
+          for (int Q = 0; Q < nq; ++Q) {
+            mbar_wait_a(wr0 + Q * 8, (cnt >> Q) & 1u);
+            if (elect_one()) {
+              if (tile_ok) {
+                asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                             ::"l"(&tmActs), "r"(sA_u + (2 * Q) * A_CHUNK_BYTES), "r"(Q * 128), "r"(grow0) : "memory");
+                asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                             ::"l"(&tmActs), "r"(sA_u + (2 * Q + 1) * A_CHUNK_BYTES), "r"(Q * 128 + 64), "r"(grow0) : "memory");
+                tma_store_commit();
+                // keep one store in flight: everything but the group just committed has been read out of shared memory
+                asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                if (pending >= 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(st0 + pending * 8) : "memory");
+              } else {
+                tma_store_wait_read0();
+                if (pending >= 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(st0 + pending * 8) : "memory");
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(st0 + Q * 8) : "memory");
+              }
+            }
+            pending = tile_ok ? Q : -1;
+            __syncwarp();
+            cnt ^= 1u << Q;
+          }
+        }
+      }
+      if (elect_one()) {
+        tma_store_wait_all0();
+        if (pending >= 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(st0 + pending * 8) : "memory");
+      }
+      __syncwarp();
+    }
   } else {
     // ================================================================ epilogue warps (both CTAs)
     const int q = warp & 3;            // TMEM lane quadrant
@@ -256,7 +303,8 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     const uint32_t ready_leader = mapa_u32(smem_u32(&bar_a_ready[0]), 0);   // + 8*quarter
     s_wlast[tid] = __ldg(args.w_last + tid);
     uint32_t mma_iter = 0;
-    bool stores_pending = false;
+    const bool stash = kTrain && args.store_acts != 0;
+    uint32_t wpar = 0, wany = 0;        // per quarter: parity of / any hand-overs to the stash warp so far
     const int tiles_alloc = int(args.n_rows_pad / TILE_M);
 
     for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
@@ -309,6 +357,8 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         // One 128-column quarter: two 16-column passes straight from TMEM into the A tile.
         auto quarter = [&](int Q, uint32_t keep) {
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
+          // the previous layer's stash of this quarter must have been read out of the tile
+          if (stash && ((wany >> Q) & 1u)) mbar_wait(&bar_q_stashed[Q], ((wpar >> Q) & 1u) ^ 1u);
           const uint32_t g0 = epi_pass16<kTrain>(tmem_row + c0, has_acc, ascale, sb + c0, swx ? swx + c0 : nullptr, px, py, pz, keep,
                                                  swl ? swl + c0 : nullptr, sA, rt, c0, ydot);
           const uint32_t g1 = epi_pass16<kTrain>(tmem_row + c0 + 16, has_acc, ascale, sb + c0 + 16, swx ? swx + c0 + 16 : nullptr, px, py,
@@ -318,17 +368,16 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           tc_fence_before();
           __syncwarp();
           if (produce_a && lane == 0) mbar_arrive_remote(ready_leader + 8u * uint32_t(Q));
+          if (stash) {
+            if (lane == 0) mbar_arrive(&bar_q_written[Q]);
+            wpar ^= 1u << Q; wany |= 1u << Q;
+          }
         };
 
         // ---- half 0: ready while the tensor cores still compute half 1.  Activation chunks 0,1 may be overwritten once
         //      half 1's MMAs have passed K chunk 1 (free_q0), chunks 2,3 after K chunk 3 (free_lo); the previous layer's
         //      stash (TMA store) must have been read out of the tile.
         if (has_acc) { mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); mbar_wait(&bar_free_q0, par); }
-        if (kTrain && stores_pending) {
-          if (tid == 0) tma_store_wait_read0();
-          epi_bar();
-          stores_pending = false;
-        }
         quarter(0, kwa);
         if (has_acc) mbar_wait(&bar_free_lo, par);
         quarter(1, kwb);
@@ -346,17 +395,6 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           tc_fence_before();
           __syncwarp();
           if (produce_a && lane == 0) { mbar_arrive_remote(ready_leader + 16u); mbar_arrive_remote(ready_leader + 24u); }
-        }
-        // ---- the activation stash for the backward
-        if (kTrain && args.store_acts) {
-          epi_bar();
-          if (tid == 0 && tile_ok) {
-            const int nchunks = L.n_halves * 4;
-            for (int c = 0; c < nchunks; ++c)
-              tma_store_2d(&tmActs, sA + c * A_CHUNK_BYTES, c * 64, int32_t(int64_t(l) * args.n_rows_pad + int64_t(tile) * TILE_M));
-            tma_store_commit();
-          }
-          stores_pending = true;
         }
       }
 
@@ -391,7 +429,6 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       if (kTrain && args.gt != nullptr && tid == 0 && tile_ok)
         args.tile_loss[tile] = ((s_loss[0] + s_loss[1]) + s_loss[2]) + s_loss[3];
     }
-    if (kTrain && stores_pending && tid == 0) tma_store_wait_all0();
   }
 
   tc_fence_before();

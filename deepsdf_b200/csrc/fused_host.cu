@@ -298,6 +298,7 @@ extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, c
   a.tile_loss = tr->tile_loss;
   a.bitmask = tr->bitmask;
   a.store_acts = (tr->acts != nullptr);
+  if (getenv("DSDF_EXP_NOSTASH")) a.store_acts = 0;        // timing experiment only (wgrad then reads stale data)
   if (a.training) {
     DSDF_REQUIRE(tr->n_rows_pad == a.n_rows_pad, "n_rows_pad must be n_rows rounded up to 128");
     if (a.gt) DSDF_REQUIRE(a.dy_out && a.tile_loss, "training with gt needs dy_out and tile_loss");

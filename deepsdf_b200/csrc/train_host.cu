@@ -126,7 +126,7 @@ extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, con
   a.xyz_stride = xyz_stride;
   a.tile_part = bufs->tile_part;
   a.part_stride = n_slots(lo) * FH;
-  a.store_dys = 1;
+  a.store_dys = getenv("DSDF_EXP_NOSTASH") ? 0 : 1;       // timing experiment only
   CUtensorMap tmW, tmDys;
   static const bool use_v1 = getenv("DSDF_CHAIN_V1") != nullptr;   // debugging aid: the single-CTA first-generation kernel
   if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wpt, FH, lo.bwd_rows, FH * 2, 64, use_v1 ? HALF_N : 128)) return e;
