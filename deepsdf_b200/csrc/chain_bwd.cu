@@ -22,7 +22,7 @@ namespace {
 
 constexpr int B_EPI_WARPS = 16;
 constexpr int B_EPI_THREADS = B_EPI_WARPS * 32;
-constexpr int B_THREADS = (B_EPI_WARPS + 2) * 32;
+constexpr int B_THREADS = (B_EPI_WARPS + 3) * 32;   // + TMA warp + MMA warp + stash warp
 constexpr int B_STAGES = 5;
 constexpr int B_STAGE_BYTES = 128 * 128;
 constexpr int B_OFF_B = A_BYTES;
@@ -72,6 +72,9 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   float* s_wlast = reinterpret_cast<float*>(smem + B_OFF_WLAST);
   float* s_xyz = reinterpret_cast<float*>(smem + B_OFF_XYZ);
   __shared__ uint64_t bar_full[B_STAGES], bar_empty[B_STAGES], bar_tmem_full[2], bar_free_q0, bar_free_lo, bar_a_ready[4];
+  // per 128-column quarter of the dY tile: written by all 16 epilogue warps -> read by the stash warp (TMA store) and by
+  // the four warps that own its column sums -> released for the next chain link
+  __shared__ uint64_t bar_q_written[4], bar_q_released[4];
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5;
@@ -85,6 +88,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     mbar_init(&bar_free_q0, 1);
     mbar_init(&bar_free_lo, 1);
     for (int i = 0; i < 4; ++i) mbar_init(&bar_a_ready[i], 2 * B_EPI_WARPS);
+    for (int i = 0; i < 4; ++i) { mbar_init(&bar_q_written[i], B_EPI_WARPS); mbar_init(&bar_q_released[i], 5); }
     fence_barrier_init();
   }
   if (warp == B_EPI_WARPS + 1) tmem_alloc_pair<512>(&tmem_slot);
@@ -180,6 +184,47 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         }
       }
     }
+  } else if (warp == B_EPI_WARPS + 2) {
+    // ================================================================ stash warp: TMA-store every completed quarter of
+    // dY_t (t > 0) for wgrad and release it once the store has read the shared memory (one store kept in flight)
+    const uint32_t wr0 = smem_u32(&bar_q_written[0]), rl0 = smem_u32(&bar_q_released[0]), sA_u = smem_u32(sA);
+    uint32_t cnt = 0;
+    int pending = -1;
+    for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+      const int tile = 2 * tp + int(rank);
+      const bool tile_ok = tile < args.n_tiles;
+      for (int t = nh - 1; t >= 0; --t) {
+        const int nq = (t < nh - 1 ? args.prog[t + 1].n_halves : 2) * 2;
+        const bool do_store = tile_ok && args.store_dys && t > 0;
+        const int32_t grow0 = int32_t(int64_t(t) * args.n_rows_pad + int64_t(tile) * TILE_M);
+        for (int Q = 0; Q < nq; ++Q) {
+          mbar_wait_a(wr0 + Q * 8, (cnt >> Q) & 1u);
+          if (elect_one()) {
+            if (do_store) {
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                           ::"l"(&tmDys), "r"(sA_u + (2 * Q) * A_CHUNK_BYTES), "r"(Q * 128), "r"(grow0) : "memory");
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                           ::"l"(&tmDys), "r"(sA_u + (2 * Q + 1) * A_CHUNK_BYTES), "r"(Q * 128 + 64), "r"(grow0) : "memory");
+              tma_store_commit();
+              asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+              if (pending >= 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(rl0 + pending * 8) : "memory");
+            } else {
+              tma_store_wait_read0();
+              if (pending >= 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(rl0 + pending * 8) : "memory");
+              asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(rl0 + Q * 8) : "memory");
+            }
+          }
+          pending = do_store ? Q : -1;
+          __syncwarp();
+          cnt ^= 1u << Q;
+        }
+      }
+    }
+    if (elect_one()) {
+      tma_store_wait_all0();
+      if (pending >= 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(rl0 + pending * 8) : "memory");
+    }
+    __syncwarp();
   } else {
     // ================================================================ epilogue warps (both CTAs)
     const int q = warp & 3;
@@ -190,7 +235,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const uint32_t ready_leader = mapa_u32(smem_u32(&bar_a_ready[0]), 0);
     s_wlast[tid] = __ldg(args.w_last + tid);
     uint32_t mma_iter = 0;
-    bool stores_pending = false;
+    uint32_t wpar = 0, wany = 0;        // per quarter: parity of / any hand-overs so far
     const int tiles_alloc = int(args.n_rows_pad / TILE_M);
 
     for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
@@ -206,6 +251,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         s_xyz[TILE_M + rt] = valid ? __ldg(pt + 1) : 0.0f;
         s_xyz[2 * TILE_M + rt] = valid ? __ldg(pt + 2) : 0.0f;
       }
+      bwd_bar();      // s_xyz visible to the column-sum passes of this tile
 
       for (int t = nh - 1; t >= 0; --t) {
         const bool has_acc = (t < nh - 1);
@@ -219,27 +265,24 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           gw0 = __ldg(mrow); gw1 = __ldg(mrow + 4 * TILE_M);
           if (n_halves == 2) { gw2 = __ldg(mrow + 8 * TILE_M); gw3 = __ldg(mrow + 12 * TILE_M); }
         }
-        // every warp has finished the column-sum pass over the previous dY tile before anyone overwrites it
-        bwd_bar();
         uint32_t par = 0;
         if (has_acc) { par = mma_iter & 1; ++mma_iter; }
 
         auto quarter = [&](int Q, uint32_t gate) {
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
+          // the previous dY tile's quarter must have been stashed and column-summed before it is overwritten
+          if ((wany >> Q) & 1u) mbar_wait(&bar_q_released[Q], ((wpar >> Q) & 1u) ^ 1u);
           bwd_pass16(tmem_row + c0, has_acc, dyv, s_wlast + c0, gate, scale, sA, rt, c0);
           bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, s_wlast + c0 + 16, gate >> 16, scale, sA, rt, c0 + 16);
           fence_proxy_async_smem();
           tc_fence_before();
           __syncwarp();
           if (produce_a && lane == 0) mbar_arrive_remote(ready_leader + 8u * uint32_t(Q));
+          if (lane == 0) mbar_arrive(&bar_q_written[Q]);
+          wpar ^= 1u << Q; wany |= 1u << Q;
         };
 
         if (has_acc) { mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); mbar_wait(&bar_free_q0, par); }
-        if (stores_pending) {
-          if (tid == 0) tma_store_wait_read0();
-          bwd_bar();
-          stores_pending = false;
-        }
         quarter(0, gw0);
         if (has_acc) mbar_wait(&bar_free_lo, par);
         quarter(1, gw1);
@@ -253,17 +296,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           if (produce_a && lane == 0) { mbar_arrive_remote(ready_leader + 16u); mbar_arrive_remote(ready_leader + 24u); }
         }
 
-        // ---- tile of dY_t complete in shared memory: stash + column sums
-        bwd_bar();
-        if (args.store_dys && t > 0) {
-          if (tid == 0 && tile_ok) {
-            const int nchunks = n_halves * 4;
-            for (int c = 0; c < nchunks; ++c)
-              tma_store_2d(&tmDys, sA + c * A_CHUNK_BYTES, c * 64, int32_t(int64_t(t) * args.n_rows_pad + int64_t(tile) * TILE_M));
-            tma_store_commit();
-          }
-          stores_pending = true;
-        }
+        // ---- column sums of this warp's 32 columns, once all 16 warps have written that quarter
         {
           // warp w owns columns [32w, 32w+32): lane = (row set, bf16x2 word).  Lanes 0-15 walk the rows with bit 2
           // clear, lanes 16-31 the same rows ^ 4: the SW128 XOR then puts the two half-warps on disjoint bank groups.
@@ -273,6 +306,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           const int word = lane & 15, rpar = lane >> 4;
           float s0 = 0.f, s1 = 0.f, sx0 = 0.f, sx1 = 0.f, sy0 = 0.f, sy1 = 0.f, sz0 = 0.f, sz1 = 0.f;
           if (cols_valid) {
+            mbar_wait(&bar_q_written[warp >> 2], ((wpar >> (warp >> 2)) & 1u) ^ 1u);
             const uint32_t cb = smem_u32(sA) + uint32_t(cw >> 6) * A_CHUNK_BYTES;
             const uint32_t xb = smem_u32(s_xyz);
             const uint32_t colw = uint32_t(cw & 63) / 2 + word;            // bf16x2 word index within the 64-column chunk row
@@ -295,6 +329,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
               }
             }
           }
+          if (cols_valid) { __syncwarp(); if (lane == 0) mbar_arrive(&bar_q_released[warp >> 2]); }
           // combine the two row sets (fixed order)
           s0 += __shfl_down_sync(0xffffffffu, s0, 16); s1 += __shfl_down_sync(0xffffffffu, s1, 16);
           if (want_xyz) {
@@ -319,7 +354,6 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       // s_xyz of this tile must not be overwritten while a slower warp is still in the last column-sum pass
       bwd_bar();
     }
-    if (stores_pending && tid == 0) tma_store_wait_all0();
   }
 
   tc_fence_before();
