@@ -195,7 +195,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       const bool tile_ok = tile < args.n_tiles;
       for (int t = nh - 1; t >= 0; --t) {
         const int nq = (t < nh - 1 ? args.prog[t + 1].n_halves : 2) * 2;
-        const bool do_store = tile_ok && args.store_dys && t > 0;
+        const bool do_store = tile_ok && ((args.store_dys >> t) & 1);
         const int32_t grow0 = int32_t(int64_t(t) * args.n_rows_pad + int64_t(tile) * TILE_M);
         for (int Q = 0; Q < nq; ++Q) {
           mbar_wait_a(wr0 + Q * 8, (cnt >> Q) & 1u);

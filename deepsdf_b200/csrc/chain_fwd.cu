@@ -311,7 +311,8 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       const int tile = 2 * tp + int(rank);
       const bool tile_ok = tile < args.n_tiles;
       const int tile_c = tile_ok ? tile : args.n_tiles - 1;
-      const bool valid = tile_ok && (int64_t(tile_c) * TILE_M + rt) < args.n_rows;
+      const bool valid = tile_ok && (int64_t(tile_c) * TILE_M + rt) < args.n_rows &&
+                         (args.tile_rows == nullptr || int(rt) < __ldg(args.tile_rows + tile_c));
       float px = 0.f, py = 0.f, pz = 0.f;
       if (valid) {
         const float* pt = args.xyz + (int64_t(tile_c) * TILE_M + rt) * args.xyz_stride;
@@ -324,7 +325,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         const ChainLayer& L = args.prog[l];
         const bool last = (l == nh - 1);
         const bool produce_a = !last;
-        const bool drop = kTrain && L.dropout != 0;
+        const bool drop = kTrain && L.dropout != 0 && args.dropout_on != 0;
         const bool has_acc = L.has_mma != 0;
         const float ascale = drop ? args.drop_scale : 1.0f;
         const float* sb = s_bias + (l & 1) * FH;
@@ -423,6 +424,8 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
           if (lane == 0) s_loss[q] = a;
+        } else if (kTrain && args.dy_unit != 0) {
+          if (tile_ok) args.dy_out[lrow] = valid ? dt : 0.0f;
         }
       }
       epi_bar();

@@ -60,6 +60,9 @@ struct FwdArgs {
   float* tile_loss;                         // [n_tiles] sum |pred-gt| of the tile's rows
   uint32_t* bitmask;                        // [num_hidden][N_pad][16]
   int32_t store_acts;
+  int32_t dropout_on;                       // 0: gates mode without dropout (eval-mode forward that still records relu gates)
+  int32_t dy_unit;                          // gt == null: dy_out = d sdf / d(pre-tanh output)  (input-gradient path)
+  const int32_t* tile_rows;                 // [n_tiles] valid rows of each tile (ragged scenes padded to 128), or null
 };
 
 struct BwdArgs {
@@ -78,7 +81,7 @@ struct BwdArgs {
   int32_t part_stride;
   int32_t colsum_slot[DSDF_MAX_LAYERS];     // slot (x512 floats) of colsum(dY_l) in tile_part, or -1
   int32_t xyzsum_slot[DSDF_MAX_LAYERS];     // first of 3 slots of sum_r xyz[r,d]*dY_l[r,:], or -1
-  int32_t store_dys;
+  int32_t store_dys;                        // bit t: TMA-store the bf16 dY tile of hidden layer t
 };
 
 // wgrad work plan.  The row axis of every layer is cut into contiguous segments, one per CLUSTER of four CTAs (the four

@@ -202,7 +202,6 @@ static void fill_programs(const dsdf_net_desc* d, const FusedLayout& lo, ChainLa
   }
 }
 
-int launch_fused_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, const FwdArgs& args, int grid, cudaStream_t stream);
 int launch_chain_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, const FwdArgs& args, int n_sms, cudaStream_t stream);
 
 }  // namespace dsdf
@@ -298,19 +297,18 @@ extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, c
   a.tile_loss = tr->tile_loss;
   a.bitmask = tr->bitmask;
   a.store_acts = (tr->acts != nullptr);
-  if (getenv("DSDF_EXP_NOSTASH")) a.store_acts = 0;        // timing experiment only (wgrad then reads stale data)
+  a.dropout_on = tr->dropout_off ? 0 : 1;
+  a.dy_unit = tr->dy_unit;
+  a.tile_rows = tr->tile_rows;
   if (a.training) {
     DSDF_REQUIRE(tr->n_rows_pad == a.n_rows_pad, "n_rows_pad must be n_rows rounded up to 128");
     if (a.gt) DSDF_REQUIRE(a.dy_out && a.tile_loss, "training with gt needs dy_out and tile_loss");
+    if (a.dy_unit) DSDF_REQUIRE(a.dy_out && !a.gt, "dy_unit needs dy_out and no gt");
   }
   CUtensorMap tmW, tmActs;
-  static const bool use_v1 = getenv("DSDF_CHAIN_V1") != nullptr;   // debugging aid: the single-CTA first-generation kernel
-  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wp, FH, lo.fwd_rows, FH * 2, 64, use_v1 ? HALF_N : 128)) return e;
+  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wp, FH, lo.fwd_rows, FH * 2, 64, 128)) return e;
   const void* acts_ptr = tr->acts ? tr->acts : static_cast<const void*>(p + lo.off_wp);   // dummy map when unused
   const uint64_t acts_rows = tr->acts ? uint64_t(lo.num_hidden) * a.n_rows_pad : uint64_t(lo.fwd_rows);
   if (int e = make_tmap_bf16_2d(&tmActs, acts_ptr, FH, acts_rows, FH * 2, 64, TILE_M)) return e;
-  if (!use_v1) return launch_chain_forward(tmW, tmActs, a, sm_count(), static_cast<cudaStream_t>(stream));
-  int grid = sm_count();
-  if (grid > a.n_tiles) grid = a.n_tiles;
-  return launch_fused_forward(tmW, tmActs, a, grid, static_cast<cudaStream_t>(stream));
+  return launch_chain_forward(tmW, tmActs, a, sm_count(), static_cast<cudaStream_t>(stream));
 }
