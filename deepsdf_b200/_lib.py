@@ -39,6 +39,7 @@ class TrainIO(C.Structure):
         ("b_last", C.c_void_p), ("training", C.c_int32), ("seed", C.c_uint64), ("row0", C.c_uint64),
         ("gt", C.c_void_p), ("gt_stride", C.c_int32), ("clamp", C.c_float), ("inv_n", C.c_float), ("dy_out", C.c_void_p),
         ("tile_loss", C.c_void_p), ("bitmask", C.c_void_p), ("acts", C.c_void_p), ("n_rows_pad", C.c_int64),
+        ("dropout_off", C.c_int32), ("dy_unit", C.c_int32), ("tile_rows", C.c_void_p),
     ]
 
 
@@ -67,6 +68,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_pack_weights": (C.c_int, [P(NetDesc), P(Params), vp, vp]),
         "dsdf_scene_prepare": (C.c_int, [P(NetDesc), vp, vp, vp, i32, f32, vp, vp]),
         "dsdf_fused_forward": (C.c_int, [P(NetDesc), vp, vp, vp, vp, i32, i64, vp, P(TrainIO), vp]),
+        "dsdf_grid_points": (C.c_int, [i32, i64, i64, vp, vp]),
         "dsdf_selftest_umma_pair": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp]),
         "dsdf_selftest_umma": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint,
                                          C.c_uint, vp]),
@@ -88,7 +90,7 @@ def lib() -> C.CDLL:
                 "or `make -C deepsdf_b200/csrc` (there is no fallback path)")
         _lib = C.CDLL(LIB_PATH)
         _declare(_lib)
-        if _lib.dsdf_abi_version() != 1:
+        if _lib.dsdf_abi_version() != 2:
             raise DsdfError("libdsdf_b200.so ABI version mismatch")
     return _lib
 

@@ -303,10 +303,13 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           const int cw = warp * 32;
           const bool cols_valid = cw < n_halves * 256;
           const bool want_xyz = args.xyzsum_slot[t] >= 0;
+          const bool do_sums = want_xyz || args.colsum_slot[t] >= 0;
           const int word = lane & 15, rpar = lane >> 4;
           float s0 = 0.f, s1 = 0.f, sx0 = 0.f, sx1 = 0.f, sy0 = 0.f, sy1 = 0.f, sz0 = 0.f, sz1 = 0.f;
           if (cols_valid) {
             mbar_wait(&bar_q_written[warp >> 2], ((wpar >> (warp >> 2)) & 1u) ^ 1u);
+          }
+          if (cols_valid && do_sums) {
             const uint32_t cb = smem_u32(sA) + uint32_t(cw >> 6) * A_CHUNK_BYTES;
             const uint32_t xb = smem_u32(s_xyz);
             const uint32_t colw = uint32_t(cw & 63) / 2 + word;            // bf16x2 word index within the 64-column chunk row
@@ -337,7 +340,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
             sy0 += __shfl_down_sync(0xffffffffu, sy0, 16); sy1 += __shfl_down_sync(0xffffffffu, sy1, 16);
             sz0 += __shfl_down_sync(0xffffffffu, sz0, 16); sz1 += __shfl_down_sync(0xffffffffu, sz1, 16);
           }
-          if (tile_ok && rpar == 0) {
+          if (tile_ok && rpar == 0 && do_sums) {
             float* part = args.tile_part + size_t(tile) * args.part_stride;
             const int col = cw + word * 2;
             if (args.colsum_slot[t] >= 0)

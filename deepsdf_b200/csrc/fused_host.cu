@@ -71,6 +71,8 @@ int fused_layout(const dsdf_net_desc* d, FusedLayout* lo) {
   lo->off_wxyz = off;    off = align_up(off + size_t(2) * 3 * FH * 4, 256);        // slot 0: lin0, slot 1: skip layer
   lo->off_wlatT = off;   off = align_up(off + size_t(2) * L * FH * 4, 256);        // [slot][k][512]
   lo->off_wlast = off;   off = align_up(off + size_t(FH) * 4, 256);
+  lo->jac_rows = (LD + 15) / 16 * 16;
+  lo->off_wjac = align_up(off, 1024);   off = align_up(lo->off_wjac + size_t(lo->jac_rows) * 2 * FH * 2, 1024);
   for (int l = 0; l < nl; ++l) {
     lo->off_weff[l] = off;  off = align_up(off + size_t(d->out_dim[l]) * d->in_dim[l] * 4, 256);
     lo->off_invn[l] = off;  off = align_up(off + size_t(d->out_dim[l]) * 4, 256);
@@ -118,6 +120,7 @@ __global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
   float* wxyz = reinterpret_cast<float*>(a.pack + a.lo.off_wxyz);
   float* wlatT = reinterpret_cast<float*>(a.pack + a.lo.off_wlatT);
   float* wlast = reinterpret_cast<float*>(a.pack + a.lo.off_wlast);
+  __nv_bfloat16* wjac = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wjac);
   const int L = d.latent_size;
   for (int k = threadIdx.x; k < in; k += blockDim.x) {
     const float w = vrow[k] * scale;
@@ -132,9 +135,11 @@ __global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
     } else if (a.lo.lat_col0[l] >= 0 && k < a.lo.lat_col0[l] + L) {
       const int slot = (l == 0) ? 0 : 1;
       wlatT[(size_t(slot) * L + (k - a.lo.lat_col0[l])) * FH + o] = w;
+      wjac[size_t(k - a.lo.lat_col0[l]) * (2 * FH) + slot * FH + o] = __float2bfloat16_rn(w);
     } else if (a.lo.xyz_col0[l] >= 0 && k >= a.lo.xyz_col0[l]) {
       const int slot = (l == 0) ? 0 : 1;
       wxyz[(size_t(slot) * 3 + (k - a.lo.xyz_col0[l])) * FH + o] = w;
+      wjac[size_t(L + k - a.lo.xyz_col0[l]) * (2 * FH) + slot * FH + o] = __float2bfloat16_rn(w);
     }
   }
 }

@@ -21,6 +21,9 @@ struct FusedLayout {
   size_t off_wxyz;                       // f32  [2][3][512]       xyz columns of lin0 / skip layer
   size_t off_wlatT;                      // f32  [2][L][512]       latent columns of lin0 / skip layer, transposed
   size_t off_wlast;                      // f32  [512]             effective last-layer weight
+  size_t off_wjac;                       // bf16 [jac_rows][1024]  input-gradient B operand: row c < L latent column c, rows
+                                         //                        L..L+2 xyz; K < 512 from lin0, K >= 512 from the latent_in layer
+  int32_t jac_rows;                      // L+3 rounded up to a multiple of 16 (<= 272)
   size_t off_weff[DSDF_MAX_LAYERS];      // f32  [out][in]         effective (folded) weights, reference layout
   size_t off_invn[DSDF_MAX_LAYERS];      // f32  [out]             1/||v|| per row (1 for plain layers)
   size_t total_bytes;

@@ -6,7 +6,6 @@
 
 namespace dsdf {
 
-int launch_fused_dgrad(const CUtensorMap& tmW, const CUtensorMap& tmDys, const BwdArgs& args, int grid, cudaStream_t stream);
 int launch_chain_dgrad(const CUtensorMap& tmW, const CUtensorMap& tmDys, const BwdArgs& args, int n_sms, cudaStream_t stream);
 int launch_wgrad(const CUtensorMap& tmDys, const CUtensorMap& tmActs, const WgradArgs& args, cudaStream_t stream);
 int wgrad_max_active_clusters();
@@ -89,7 +88,8 @@ extern "C" int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, i
 }
 
 extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, const dsdf_train_bufs* bufs, const float* xyz,
-                                int32_t xyz_stride, int64_t n_rows, int32_t training, void* stream) {
+                                int32_t xyz_stride, int64_t n_rows, int32_t training, uint32_t store_mask,
+                                uint32_t sum_mask, void* stream) {
   if (int e = require_sm100()) return e;
   FusedLayout lo;
   if (int e = fused_layout(desc, &lo)) return e;
@@ -118,23 +118,24 @@ extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, con
   const float sc = 1.0f / (1.0f - desc->dropout_prob);
   for (int l = 0; l < lo.num_hidden; ++l) {
     a.scale[l] = (training && ((desc->dropout_mask >> l) & 1)) ? sc : 1.0f;
-    a.colsum_slot[l] = l;
-    a.xyzsum_slot[l] = (l == 0) ? lo.num_hidden : (l == lo.lat_layer ? lo.num_hidden + 3 : -1);
+    const bool sums = (sum_mask >> l) & 1u;
+    a.colsum_slot[l] = sums ? l : -1;
+    a.xyzsum_slot[l] = !sums ? -1 : ((l == 0) ? lo.num_hidden : (l == lo.lat_layer ? lo.num_hidden + 3 : -1));
   }
   a.xyz = xyz;
   DSDF_REQUIRE(xyz_stride >= 3, "xyz_stride must be >= 3");
   a.xyz_stride = xyz_stride;
   a.tile_part = bufs->tile_part;
   a.part_stride = n_slots(lo) * FH;
-  a.store_dys = getenv("DSDF_EXP_NOSTASH") ? 0 : 1;       // timing experiment only
+  a.store_dys = int32_t(store_mask & ((1u << lo.num_hidden) - 1u));
+  DSDF_REQUIRE(a.store_dys == 0 || bufs->dys != nullptr, "store_mask needs bufs->dys");
+  DSDF_REQUIRE(sum_mask == 0 || bufs->tile_part != nullptr, "sum_mask needs bufs->tile_part");
   CUtensorMap tmW, tmDys;
-  static const bool use_v1 = getenv("DSDF_CHAIN_V1") != nullptr;   // debugging aid: the single-CTA first-generation kernel
-  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wpt, FH, lo.bwd_rows, FH * 2, 64, use_v1 ? HALF_N : 128)) return e;
-  if (int e = make_tmap_bf16_2d(&tmDys, bufs->dys, FH, uint64_t(lo.num_hidden) * n_rows, FH * 2, 64, TILE_M)) return e;
-  if (!use_v1) return launch_chain_dgrad(tmW, tmDys, a, sm_count(), static_cast<cudaStream_t>(stream));
-  int grid = sm_count();
-  if (grid > a.n_tiles) grid = a.n_tiles;
-  return launch_fused_dgrad(tmW, tmDys, a, grid, static_cast<cudaStream_t>(stream));
+  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wpt, FH, lo.bwd_rows, FH * 2, 64, 128)) return e;
+  const void* dys_ptr = bufs->dys ? bufs->dys : static_cast<const void*>(p + lo.off_wpt);   // dummy map when nothing is stored
+  const uint64_t dys_rows = bufs->dys ? uint64_t(lo.num_hidden) * n_rows : uint64_t(lo.bwd_rows);
+  if (int e = make_tmap_bf16_2d(&tmDys, dys_ptr, FH, dys_rows, FH * 2, 64, TILE_M)) return e;
+  return launch_chain_dgrad(tmW, tmDys, a, sm_count(), static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs* bufs, int64_t n_rows, void* stream) {

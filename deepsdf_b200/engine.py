@@ -20,6 +20,8 @@ from . import _lib as L
 from .networks.deep_sdf_decoder import Decoder
 
 TILE = 128
+STORE_DYS_TRAIN = 0xFFFFFFFE      # include/dsdf.h DSDF_STORE_DYS_TRAIN
+SUMS_ALL = 0xFFFFFFFF
 
 
 class TrainBufs(C.Structure):
@@ -35,7 +37,11 @@ def _declare_train(lib) -> None:
     lib.dsdf_train_buf_sizes.restype = C.c_int
     lib.dsdf_train_buf_sizes.argtypes = [P(L.NetDesc), i64, i32, P(sz)]
     lib.dsdf_fused_dgrad.restype = C.c_int
-    lib.dsdf_fused_dgrad.argtypes = [P(L.NetDesc), vp, P(TrainBufs), vp, i32, i64, i32, vp]
+    lib.dsdf_fused_dgrad.argtypes = [P(L.NetDesc), vp, P(TrainBufs), vp, i32, i64, i32, C.c_uint32, C.c_uint32, vp]
+    lib.dsdf_fused_input_grad.restype = C.c_int
+    lib.dsdf_fused_input_grad.argtypes = [P(L.NetDesc), vp, P(TrainBufs), i64, vp, i64, vp]
+    lib.dsdf_fused_latent_finish.restype = C.c_int
+    lib.dsdf_fused_latent_finish.argtypes = [P(L.NetDesc), vp, P(TrainBufs), vp, i64, vp, vp, i32, f32, f32, vp, vp, vp]
     lib.dsdf_fused_wgrad.restype = C.c_int
     lib.dsdf_fused_wgrad.argtypes = [P(L.NetDesc), P(TrainBufs), i64, vp]
     lib.dsdf_fused_finish.restype = C.c_int
@@ -117,9 +123,119 @@ class FusedEngine:
                                                 xyz.data_ptr(), 3, N, sdf.data_ptr(), C.byref(io), self._st()))
         return sdf
 
+    # ------------------------------------------------------------------ input gradient (mesh.py:405-454 consumers)
+    @property
+    def lat_layer(self) -> int:
+        li = [l for l in (self.spec.latent_in or ()) if 0 < l < self.num_hidden]
+        return li[0] if li else -1
+
+    def grad_buffers(self, n_rows: int, need_dys: bool = True) -> Dict[str, torch.Tensor]:
+        """Scratch of the input-gradient / latent-optimisation passes for ``n_rows`` (multiple of 128) rows: gate bits,
+        dL/dy seed, the bf16 dY stash (only lin0's and the latent_in layer's regions are written) and per-tile sums."""
+        key = ("grad", n_rows, need_dys)
+        if self._bufs_key == key:
+            return self._bufs
+        nh = self.num_hidden
+        n_tiles = n_rows // TILE
+        self._bufs = {}                      # drop the previous set before allocating the next
+        self._bufs_key = None
+        b = {
+            "bitmask": torch.empty(nh * n_rows * 16, dtype=torch.int32, device=self.device),
+            "dy": torch.empty(n_rows, device=self.device),
+            "dys": torch.empty(nh * n_rows * 512 if need_dys else 8, dtype=torch.bfloat16, device=self.device),
+            "tile_loss": torch.empty(n_tiles, device=self.device),
+            "tile_part": torch.empty(n_tiles * (nh + 6) * 512, device=self.device),
+            "sdf": torch.empty(n_rows, device=self.device),
+        }
+        tb = TrainBufs()
+        for n in ("bitmask", "dy", "dys", "tile_loss", "tile_part"):
+            if n != "dys" or need_dys:
+                setattr(tb, n, b[n].data_ptr())
+        self._bufs, self._tb, self._bufs_key = b, tb, key
+        return b
+
+    def sdf_and_input_grad(self, cbias: torch.Tensor, tile_scene: torch.Tensor, xyz: torch.Tensor,
+                           G: Optional[torch.Tensor] = None, sdf: Optional[torch.Tensor] = None):
+        """Eval-mode SDF [N] and G [N, L+3] = dSDF/d[latent, xyz] (column order of the decoder input) of scene-tiled
+        points ``xyz`` [N,3], N % 128 == 0.  Three launches: forward (records relu gates, seeds dy = 1 - tanh^2),
+        dgrad chain (stashes dY of lin0 and of the latent_in layer), input-gradient GEMM."""
+        L.require_cuda(cbias, tile_scene, xyz)
+        N = xyz.shape[0]
+        if N % TILE or N == 0:
+            raise L.DsdfError("sdf_and_input_grad needs a positive multiple of 128 rows (pad the queries)")
+        assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.shape[1] == 3
+        assert tile_scene.dtype == torch.int32 and tile_scene.numel() == N // TILE
+        Lz = self.spec.latent_size
+        b = self.grad_buffers(N)
+        sdf = sdf if sdf is not None else torch.empty(N, device=self.device)
+        G = G if G is not None else torch.empty(N, Lz + 3, device=self.device)
+        assert G.dtype == torch.float32 and G.shape[0] == N and G.shape[1] >= Lz + 3 and G.stride(1) == 1
+        io = L.TrainIO()
+        io.b_last = self._b_last().data_ptr()
+        io.training, io.dropout_off, io.dy_unit = 1, 1, 1
+        io.dy_out = b["dy"].data_ptr()
+        io.bitmask = b["bitmask"].data_ptr()
+        io.n_rows_pad = N
+        lat = self.lat_layer
+        store = 1 | ((1 << lat) if lat > 0 else 0)
+        lib, desc, st = self.lib, self.desc, self._st()
+        with torch.cuda.device(self.device):
+            L.check(lib.dsdf_fused_forward(C.byref(desc), self.pack.data_ptr(), cbias.data_ptr(), tile_scene.data_ptr(),
+                                           xyz.data_ptr(), 3, N, sdf.data_ptr(), C.byref(io), st))
+            L.check(lib.dsdf_fused_dgrad(C.byref(desc), self.pack.data_ptr(), C.byref(self._tb), xyz.data_ptr(), 3, N, 0,
+                                         store, 0, st))
+            L.check(lib.dsdf_fused_input_grad(C.byref(desc), self.pack.data_ptr(), C.byref(self._tb), N, G.data_ptr(),
+                                              G.stride(0), st))
+        return sdf, G
+
+    def grid_points(self, N: int, i0: int, n: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Rows [i0, i0+n) of create_mesh's N^3 sample grid (deep_sdf/mesh.py:37-53) as [n,3] fp32."""
+        out = out if out is not None else torch.empty(n, 3, device=self.device)
+        with torch.cuda.device(self.device):
+            L.check(self.lib.dsdf_grid_points(N, i0, n, out.data_ptr(), self._st()))
+        return out
+
+    # ------------------------------------------------------------------ frozen-decoder latent optimisation
+    def latent_loss_and_grad(self, lat_table: torch.Tensor, scene_ids: torch.Tensor, tile_scene: torch.Tensor,
+                             tile_rows: Optional[torch.Tensor], samples: torch.Tensor, *, clamp: float, rows_per_shape: int,
+                             l2reg: float, lat_grad: torch.Tensor, shape_loss: torch.Tensor) -> None:
+        """One iteration of upstream reconstruct.py for every shape of the batch: ``samples`` [S * T * 128, 4] (x,y,z,sdf),
+        shape-major, each shape padded to T tiles with ``tile_rows`` giving the valid rows of every tile.  Writes
+        lat_grad [S, L] = d(mean|clamp(pred)-clamp(gt)| + l2reg*mean(z^2))/dz and shape_loss [S]."""
+        N = samples.shape[0]
+        S = scene_ids.numel()
+        b = self.grad_buffers(N, need_dys=False)
+        if "cbias" not in b or b["cbias"].shape[0] != S:
+            b["cbias"] = torch.empty(S, 2, 512, device=self.device)
+        cb = self.scene_bias(lat_table, scene_ids, None, out=b["cbias"])
+        io = L.TrainIO()
+        io.b_last = self._b_last().data_ptr()
+        io.training, io.dropout_off = 1, 1
+        flat = samples.view(-1)
+        io.gt = flat[3:].data_ptr()
+        io.gt_stride = 4
+        io.clamp = float(clamp)
+        io.inv_n = 1.0 / float(rows_per_shape)
+        io.dy_out = b["dy"].data_ptr()
+        io.tile_loss = b["tile_loss"].data_ptr()
+        io.bitmask = b["bitmask"].data_ptr()
+        io.n_rows_pad = N
+        io.tile_rows = tile_rows.data_ptr() if tile_rows is not None else None
+        lat = self.lat_layer
+        sums = 1 | ((1 << lat) if lat > 0 else 0)
+        lib, desc, st = self.lib, self.desc, self._st()
+        with torch.cuda.device(self.device):
+            L.check(lib.dsdf_fused_forward(C.byref(desc), self.pack.data_ptr(), cb.data_ptr(), tile_scene.data_ptr(),
+                                           flat.data_ptr(), 4, N, b["sdf"].data_ptr(), C.byref(io), st))
+            L.check(lib.dsdf_fused_dgrad(C.byref(desc), self.pack.data_ptr(), C.byref(self._tb), flat.data_ptr(), 4, N, 0,
+                                         0, sums, st))
+            L.check(lib.dsdf_fused_latent_finish(C.byref(desc), self.pack.data_ptr(), C.byref(self._tb), tile_scene.data_ptr(), N,
+                                                 lat_table.data_ptr(), scene_ids.data_ptr(), S, float(l2reg),
+                                                 1.0 / float(rows_per_shape), lat_grad.data_ptr(), shape_loss.data_ptr(), st))
+
     # ------------------------------------------------------------------ training
     def train_buffers(self, n_rows: int, n_scenes: int) -> Dict[str, torch.Tensor]:
-        key = (n_rows, n_scenes)
+        key = ("train", n_rows, n_scenes)
         if self._bufs_key == key:
             return self._bufs
         sizes = (C.c_size_t * 10)()
@@ -198,7 +314,7 @@ class FusedEngine:
                                            point_stride, N, b["sdf"].data_ptr(), C.byref(io), st))
             e1 = mark()
             L.check(lib.dsdf_fused_dgrad(C.byref(desc), self.pack.data_ptr(), C.byref(tb), xyz.data_ptr(), point_stride, N,
-                                         int(training), st))
+                                         int(training), STORE_DYS_TRAIN, SUMS_ALL, st))
             e2 = mark()
             L.check(lib.dsdf_fused_wgrad(C.byref(desc), C.byref(tb), N, st))
             e3 = mark()

@@ -1,0 +1,50 @@
+"""Drop-in for ``deep_sdf/utils.py:54-65`` ``decode_sdf`` on the B200 path.
+
+``decode_sdf(decoder, latent_vector, queries)`` keeps the reference's meaning: ``latent_vector`` ([L] or [1, L]) is
+broadcast over ``queries`` [n, 3]; with ``latent_vector=None`` the queries already carry their latent columns
+([n, L+3]).  For the 8x512-class decoders and a broadcast latent the call runs on the fused tcgen05 forward (the latent
+collapses into one per-scene bias vector, nothing of size [n, L+3] is materialised); everything else goes through the
+module's generic CUDA path.  No CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+TILE = 128
+
+
+def fused_engine_for(decoder):
+    """The module's cached FusedEngine (re-packed from the live parameters), or None if its NetworkSpecs is not
+    supported by the fused path."""
+    from .engine import FusedEngine
+    dec = decoder.module if isinstance(decoder, torch.nn.DataParallel) else decoder
+    if not hasattr(dec, "_desc") or L.lib().dsdf_fused_supported(C.byref(dec._desc)) != 1:
+        return None
+    eng = getattr(dec, "_fused_engine", None)
+    if eng is None or eng.device != next(dec.parameters()).device:
+        eng = FusedEngine(dec)
+        object.__setattr__(dec, "_fused_engine", eng)
+    else:
+        eng.repack()
+    return eng
+
+
+def decode_sdf(decoder, latent_vector, queries):
+    num_samples = queries.shape[0]
+    if latent_vector is None:
+        return decoder(queries)
+    needs_grad = torch.is_grad_enabled() and (latent_vector.requires_grad or queries.requires_grad)
+    eng = None if (needs_grad or decoder.training or num_samples == 0) else fused_engine_for(decoder)
+    if eng is None:
+        latent_repeat = latent_vector.reshape(1, -1).expand(num_samples, -1).to(queries.device)
+        return decoder(torch.cat([latent_repeat, queries], 1))
+    dev = eng.device
+    q = queries.detach().to(dev, torch.float32).contiguous()
+    table = latent_vector.detach().reshape(1, -1).to(dev, torch.float32).contiguous()
+    cb = eng.scene_bias(table, torch.zeros(1, dtype=torch.int64, device=dev))
+    ts = torch.zeros((num_samples + TILE - 1) // TILE, dtype=torch.int32, device=dev)
+    return eng.decode_scenes(cb, ts, q).unsqueeze(1)

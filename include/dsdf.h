@@ -18,6 +18,8 @@
  *   dsdf_fused_finish        weight_norm backward, latent grad, code regulariser   train_deep_sdf.py:523-533
  *   dsdf_adam                optimizer_all.step()              train_deep_sdf.py:400-411,545
  *   dsdf_grid_points         create_mesh sample grid           deep_sdf/mesh.py:37-53
+ *   dsdf_fused_input_grad    autograd.functional.jvp loop      deep_sdf/mesh.py:405-422
+ *   dsdf_fused_latent_finish reconstruct.py latent optimisation (upstream; README.md:134-142)
  */
 #ifndef DSDF_B200_H
 #define DSDF_B200_H
@@ -30,7 +32,7 @@ extern "C" {
 #endif
 
 #define DSDF_MAX_LAYERS 16
-#define DSDF_ABI_VERSION 1
+#define DSDF_ABI_VERSION 2
 
 /* Network description == the reference's NetworkSpecs after Decoder.__init__ resolved the layer sizes. */
 typedef struct dsdf_net_desc {
@@ -118,6 +120,10 @@ typedef struct dsdf_train_io {
   uint32_t* bitmask;       /* [num_hidden][n_rows_pad][16] relu*dropout keep bits, or NULL */
   void* acts;              /* bf16 [num_hidden][n_rows_pad][512] post-activation stash for wgrad, or NULL */
   int64_t n_rows_pad;      /* n_rows rounded up to a multiple of 128 */
+  int32_t dropout_off;     /* training=1 with dropout disabled: an eval-mode forward that still records the relu gates
+                              (what the input-gradient path and the frozen-decoder latent optimisation need) */
+  int32_t dy_unit;         /* gt == NULL: dy_out = d sdf / d(pre-tanh output), the seed of the input gradient */
+  const int32_t* tile_rows;/* [n_tiles] valid rows per 128-row tile (ragged scenes padded to tiles), or NULL = all */
 } dsdf_train_io;
 
 int dsdf_fused_supported(const dsdf_net_desc* desc);
@@ -157,13 +163,44 @@ typedef struct dsdf_train_bufs {
 } dsdf_train_bufs;
 
 int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, int32_t n_scenes, size_t* sizes);
+/* store_mask: bit t set = keep the bf16 dY tile of hidden layer t in bufs->dys (training: every t > 0 =
+ * DSDF_STORE_DYS_TRAIN; input gradient: layer 0 and the latent_in layer; latent-only optimisation: 0).
+ * sum_mask: bit t set = emit the per-tile column sums of dY_t (and the xyz-weighted ones of lin0 / latent_in layer)
+ * into bufs->tile_part (training: all layers; latent-only optimisation: layer 0 and the latent_in layer). */
+#define DSDF_STORE_DYS_TRAIN 0xFFFFFFFEu
+#define DSDF_SUMS_ALL 0xFFFFFFFFu
 int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, const dsdf_train_bufs* bufs, const float* xyz,
-                     int32_t xyz_stride, int64_t n_rows, int32_t training, void* stream);
+                     int32_t xyz_stride, int64_t n_rows, int32_t training, uint32_t store_mask, uint32_t sum_mask,
+                     void* stream);
 int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs* bufs, int64_t n_rows, void* stream);
 int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
                       const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows, const float* lat_table,
                       const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total, float reg_lambda_eff,
                       float inv_n, const dsdf_param_grads* pgrads, float* lat_grad, float* loss_out, void* stream);
+/* ------------------------------------------------------------------------------------------------
+ * Input gradient (the derivative consumers of deep_sdf/mesh.py:405-454 and analysis/: dSDF/dlatent, dSDF/dxyz).
+ * After  dsdf_fused_forward(training=1, dropout_off=1, dy_unit=1)  and  dsdf_fused_dgrad(store_mask = layer 0 |
+ * latent_in layer)  this contracts the stashed dY tiles of those two layers with the latent / xyz columns of their
+ * weights on the tensor cores:   G[r, 0:L] = dSDF/dlatent,  G[r, L:L+3] = dSDF/dxyz   - the column order of the
+ * reference's decoder input [latent, xyz] (deep_sdf/utils.py:57-63), so G == input.grad of Decoder.forward.
+ * G is fp32 [n_rows][ldg], ldg >= L+3. */
+int dsdf_fused_input_grad(const dsdf_net_desc* desc, const void* pack, const dsdf_train_bufs* bufs, int64_t n_rows,
+                          float* G, int64_t ldg, void* stream);
+
+/* create_mesh's sample grid (deep_sdf/mesh.py:37-53): linear index i = (ix*N + iy)*N + iz  ->  xyz = -1 + idx*2/(N-1).
+ * Writes rows [i0, i0+n) of the N^3 grid as fp32 [n][3] (a z-slab of the slowest index is a contiguous index range). */
+int dsdf_grid_points(int32_t N, int64_t i0, int64_t n, float* xyz_out, void* stream);
+
+/* Frozen-decoder latent optimisation (upstream DeepSDF reconstruct.py; README.md:134-142 of the reference): after
+ * forward(training=1, dropout_off=1, gt, clamp, inv_n = 1/rows_per_shape) + dgrad(sum_mask = layer 0 | latent_in layer)
+ * reduce the per-tile column sums per shape and form   lat_grad[s] = d/dz ( mean|clamp(pred)-clamp(gt)| +
+ * l2reg * mean(z^2) )   and   shape_loss[s] (same expression).  lat_grad is [n_scenes][L] (row s = scene_ids[s]'s
+ * gradient, dense in batch order), deterministic. */
+int dsdf_fused_latent_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_train_bufs* bufs,
+                             const int32_t* tile_scene, int64_t n_rows, const float* lat_table, const int64_t* scene_ids,
+                             int32_t n_scenes, float l2reg, float inv_n, float* lat_grad, float* shape_loss,
+                             void* stream);
+
 /* torch.optim.Adam update of one flat fp32 tensor (dense, no weight decay); step counts from 1; g is multiplied by
  * grad_scale and, if grad_scale_dev != NULL, by the device scalar *grad_scale_dev first (gradient clipping without a
  * host round trip). */
