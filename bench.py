@@ -305,6 +305,15 @@ def run_gpu(args):
         "step_frac_of_datasheet_2250": FLOP_TRAIN_PER_ROW * N / (ms_step / 1e3) / 1e12 / 2250.0,
     }
 
+    # ---- secondary metrics of BASELINE.json (never part of the timed train region): grid queries/s (config #4) and the
+    #      batched latent-only optimisation (config #3), each sharded without a collective
+    extras = {}
+    if not args.no_extras:
+        try:
+            extras = run_extras(trainer, dev, rank, world, barrier, max_over_ranks)
+        except Exception as exc:  # noqa: BLE001 - the headline line must still be printed
+            extras = {"error": repr(exc)[:300]}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -327,16 +336,92 @@ def run_gpu(args):
                    "cache": "per-step working set (bf16 activation + dY stashes, 17 GB) is far larger than the 126 MB L2; 4 rotating input batches"},
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e},
-        "gpu_launches": 13 * args.steps,
+        "gpu_launches": 14 * args.steps,      # per step: renorm, scene bias, forward, dgrad, wgrad, wgrad_last, 5 finish, 2 Adam, pack
         "roofline": roofline,
         "cpu_baseline": cpu,
         "clocks": clk,
+        "grid": extras.get("grid"), "latent_opt": extras.get("latent_opt"), "extras_error": extras.get("error"),
         "loss_last_step": loss_dev,
         "loss_last_step_e2e": [float(x) for x in last],
     }
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_extras(trainer, dev, rank, world, barrier, max_over_ranks):
+    """BASELINE.json configs #4 and #3 on the trained-shape decoder of the bench (random weights):
+    grid   create_mesh's 512^3 grid (mesh.py:37-73), z-slab sharded over the ranks, SDF only and SDF + full input gradient
+           (dSDF/dxyz [n,3] and dSDF/dlatent [n,256] written to HBM chunk by chunk);
+    latent reconstruct.py-style latent-only optimisation, 1024 shapes per GPU x 8000 samples, a bounded number of iterations."""
+    from deepsdf_b200.mesh import slab_for_rank
+    from deepsdf_b200.reconstruct import LatentOptimizer
+    from deepsdf_b200.utils import fused_engine_for
+    out = {}
+    dec = trainer.decoder
+    dec.eval()
+    trainer.engine._bufs, trainer.engine._bufs_key = {}, None     # release the 18 GB training stash
+    torch.cuda.empty_cache()
+    eng = fused_engine_for(dec)
+    Lz = eng.spec.latent_size
+    NG = 512
+    i0, i1 = slab_for_rank(NG, rank, world)
+    first, total = i0 * NG * NG, (i1 - i0) * NG * NG
+    chunk = 1 << 21
+    xyz = torch.zeros(chunk, 3, device=dev)
+    ts = torch.zeros(chunk // 128, dtype=torch.int32, device=dev)
+    sdf = torch.empty(chunk, device=dev)
+    G = torch.empty(chunk, Lz + 3, device=dev)
+    cb = eng.scene_bias(trainer.lat_vecs[:1].contiguous(), torch.zeros(1, dtype=torch.int64, device=dev))
+
+    def sweep(with_grad):
+        head = 0
+        while head < total:
+            n = min(chunk, total - head)
+            eng.grid_points(NG, first + head, n, out=xyz)
+            if with_grad:
+                eng.sdf_and_input_grad(cb, ts, xyz, G=G, sdf=sdf)
+            else:
+                eng.decode_scenes(cb, ts, xyz, out=sdf)
+            head += n
+
+    res = {}
+    for with_grad in (False, True):
+        sweep(with_grad)                                     # warm-up (allocations, attribute setup)
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); sweep(with_grad); b.record()
+        barrier()
+        ms = max_over_ranks(a.elapsed_time(b))
+        res["sdf_and_grad" if with_grad else "sdf_only"] = {"ms": ms, "queries_per_s": NG ** 3 / (ms / 1e3)}
+    flop = 2 * FLOP_FWD_PER_ROW
+    out["grid"] = {"N": NG, "queries": NG ** 3, "sharding": f"z-slab x{world}", "chunk_rows": chunk, **res,
+                   "sdf_and_grad_tflops_algorithmic": flop * NG ** 3 / (res["sdf_and_grad"]["ms"] / 1e3) / 1e12,
+                   "outputs": f"sdf [n], G [n,{Lz + 3}] = dSDF/d[latent, xyz] fp32 per chunk"}
+    del xyz, ts, sdf, G
+    eng._bufs, eng._bufs_key = {}, None
+    torch.cuda.empty_cache()
+
+    S, ns, M, iters = 1024, 8000, 16384, 10
+    gen = torch.Generator(device=dev).manual_seed(11 + rank)
+    ids = torch.arange(S) % SCENES_TOTAL
+    data = torch.empty(S, M, 4, device=dev)
+    for s0 in range(0, S, SCENES_PER_STEP):
+        blk = make_batch(gen, dev, ids[s0:s0 + SCENES_PER_STEP], SCENES_TOTAL)
+        data[s0:s0 + SCENES_PER_STEP] = blk.view(SCENES_PER_STEP, M, 4)
+    opt = LatentOptimizer(dec, S, num_samples=ns, seed=rank)
+    opt.reconstruct(data, num_iterations=2)
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(); hist = opt.reconstruct(data, num_iterations=iters, record_every=iters); b.record()
+    barrier()
+    ms = max_over_ranks(a.elapsed_time(b))
+    out["latent_opt"] = {"shapes_per_gpu": S, "samples_per_shape": ns, "iterations_timed": iters, "ms_per_iteration": ms / iters,
+                         "samples_per_s": world * S * ns * iters / (ms / 1e3),
+                         "projected_s_for_800_iterations": 800 * ms / iters / 1e3,
+                         "mean_loss_last": float(hist[-1].mean()) if hist else None,
+                         "sharding": f"shapes x{world} (replicas, no collective)"}
+    return out
 
 
 def main():
@@ -346,6 +431,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the grid / latent-optimisation secondary metrics")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

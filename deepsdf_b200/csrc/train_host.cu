@@ -182,7 +182,7 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
   a.scene_reg = bufs->scene_sums + size_t(n_scenes) * a.n_slots * FH;
   a.wg_part = bufs->wg_part;
   a.last_part = bufs->last_part;
-  a.n_last_blocks = kLastBlocks;
+  a.n_last_blocks = 1;               // last_reduce_kernel folds the kLastBlocks partials into row 0 first
   a.lat_table = lat_table;
   a.scene_ids = scene_ids;
   a.lat_grad = lat_grad;
@@ -195,6 +195,7 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
     DSDF_REQUIRE(pgrads->v[l] && pgrads->b[l], "missing gradient pointers");
     if ((desc->weight_norm_mask >> l) & 1) DSDF_REQUIRE(pgrads->g[l] && params->g[l], "missing g pointers");
   }
+  last_reduce_kernel<<<(FH + 1 + 31) / 32, 256, 0, st>>>(bufs->last_part, kLastBlocks);
   scene_sums_kernel<<<dim3(n_scenes, a.n_slots), FH, 0, st>>>(a.tile_part, tile_scene, a.n_tiles, a.n_slots, a.scene_sums);
   if (lat_grad) {
     DSDF_CHECK_CUDA(cudaMemsetAsync(lat_grad, 0, size_t(n_scenes_total) * desc->latent_size * sizeof(float), st));

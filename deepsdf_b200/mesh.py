@@ -14,16 +14,10 @@ from typing import Optional, Tuple
 import torch
 
 from . import _lib as L
+from .sharding import slab_for_rank  # noqa: F401  (re-exported: callers shard the grid with it)
 from .utils import fused_engine_for
 
 TILE = 128
-
-
-def slab_for_rank(N: int, rank: int, world_size: int) -> Tuple[int, int]:
-    """Contiguous range [i0, i1) of the slowest grid index owned by ``rank`` (sizes differ by at most one)."""
-    base, rem = divmod(N, world_size)
-    i0 = rank * base + min(rank, rem)
-    return i0, i0 + base + (1 if rank < rem else 0)
 
 
 def create_mesh_sdf(decoder, latent_vec: torch.Tensor, N: int = 256, max_batch: int = 1 << 21, with_grad: bool = False,

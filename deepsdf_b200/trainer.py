@@ -29,6 +29,7 @@ import torch
 from . import _lib as L
 from .engine import FusedEngine, TILE
 from .networks.deep_sdf_decoder import Decoder
+from .sharding import allreduce_sum_
 
 
 # ---------------------------------------------------------------------------------------------- LR schedules
@@ -165,9 +166,7 @@ class SceneTrainer:
                                   reg_lambda_eff=lam, n_total=n_total, code_bound=self.code_bound, seed=seed,
                                   row0=row0, PG=self.PG, lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
                                   n_rows=N)
-        if self.world_size > 1:
-            import torch.distributed as dist
-            dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=self.pg)
+        allreduce_sum_(self.flat_g, self.pg, self.world_size)
         scale_dev = None
         if self.grad_clip is not None:                                                  # :541-543 (decoder only)
             eng.clip_coef(self.flat_g, self.grad_clip, self._clip_scratch, self._clip_out)

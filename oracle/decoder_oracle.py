@@ -232,8 +232,10 @@ def train_loss_and_grads(spec: OracleSpec, params: Dict[str, torch.Tensor], lat_
                          scene_of_row: torch.Tensor, xyz: torch.Tensor, sdf_gt: torch.Tensor,
                          clamp_dist: Optional[float], code_reg_lambda: Optional[float], epoch: int,
                          masks: Optional[Dict[int, torch.Tensor]] = None, training: bool = True,
-                         code_bound: Optional[float] = None):
+                         code_bound: Optional[float] = None, n_total: Optional[int] = None):
     """One optimiser-step's loss and gradients (batch_split = 1), train_deep_sdf.py:483-533.
+    ``n_total`` overrides the loss normaliser (the whole batch's row count, :485,519) when the rows given are one
+    shard of a larger batch - the same role it plays under ``batch_split``.
 
     Returns (loss, {param name: grad}, lat_grad[S_total, L] dense, pred_sdf_raw[N,1]).
     ``lat_table`` is modified in place by the max_norm renorm exactly like the reference.
@@ -241,7 +243,7 @@ def train_loss_and_grads(spec: OracleSpec, params: Dict[str, torch.Tensor], lat_
     embedding_renorm_(lat_table, scene_of_row, code_bound)                  # :509 (lookup side effect)
     P = {k: v.detach().clone().requires_grad_(True) for k, v in params.items()}
     Z = lat_table.detach().clone().requires_grad_(True)
-    n_total = xyz.shape[0]                                                # :485
+    n_total = xyz.shape[0] if n_total is None else n_total                # :485
     gt = sdf_gt.reshape(-1, 1)
     if clamp_dist is not None:                                            # :492-493
         gt = torch.clamp(gt, -clamp_dist, clamp_dist)
