@@ -33,8 +33,9 @@ constexpr int B_SMEM = B_OFF_XYZ + 3 * TILE_M * 4 + 1024;
 __device__ __forceinline__ void bwd_bar() { asm volatile("bar.sync 1, %0;" ::"n"(B_EPI_THREADS) : "memory"); }
 
 // 16 columns [c0, c0+16) of one row: v = accumulators (or dy * w_last), gated and scaled, packed to bf16 into the A tile
-__device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float dyv, const float* swl, uint32_t gate16, float scale,
-                                           uint8_t* sA, uint32_t row, uint32_t c0) {
+__device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float dyv, uint32_t swl, uint32_t gate16, float scale,
+                                           uint32_t sA, uint32_t row, uint32_t c0) {
+  // swl / sA: SHARED-space byte addresses (explicit ld/st.shared: no generic-address descriptors in the hot loop)
   float v[16];
   if (has_acc) {
     uint32_t r[16];
@@ -45,19 +46,19 @@ __device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float d
   } else {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float4 w = *reinterpret_cast<const float4*>(swl + 4 * k);
+      const float4 w = lds_f32x4(swl + 16 * k);
       const float d = dyv * scale;
       v[4 * k + 0] = d * w.x; v[4 * k + 1] = d * w.y; v[4 * k + 2] = d * w.z; v[4 * k + 3] = d * w.w;
     }
   }
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = (gate16 & (1u << i)) ? v[i] : 0.0f;
-  uint8_t* base = sA + (c0 >> 6) * A_CHUNK_BYTES + row * 128u;
+  const uint32_t base = sA + (c0 >> 6) * A_CHUNK_BYTES + row * 128u;
   const uint32_t piece0 = (c0 & 63u) >> 3;
-  *reinterpret_cast<uint4*>(base + ((piece0 ^ (row & 7u)) << 4)) =
-      make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-  *reinterpret_cast<uint4*>(base + (((piece0 + 1) ^ (row & 7u)) << 4)) =
-      make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+  sts_u32x4(base + ((piece0 ^ (row & 7u)) << 4), pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+            pack_bf16x2(v[6], v[7]));
+  sts_u32x4(base + (((piece0 + 1) ^ (row & 7u)) << 4), pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]),
+            pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
 }
 
 }  // namespace
@@ -234,6 +235,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const uint32_t tmem_row = tmem_base + (uint32_t(q * 32) << 16);
     const uint32_t ready_leader = mapa_u32(smem_u32(&bar_a_ready[0]), 0);
     s_wlast[tid] = __ldg(args.w_last + tid);
+    const uint32_t swl_a = smem_u32(s_wlast), sA_a = smem_u32(sA);
     uint32_t mma_iter = 0;
     uint32_t wpar = 0, wany = 0;        // per quarter: parity of / any hand-overs so far
     const int tiles_alloc = int(args.n_rows_pad / TILE_M);
@@ -272,8 +274,8 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
           // the previous dY tile's quarter must have been stashed and column-summed before it is overwritten
           if ((wany >> Q) & 1u) mbar_wait(&bar_q_released[Q], ((wpar >> Q) & 1u) ^ 1u);
-          bwd_pass16(tmem_row + c0, has_acc, dyv, s_wlast + c0, gate, scale, sA, rt, c0);
-          bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, s_wlast + c0 + 16, gate >> 16, scale, sA, rt, c0 + 16);
+          bwd_pass16(tmem_row + c0, has_acc, dyv, swl_a + c0 * 4, gate, scale, sA_a, rt, c0);
+          bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, swl_a + (c0 + 16) * 4, gate >> 16, scale, sA_a, rt, c0 + 16);
           fence_proxy_async_smem();
           tc_fence_before();
           __syncwarp();

@@ -46,9 +46,10 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"
 //   keep16   low 16 bits: Philox keep bits of these columns (all ones when the layer has no dropout)
 // Returns the 16 gate bits (relu AND keep); adds this row's share of the last-layer dot product to ydot.
 template <bool kTrain>
-__device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, float ascale, const float* sb, const float* swx,
-                                               float x, float y, float z, uint32_t keep16, const float* swl, uint8_t* sA,
+__device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, float ascale, uint32_t sb, bool has_xyz, uint32_t swx,
+                                               float x, float y, float z, uint32_t keep16, bool is_last, uint32_t swl, uint32_t sA,
                                                uint32_t row, uint32_t c0, float& ydot) {
+  // sb / swx / swl / sA are SHARED-space byte addresses (of this pass's first column where they are per column)
   float v[16];
   if (has_acc) {
     uint32_t r[16];
@@ -56,7 +57,7 @@ __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, flo
     tmem_ld_wait();
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float4 b = *reinterpret_cast<const float4*>(sb + 4 * k);
+      const float4 b = lds_f32x4(sb + 16 * k);
       v[4 * k + 0] = fmaf(__uint_as_float(r[4 * k + 0]), ascale, b.x);
       v[4 * k + 1] = fmaf(__uint_as_float(r[4 * k + 1]), ascale, b.y);
       v[4 * k + 2] = fmaf(__uint_as_float(r[4 * k + 2]), ascale, b.z);
@@ -65,16 +66,16 @@ __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, flo
   } else {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float4 b = *reinterpret_cast<const float4*>(sb + 4 * k);
+      const float4 b = lds_f32x4(sb + 16 * k);
       v[4 * k + 0] = b.x; v[4 * k + 1] = b.y; v[4 * k + 2] = b.z; v[4 * k + 3] = b.w;
     }
   }
-  if (swx != nullptr) {
+  if (has_xyz) {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float4 wx = *reinterpret_cast<const float4*>(swx + 4 * k);
-      const float4 wy = *reinterpret_cast<const float4*>(swx + FH + 4 * k);
-      const float4 wz = *reinterpret_cast<const float4*>(swx + 2 * FH + 4 * k);
+      const float4 wx = lds_f32x4(swx + 16 * k);
+      const float4 wy = lds_f32x4(swx + FH * 4 + 16 * k);
+      const float4 wz = lds_f32x4(swx + 2 * FH * 4 + 16 * k);
       v[4 * k + 0] += x * wx.x + y * wy.x + z * wz.x;
       v[4 * k + 1] += x * wx.y + y * wy.y + z * wz.y;
       v[4 * k + 2] += x * wx.z + y * wy.z + z * wz.z;
@@ -93,19 +94,19 @@ __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, flo
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.0f);
   }
-  if (swl != nullptr) {
+  if (is_last) {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float4 w = *reinterpret_cast<const float4*>(swl + 4 * k);
+      const float4 w = lds_f32x4(swl + 16 * k);
       ydot += v[4 * k + 0] * w.x + v[4 * k + 1] * w.y + v[4 * k + 2] * w.z + v[4 * k + 3] * w.w;
     }
   }
-  uint8_t* base = sA + (c0 >> 6) * A_CHUNK_BYTES + row * 128u;
+  const uint32_t base = sA + (c0 >> 6) * A_CHUNK_BYTES + row * 128u;
   const uint32_t piece0 = (c0 & 63u) >> 3;
-  *reinterpret_cast<uint4*>(base + ((piece0 ^ (row & 7u)) << 4)) =
-      make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-  *reinterpret_cast<uint4*>(base + (((piece0 + 1) ^ (row & 7u)) << 4)) =
-      make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+  sts_u32x4(base + ((piece0 ^ (row & 7u)) << 4), pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+            pack_bf16x2(v[6], v[7]));
+  sts_u32x4(base + (((piece0 + 1) ^ (row & 7u)) << 4), pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]),
+            pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
   return gate;
 }
 
@@ -328,7 +329,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         const bool drop = kTrain && L.dropout != 0 && args.dropout_on != 0;
         const bool has_acc = L.has_mma != 0;
         const float ascale = drop ? args.drop_scale : 1.0f;
-        const float* sb = s_bias + (l & 1) * FH;
+        const uint32_t sb = smem_u32(s_bias) + uint32_t(l & 1) * FH * 4;
         // ---- before the accumulators are ready: stage this layer's bias (+ xyz weights), draw the first keep words
         {
           const float* src = (L.bias_slot >= 0) ? (args.cbias + (size_t(scene) * 2 + L.bias_slot) * FH) : args.bias[l];
@@ -343,12 +344,12 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         const uint64_t grow = args.row0 + uint64_t(int64_t(tile_c) * TILE_M + rt);
         uint32_t kwa = 0xFFFFFFFFu, kwb = 0xFFFFFFFFu;
         if (drop) {
-          kwa = dropout_keep_word(args.seed, uint32_t(l), grow, uint32_t(j), args.drop_thr);
-          kwb = dropout_keep_word(args.seed, uint32_t(l), grow, uint32_t(4 + j), args.drop_thr);
+          kwa = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(j), args.drop_thr);
+          kwb = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(4 + j), args.drop_thr);
         }
         epi_bar();
-        const float* swx = L.has_xyz ? s_wxyz : nullptr;
-        const float* swl = last ? s_wlast : nullptr;
+        const bool has_xyz = L.has_xyz != 0;
+        const uint32_t swx = smem_u32(s_wxyz), swl = smem_u32(s_wlast), sA_a = smem_u32(sA);
         uint32_t par = 0;
         if (has_acc) { par = mma_iter & 1; ++mma_iter; }
         uint32_t* gdst = nullptr;
@@ -360,10 +361,10 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
           // the previous layer's stash of this quarter must have been read out of the tile
           if (stash && ((wany >> Q) & 1u)) mbar_wait(&bar_q_stashed[Q], ((wpar >> Q) & 1u) ^ 1u);
-          const uint32_t g0 = epi_pass16<kTrain>(tmem_row + c0, has_acc, ascale, sb + c0, swx ? swx + c0 : nullptr, px, py, pz, keep,
-                                                 swl ? swl + c0 : nullptr, sA, rt, c0, ydot);
-          const uint32_t g1 = epi_pass16<kTrain>(tmem_row + c0 + 16, has_acc, ascale, sb + c0 + 16, swx ? swx + c0 + 16 : nullptr, px, py,
-                                                 pz, keep >> 16, swl ? swl + c0 + 16 : nullptr, sA, rt, c0 + 16, ydot);
+          const uint32_t g0 = epi_pass16<kTrain>(tmem_row + c0, has_acc, ascale, sb + c0 * 4, has_xyz, swx + c0 * 4, px, py, pz, keep,
+                                                 last, swl + c0 * 4, sA_a, rt, c0, ydot);
+          const uint32_t g1 = epi_pass16<kTrain>(tmem_row + c0 + 16, has_acc, ascale, sb + (c0 + 16) * 4, has_xyz, swx + (c0 + 16) * 4,
+                                                 px, py, pz, keep >> 16, last, swl + (c0 + 16) * 4, sA_a, rt, c0 + 16, ydot);
           if (kTrain && gdst != nullptr) gdst[size_t(Q) * 4 * TILE_M] = g0 | (g1 << 16);
           fence_proxy_async_smem();
           tc_fence_before();
@@ -384,8 +385,8 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         quarter(1, kwb);
         // ---- half 1: after all of this layer's MMAs; the next layer starts on the K chunks that are already there
         if (drop && L.n_halves == 2) {
-          kwa = dropout_keep_word(args.seed, uint32_t(l), grow, uint32_t(8 + j), args.drop_thr);
-          kwb = dropout_keep_word(args.seed, uint32_t(l), grow, uint32_t(12 + j), args.drop_thr);
+          kwa = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(8 + j), args.drop_thr);
+          kwb = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(12 + j), args.drop_thr);
         }
         if (has_acc) { mbar_wait(&bar_tmem_full[1], par); tc_fence_after(); }
         if (L.n_halves == 2) {

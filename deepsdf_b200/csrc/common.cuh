@@ -39,6 +39,18 @@ __device__ __forceinline__ float lds_f32(uint32_t addr) {
   return v;
 }
 
+// explicit shared-space vector accesses with 32-bit addresses: a generic `*reinterpret_cast<float4*>(p)` on a pointer the
+// compiler cannot prove to be shared becomes LD.E/ST.E with a 64-bit address and a memory descriptor that costs two R2UR
+// per access in the epilogues' hot loops
+__device__ __forceinline__ float4 lds_f32x4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u32x4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
 // ------------------------------------------------------------------ mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -370,6 +382,38 @@ __host__ __device__ __forceinline__ Philox4 philox4x32(uint32_t c0, uint32_t c1,
     k0 += W0; k1 += W1;
   }
   return Philox4{c0, c1, c2, c3};
+}
+// Same function with the round keys k + r*W precomputed (kernel parameters live in the constant bank, so the key
+// schedule costs no instructions): rk[2r] = k0 + r*W0, rk[2r+1] = k1 + r*W1.
+__host__ __device__ __forceinline__ void philox_round_keys(uint64_t seed, uint32_t* rk) {
+  uint32_t k0 = uint32_t(seed), k1 = uint32_t(seed >> 32);
+  for (int r = 0; r < kPhiloxRounds; ++r) { rk[2 * r] = k0; rk[2 * r + 1] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+}
+__device__ __forceinline__ Philox4 philox4x32_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const uint32_t* rk) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+#pragma unroll
+  for (int r = 0; r < kPhiloxRounds; ++r) {
+    uint64_t p0 = uint64_t(M0) * c0;
+    uint64_t p1 = uint64_t(M1) * c2;
+    uint32_t n0 = uint32_t(p1 >> 32) ^ c1 ^ rk[2 * r];
+    uint32_t n1 = uint32_t(p1);
+    uint32_t n2 = uint32_t(p0 >> 32) ^ c3 ^ rk[2 * r + 1];
+    uint32_t n3 = uint32_t(p0);
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+  }
+  return Philox4{c0, c1, c2, c3};
+}
+__device__ __forceinline__ uint32_t dropout_keep_word_rk(const uint32_t* rk, uint32_t layer, uint64_t row, uint32_t g32, uint32_t thr) {
+  const Philox4 a = philox4x32_rk(uint32_t(row), uint32_t(row >> 32), layer, 2u * g32, rk);
+  const Philox4 b = philox4x32_rk(uint32_t(row), uint32_t(row >> 32), layer, 2u * g32 + 1u, rk);
+  const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  uint32_t lt = 0u, eq = 0xFFFFFFFFu;
+#pragma unroll
+  for (int bit = 7; bit >= 0; --bit) {
+    if ((thr >> bit) & 1u) { lt |= eq & ~w[bit]; eq &= w[bit]; }
+    else { eq &= ~w[bit]; }
+  }
+  return ~lt;
 }
 __host__ __device__ __forceinline__ uint32_t dropout_threshold(float p) {
   int t = int(p * 256.0f + 0.5f);

@@ -63,6 +63,7 @@ struct FwdArgs {
   int32_t dropout_on;                       // 0: gates mode without dropout (eval-mode forward that still records relu gates)
   int32_t dy_unit;                          // gt == null: dy_out = d sdf / d(pre-tanh output)  (input-gradient path)
   const int32_t* tile_rows;                 // [n_tiles] valid rows of each tile (ragged scenes padded to 128), or null
+  uint32_t philox_rk[16];                   // Philox round keys of `seed` (common.cuh philox_round_keys)
 };
 
 struct BwdArgs {

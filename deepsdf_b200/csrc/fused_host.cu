@@ -294,6 +294,7 @@ extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, c
   a.drop_thr = dropout_threshold(desc->dropout_prob);
   a.drop_scale = 1.0f / (1.0f - desc->dropout_prob);   // F.dropout scaling with the nominal p
   a.seed = tr->seed;
+  philox_round_keys(tr->seed, a.philox_rk);
   a.row0 = tr->row0;
   a.gt = tr->gt;
   a.clamp = tr->clamp;
