@@ -433,6 +433,11 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the grid / latent-optimisation secondary metrics")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: libraries that print to fd 1 (NCCL's version banner) go to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     if args.impl == "reference":
         run_reference(args)
     else:

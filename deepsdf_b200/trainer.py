@@ -29,7 +29,6 @@ import torch
 from . import _lib as L
 from .engine import FusedEngine, TILE
 from .networks.deep_sdf_decoder import Decoder
-from .sharding import allreduce_sum_
 
 
 # ---------------------------------------------------------------------------------------------- LR schedules
@@ -166,14 +165,20 @@ class SceneTrainer:
                                   reg_lambda_eff=lam, n_total=n_total, code_bound=self.code_bound, seed=seed,
                                   row0=row0, PG=self.PG, lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
                                   n_rows=N)
-        allreduce_sum_(self.flat_g, self.pg, self.world_size)
+        # the decoder-gradient all-reduce (NCCL, its own stream) overlaps the latent Adam, which needs no exchange
+        work = None
+        if self.world_size > 1:
+            import torch.distributed as dist
+            work = dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+        lr_dec, lr_lat = self.learning_rates(epoch)
+        eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat)
+        if work is not None:
+            work.wait()
         scale_dev = None
         if self.grad_clip is not None:                                                  # :541-543 (decoder only)
             eng.clip_coef(self.flat_g, self.grad_clip, self._clip_scratch, self._clip_out)
             scale_dev = self._clip_out[1:2]
-        lr_dec, lr_lat = self.learning_rates(epoch)
         eng.adam(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.step_count, lr_dec, scale_dev=scale_dev)
-        eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat)
         eng.repack()
         return loss
 
