@@ -187,3 +187,42 @@ def test_chunked_recompute_path(monkeypatch):
     yo.sum().backward()
     for k, p in mod.named_parameters():
         assert (p.grad.cpu() - P[k].grad).abs().max().item() <= 1e-6 + 2e-4 * P[k].grad.abs().max().item(), k
+
+
+def test_dropin_decoder_in_reference_loop_reproduces_main_function_fixture():
+    """BASELINE.json config #1 (scaled down): the drop-in Decoder used exactly as train_deep_sdf.py:346-545 uses the
+    reference class (DataParallel wrapper, nn.Embedding(max_norm) on the CPU, L1Loss(sum)/N, code regulariser,
+    torch.optim.Adam over both groups) replays the losses and final parameters that the REAL main_function produced
+    (tests/golden/train_epochs.npz, written by oracle/make_golden_epoch.py)."""
+    from tests.test_oracle_golden import load_train_epochs
+    z, specs, kw, init, final = load_train_epochs()
+    decoder = torch.nn.DataParallel(build_module(kw, init, DEV))                       # :346-353
+    lat_vecs = torch.nn.Embedding(6, specs["CodeLength"], max_norm=specs["CodeBound"])  # :385
+    with torch.no_grad():
+        lat_vecs.weight.copy_(torch.from_numpy(z["lat_init"]))
+    loss_l1 = torch.nn.L1Loss(reduction="sum")                                         # :398
+    sched = specs["LearningRateSchedule"]
+    opt = torch.optim.Adam([{"params": decoder.parameters(), "lr": sched[0]["Initial"]},
+                            {"params": lat_vecs.parameters(), "lr": sched[1]["Initial"]}])
+    sps, ipe, clampd = specs["SamplesPerScene"], int(z["its_per_epoch"]), specs["ClampingDistance"]
+    decoder.train()
+    for it in range(len(z["loss"])):
+        epoch = it // ipe + 1
+        sdf_data = torch.from_numpy(z["batches"][it])
+        n = sdf_data.shape[0]
+        xyz, sdf_gt = sdf_data[:, 0:3], torch.clamp(sdf_data[:, 3].unsqueeze(1), -clampd, clampd)
+        indices = torch.from_numpy(z["indices"][it]).unsqueeze(-1).repeat(1, sps).view(-1)
+        opt.zero_grad()
+        batch_vecs = lat_vecs(indices)
+        pred = torch.clamp(decoder(torch.cat([batch_vecs, xyz], dim=1)), -clampd, clampd)     # CPU tensor in, like :511-514
+        loss = loss_l1(pred, sdf_gt.to(DEV)) / n
+        reg = specs["CodeRegularizationLambda"] * min(1, epoch / 100) * torch.sum(torch.norm(batch_vecs, dim=1)) / n
+        loss = loss + reg.to(DEV)
+        loss.backward()
+        opt.step()
+        ref = float(z["loss"][it])
+        assert abs(loss.item() - ref) <= 1e-5 * abs(ref), (it, loss.item(), ref)
+    sd = decoder.module.state_dict()
+    for k, v in final.items():
+        assert torch.allclose(sd[k].cpu(), v, rtol=1e-4, atol=5e-6), k
+    assert torch.allclose(lat_vecs.weight.detach(), torch.from_numpy(z["lat_final"]), rtol=1e-4, atol=5e-6)

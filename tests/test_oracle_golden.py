@@ -102,3 +102,45 @@ def test_analytic_sdfs():
     assert s.shape == (3, 1) and abs(s[0, 0] - (-0.9)) < 1e-12 and s[1, 0] > 0
     c = O.cross_ms_sdf(x, 0.3)
     assert abs(c[0, 0] - (-0.3)) < 1e-12
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# BASELINE.json config #1 (scaled down): two epochs of the REAL train_deep_sdf.main_function, recorded by
+# oracle/make_golden_epoch.py -> tests/golden/train_epochs.npz.  The oracle's training loop must reproduce it.
+def load_train_epochs():
+    import json
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "train_epochs.npz"))
+    specs = json.loads(str(z["specs_json"]))
+    kw = dict(latent_size=specs["CodeLength"], **specs["NetworkSpecs"])
+    init = {k[len("init::"):]: torch.from_numpy(z[k]) for k in z.files if k.startswith("init::")}
+    final = {k[len("final::"):]: torch.from_numpy(z[k]) for k in z.files if k.startswith("final::")}
+    return z, specs, kw, init, final
+
+
+def test_oracle_training_loop_reproduces_reference_main_function():
+    z, specs, kw, init, final = load_train_epochs()
+    spec = O.OracleSpec(**kw)
+    assert list(init) == spec.param_names()                     # the reference's own parameter names and order
+    P = {k: v.clone() for k, v in init.items()}
+    m1 = {k: torch.zeros_like(v) for k, v in P.items()}
+    m2 = {k: torch.zeros_like(v) for k, v in P.items()}
+    Z = torch.from_numpy(z["lat_init"]).clone()
+    zm, zv = torch.zeros_like(Z), torch.zeros_like(Z)
+    sps, ipe = specs["SamplesPerScene"], int(z["its_per_epoch"])
+    sched = specs["LearningRateSchedule"]
+    for it in range(len(z["loss"])):
+        epoch = it // ipe + 1
+        batch = torch.from_numpy(z["batches"][it])
+        row_scene = torch.from_numpy(z["indices"][it]).repeat_interleave(sps)
+        loss, grads, zgrad, _ = O.train_loss_and_grads(spec, P, Z, row_scene, batch[:, :3], batch[:, 3], specs["ClampingDistance"],
+                                                       specs["CodeRegularizationLambda"], epoch, training=True,
+                                                       code_bound=specs["CodeBound"])
+        assert abs(loss - float(z["loss"][it])) <= 2e-6 * abs(float(z["loss"][it])), (it, loss, float(z["loss"][it]))
+        lr_d = O.step_lr(sched[0]["Initial"], sched[0]["Interval"], sched[0]["Factor"], epoch)
+        lr_z = O.step_lr(sched[1]["Initial"], sched[1]["Interval"], sched[1]["Factor"], epoch)
+        for k in P:
+            O.adam_step_(P[k], grads[k], m1[k], m2[k], it + 1, lr_d)
+        O.adam_step_(Z, zgrad, zm, zv, it + 1, lr_z)
+    for k in P:
+        assert torch.allclose(P[k], final[k], rtol=1e-5, atol=2e-6), k
+    assert torch.allclose(Z, torch.from_numpy(z["lat_final"]), rtol=1e-5, atol=2e-6)
