@@ -89,9 +89,11 @@ struct BwdArgs {
 // 128-feature output blocks of the layer share every activation box through TMA multicast).  The plan depends only on
 // the network and the row count - never on the device - so the split-K summation order, and with it every gradient
 // bit, is reproducible.
-constexpr int WG_CLUSTERS = 32;      // 32 clusters x 4 CTAs = 128 SMs: a 4-CTA cluster must sit inside one GPC, and the
-                                     // B200's GPCs (18-20 SMs) leave SMs over; wgrad is HBM-bound, 128 SMs saturate it
-constexpr int WG_MAX_SEGS = 64;
+constexpr int WG_CLUSTERS = 33;      // 33 clusters x 4 CTAs = 132 SMs: a 4-CTA cluster must sit inside one GPC, and the
+                                     // B200's GPCs leave SMs over (cudaOccupancyMaxActiveClusters = 33); a constant, so that
+                                     // the split-K order never depends on the device
+constexpr int WG_MAX_CLUSTERS = 40;
+constexpr int WG_MAX_SEGS = 128;
 struct WgradSeg {
   int32_t layer;        // hidden layer l: dW_l = dY_l^T . X_{l-1}
   int32_t n;            // input features covered (256 or 512)
@@ -101,7 +103,8 @@ struct WgradSeg {
 };
 struct WgradPlan {
   int32_t n_segs;
-  int32_t cluster_seg0[WG_CLUSTERS + 1];       // segments of cluster c: [cluster_seg0[c], cluster_seg0[c+1])
+  int32_t n_clusters;                          // clusters launched (WG_CLUSTERS; other values only for experiments)
+  int32_t cluster_seg0[WG_MAX_CLUSTERS + 1];   // segments of cluster c: [cluster_seg0[c], cluster_seg0[c+1])
   int32_t layer_seg0[DSDF_MAX_LAYERS + 1];     // segments of layer l:   [layer_seg0[l], layer_seg0[l+1])
   WgradSeg seg[WG_MAX_SEGS];
   int64_t total_floats;

@@ -15,24 +15,30 @@ namespace {
 
 constexpr int kLastBlocks = 1184;   // fixed (not device dependent): 8 x 148
 
-// Cut the (layer, 32-row step) space into WG_CLUSTERS contiguous pieces of equal tensor-core cost (a 512-wide layer costs
-// two units per step, a 256-wide one a single unit).  A cluster gets one piece = at most a few segments.
+// Cut the (layer, 32-row step) space into WG_CLUSTERS contiguous pieces of equal cost.  A cluster gets one piece = at most
+// a few segments.
 int build_plan(const dsdf_net_desc* d, const FusedLayout& lo, int64_t n_rows, WgradPlan* p) {
   memset(p, 0, sizeof(*p));
   (void)d;
   const int64_t n_steps = n_rows / 32;
   int64_t total = 0;
-  for (int l = 1; l < lo.num_hidden; ++l) total += n_steps * lo.bwd_halves[l];
-  const int64_t share = (total + WG_CLUSTERS - 1) / WG_CLUSTERS;
+  // Cost model: wgrad runs at the HBM roofline and a step's time is set by its load latency, not by its bytes or MMAs, so
+  // a 32-row step of a 256-wide layer costs the SAME as one of a 512-wide layer.  (Weighting it by its tensor work, 1:2,
+  // gave the clusters that own the narrow layer twice the steps: measured 4.0 ms instead of 2.4 ms for the kernel.)
+  auto cost = [&](int) { return 1; };
+  for (int l = 1; l < lo.num_hidden; ++l) total += n_steps * cost(l);
+  const int ncl = WG_CLUSTERS;
+  p->n_clusters = ncl;
+  const int64_t share = (total + ncl - 1) / ncl;
   int l = 1, nseg = 0;
   int64_t step = 0, off = 0;
   for (int l2 = 0; l2 <= DSDF_MAX_LAYERS; ++l2) p->layer_seg0[l2] = -1;
-  for (int c = 0; c < WG_CLUSTERS; ++c) {
+  for (int c = 0; c < ncl; ++c) {
     p->cluster_seg0[c] = nseg;
     int64_t remaining = share;
     while (remaining > 0 && l < lo.num_hidden) {
-      const int u = lo.bwd_halves[l];
-      int64_t take = (remaining + u - 1) / u;
+      const int u = lo.bwd_halves[l], cu = cost(l);
+      int64_t take = (remaining + cu - 1) / cu;
       if (take > n_steps - step) take = n_steps - step;
       if (take > 0) {
         if (nseg >= WG_MAX_SEGS) return set_error("too many wgrad segments");
@@ -43,12 +49,12 @@ int build_plan(const dsdf_net_desc* d, const FusedLayout& lo, int64_t n_rows, Wg
         if (p->layer_seg0[l] < 0) p->layer_seg0[l] = nseg;
         ++nseg;
         step += take;
-        remaining -= take * u;
+        remaining -= take * cu;
       }
       if (step >= n_steps) { ++l; step = 0; }
     }
   }
-  p->cluster_seg0[WG_CLUSTERS] = nseg;
+  p->cluster_seg0[ncl] = nseg;
   p->n_segs = nseg;
   // close the per-layer ranges: layer_seg0[l+1] = first segment of the next layer that has one (or n_segs)
   int next = nseg;

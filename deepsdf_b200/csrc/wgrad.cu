@@ -26,7 +26,7 @@ namespace {
 constexpr int WG_ROWS = 32;                       // rows (K) per pipeline stage
 constexpr int WG_BOX_BYTES = WG_ROWS * 128;       // one {64 x 32} bf16 box = 4 KB
 constexpr int WG_STAGE_BYTES = 6 * WG_BOX_BYTES;  // A: 2 boxes (128 out features), B: 2 boxes per 256-wide N block (this CTA's half)
-constexpr int WG_STAGES = 8;
+constexpr int WG_STAGES = 9;
 constexpr int WG_THREADS = 192;                   // warp 0 TMA, warp 1 MMA (even rank) / relay (odd rank) + TMEM alloc, warps 2..5 epilogue
 constexpr int WG_SMEM = WG_STAGES * WG_STAGE_BYTES + 1024;
 }  // namespace
@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(256) wgrad_last_kernel(const __nv_bfloat16* __
 
 int launch_wgrad(const CUtensorMap& tmDys, const CUtensorMap& tmActs, const WgradArgs& args, cudaStream_t stream) {
   DSDF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
-  wgrad_kernel<<<4 * WG_CLUSTERS, WG_THREADS, WG_SMEM, stream>>>(tmDys, tmActs, args);
+  wgrad_kernel<<<4 * args.plan.n_clusters, WG_THREADS, WG_SMEM, stream>>>(tmDys, tmActs, args);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
