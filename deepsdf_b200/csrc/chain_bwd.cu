@@ -22,7 +22,9 @@ namespace {
 
 constexpr int B_EPI_WARPS = 16;
 constexpr int B_EPI_THREADS = B_EPI_WARPS * 32;
-constexpr int B_THREADS = (B_EPI_WARPS + 3) * 32;   // + TMA warp + MMA warp + stash warp
+constexpr int B_THREADS = (B_EPI_WARPS + 4) * 32;   // + TMA warp + MMA warp + stash warp + one idle warp (completes the service
+                                                    //   warpgroup: setmaxnreg works on whole warpgroups)
+constexpr int B_EPI_REGS = 112, B_SVC_REGS = 24;    // register re-split: 16 x 112 + 4 x 24 <= 20 x 96 per thread-slot
 constexpr int B_STAGES = 5;
 constexpr int B_STAGE_BYTES = 128 * 128;
 constexpr int B_OFF_B = A_BYTES;
@@ -103,7 +105,10 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   const int n_pairs = (args.n_tiles + 1) >> 1;
   const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
 
+  // Register re-split (each role issues its own setmaxnreg first): 96 registers per thread at launch (20 warps); the four
+  // single-lane service warps keep 24, the sixteen epilogue warps get 112.
   if (warp == B_EPI_WARPS) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(B_SVC_REGS));
     // ================================================================ TMA producer (this CTA's half of every W^T block)
     const uint32_t full_leader = mapa_u32(smem_u32(&bar_full[0]), 0);
     const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]), sB_u = smem_u32(sB);
@@ -125,6 +130,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       }
     }
   } else if (warp == B_EPI_WARPS + 1) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(B_SVC_REGS));
     // ================================================================ MMA issuer (leader CTA; whole warp, elected issue)
     if (leader) {
       const uint32_t idesc = umma_idesc_bf16(2 * TILE_M, HALF_N, 0, 0);
@@ -185,7 +191,10 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         }
       }
     }
+  } else if (warp == B_EPI_WARPS + 3) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(B_SVC_REGS));      // idle warp: completes the service warpgroup
   } else if (warp == B_EPI_WARPS + 2) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(B_SVC_REGS));
     // ================================================================ stash warp: TMA-store every completed quarter of
     // dY_t (t > 0) for wgrad and release it once the store has read the shared memory (one store kept in flight)
     const uint32_t wr0 = smem_u32(&bar_q_written[0]), rl0 = smem_u32(&bar_q_released[0]), sA_u = smem_u32(sA);
@@ -227,6 +236,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     }
     __syncwarp();
   } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(B_EPI_REGS));
     // ================================================================ epilogue warps (both CTAs)
     const int q = warp & 3;
     const int j = warp >> 2;

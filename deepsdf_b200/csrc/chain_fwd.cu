@@ -28,7 +28,9 @@ namespace {
 
 constexpr int P_EPI_WARPS = 16;
 constexpr int P_EPI_THREADS = P_EPI_WARPS * 32;        // 512
-constexpr int P_THREADS = (P_EPI_WARPS + 3) * 32;      // + TMA warp + MMA warp + stash warp
+constexpr int P_THREADS = (P_EPI_WARPS + 4) * 32;      // + TMA warp + MMA warp + stash warp + one idle warp that completes the
+                                                       //   service warpgroup (setmaxnreg works on whole warpgroups)
+constexpr int P_EPI_REGS = 112, P_SVC_REGS = 24;       // register re-split: 16 x 112 + 4 x 24 <= 20 x 96 per thread-slot
 constexpr int P_STAGES = 5;
 constexpr int P_STAGE_BYTES = 128 * 128;               // this CTA's half ([128 out rows][64 K] bf16) of a weight block
 constexpr int P_OFF_B = A_BYTES;
@@ -154,7 +156,10 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   const int n_pairs = (args.n_tiles + 1) >> 1;
   const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
 
+  // Register re-split (each role issues its own setmaxnreg first): the kernel launches with 96 registers per thread (20
+  // warps), the four single-lane service warps keep 24, the sixteen epilogue warps get 112.
   if (warp == P_EPI_WARPS) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(P_SVC_REGS));
     // ================================================================ TMA producer (this CTA's half of every weight block)
     {
       // the whole warp walks the loop (warp-uniform values stay in uniform registers); one elected lane issues
@@ -180,6 +185,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       }
     }
   } else if (warp == P_EPI_WARPS + 1) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(P_SVC_REGS));
     // ================================================================ MMA issuer (leader CTA).  The whole warp walks the
     // loop so that every operand is warp-uniform (uniform registers feed UTCHMMA directly; issuing from a divergent
     // `lane == 0` branch makes the compiler wrap each MMA in an ELECT / R2UR waterfall that costs more than the 128
@@ -249,7 +255,10 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         }
       }
     }
+  } else if (warp == P_EPI_WARPS + 3) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(P_SVC_REGS));      // idle warp: completes the service warpgroup
   } else if (warp == P_EPI_WARPS + 2) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(P_SVC_REGS));
     // ================================================================ stash warp (training): as soon as all 16 epilogue
     // warps have written a 128-column quarter of the activation tile, TMA-store its two 64-column chunks (bf16) for
     // wgrad and tell the epilogue when the store has read the shared memory, so that the quarter may be overwritten by
@@ -295,6 +304,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       __syncwarp();
     }
   } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(P_EPI_REGS));
     // ================================================================ epilogue warps (both CTAs)
     const int q = warp & 3;            // TMEM lane quadrant
     const int j = warp >> 2;           // 32-column slice of every 128-column quarter
