@@ -346,7 +346,7 @@ def run_gpu(args):
         "roofline": roofline,
         "cpu_baseline": cpu,
         "clocks": clk,
-        "grid": extras.get("grid"), "latent_opt": extras.get("latent_opt"), "extras_error": extras.get("error"),
+        "grid": extras.get("grid"), "latent_opt": extras.get("latent_opt"), "sampler": extras.get("sampler"), "extras_error": extras.get("error"),
         "loss_last_step": loss_dev,
         "loss_last_step_e2e": [float(x) for x in last],
     }
@@ -408,6 +408,34 @@ def run_extras(trainer, dev, rank, world, barrier, max_over_ranks):
     eng._bufs, eng._bufs_key = {}, None
     torch.cuda.empty_cache()
 
+    # device-resident dataset + sampler (deep_sdf/data.py:75-110 on the GPU): 64 scenes x 16384 of 100000 stored rows
+    from deepsdf_b200.data import DeviceSDFSamples
+    n_st = 50000
+    arrays = []
+    g2 = torch.Generator(device=dev).manual_seed(3 + rank)
+    for s in range(SCENES_PER_STEP):
+        blk = make_batch(g2, dev, torch.tensor([s]), SCENES_TOTAL)
+        extra = make_batch(g2, dev, torch.tensor([s]), SCENES_TOTAL)
+        rows = torch.cat([blk, extra, make_batch(g2, dev, torch.tensor([s]), SCENES_TOTAL)], 0)[:2 * n_st].cpu().numpy()
+        pos, neg = rows[rows[:, 3] > 0], rows[rows[:, 3] <= 0]
+        arrays.append((pos, neg))
+    try:
+        ds = DeviceSDFSamples(None, None, SAMPLES_PER_SCENE, 3, dev, arrays=arrays)
+        ids_s = torch.arange(SCENES_PER_STEP, device=dev)
+        buf = ds.sample_batch(ids_s, 1)
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(20):
+            ds.sample_batch(ids_s, 2 + i, out=buf)
+        b.record()
+        barrier()
+        ms = max_over_ranks(a.elapsed_time(b)) / 20
+        out["sampler"] = {"ms_per_batch": ms, "rows_per_s": world * buf.shape[0] / (ms / 1e3), "stored_rows_per_gpu": ds.total_rows,
+                          "what": "on-device half-positive/half-negative subsample without replacement of a 64-scene batch"}
+        del ds, buf
+    except Exception as exc:  # noqa: BLE001 - e.g. a scene without enough rows of one sign in the synthetic family
+        out["sampler"] = {"error": repr(exc)[:200]}
     S, ns, M, iters = 1024, 8000, 16384, 10
     gen = torch.Generator(device=dev).manual_seed(11 + rank)
     ids = torch.arange(S) % SCENES_TOTAL

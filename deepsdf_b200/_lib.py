@@ -69,6 +69,8 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_scene_prepare": (C.c_int, [P(NetDesc), vp, vp, vp, i32, f32, vp, vp]),
         "dsdf_fused_forward": (C.c_int, [P(NetDesc), vp, vp, vp, vp, i32, i64, vp, P(TrainIO), vp]),
         "dsdf_grid_points": (C.c_int, [i32, i64, i64, vp, vp]),
+        "dsdf_sample_batch": (C.c_int, [vp, vp, vp, i32, i32, u64, vp, vp]),
+        "dsdf_sample_perm": (u32, [u32, u32, u64, i64, i32]),
         "dsdf_selftest_umma_pair": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp]),
         "dsdf_selftest_umma": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint,
                                          C.c_uint, vp]),

@@ -191,6 +191,21 @@ class SceneTrainer:
         d_i.copy_(scene_ids_host, non_blocking=True)
         return self.step(d_s, d_i, epoch, global_rows=global_rows, row0=row0)
 
+    def train_epoch(self, dataset, epoch: int, scenes_per_batch: Optional[int] = None, generator=None) -> List[torch.Tensor]:
+        """One epoch of train_deep_sdf.py:472-545 from a ``DeviceSDFSamples`` store: shuffled scene batches (drop_last),
+        every batch subsampled on the device (``dsdf_sample_batch``) and stepped.  Returns the per-iteration loss tensors
+        (device, no synchronisation - the reference's ``.item()`` per chunk, :535, is the caller's choice)."""
+        from .data import epoch_batches
+        spb = scenes_per_batch or self.specs["ScenesPerBatch"]
+        losses = []
+        buf = None
+        for it, ids in enumerate(epoch_batches(len(dataset), spb, generator)):
+            ids_d = ids.to(self.device)
+            seed = (self.seed * 0x51ED27 + epoch * 0x10001 + it) & 0x7FFFFFFFFFFFFFFF
+            buf = dataset.sample_batch(ids_d, seed, out=buf)
+            losses.append(self.step(buf, ids_d, epoch).clone())
+        return losses
+
     # ------------------------------------------------------------------ checkpoint surface (train_deep_sdf.py:96-143)
     def latent_state_dict(self) -> Dict[str, torch.Tensor]:
         return {"weight": self.lat_vecs.detach().cpu().clone()}

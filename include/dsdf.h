@@ -18,6 +18,7 @@
  *   dsdf_fused_finish        weight_norm backward, latent grad, code regulariser   train_deep_sdf.py:523-533
  *   dsdf_adam                optimizer_all.step()              train_deep_sdf.py:400-411,545
  *   dsdf_grid_points         create_mesh sample grid           deep_sdf/mesh.py:37-53
+ *   dsdf_sample_batch        SDFSamples.__getitem__ + DataLoader collate      deep_sdf/data.py:75-110,142-194
  *   dsdf_fused_input_grad    autograd.functional.jvp loop      deep_sdf/mesh.py:405-422
  *   dsdf_fused_latent_finish reconstruct.py latent optimisation (upstream; README.md:134-142)
  */
@@ -200,6 +201,18 @@ int dsdf_fused_latent_finish(const dsdf_net_desc* desc, const void* pack, const 
                              const int32_t* tile_scene, int64_t n_rows, const float* lat_table, const int64_t* scene_ids,
                              int32_t n_scenes, float l2reg, float inv_n, float* lat_grad, float* shape_loss,
                              void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Device-resident dataset + sampler (deep_sdf/data.py:75-110 unpack_sdf_samples, :142-194 SDFSamples.__getitem__).
+ *   store [rows][4] fp32 (x, y, z, sdf): per scene its positive rows then its negative rows, NaN rows dropped (remove_nans)
+ *   meta  [n_scenes_total][4] int64: {pos_off, n_pos, neg_off, n_neg} in rows
+ * Writes the scene-major batch [n_scenes * samples_per_scene][4]: per scene `half` positive then `half` negative rows (or
+ * all of the scarcer sign and the rest of the other, data.py:92-99), drawn without replacement by a keyed bijection of
+ * [0, n) (same role as torch.randperm(n)[:take]); rows beyond what the scene can supply are zero. */
+int dsdf_sample_batch(const float* store, const int64_t* meta, const int64_t* scene_ids, int32_t n_scenes,
+                      int32_t samples_per_scene, uint64_t seed, float* batch_out, void* stream);
+/* the bijection itself, on the host: source row of batch position i within the scene's positive / negative rows */
+uint32_t dsdf_sample_perm(uint32_t i, uint32_t n, uint64_t seed, int64_t scene, int32_t negative);
 
 /* torch.optim.Adam update of one flat fp32 tensor (dense, no weight decay); step counts from 1; g is multiplied by
  * grad_scale and, if grad_scale_dev != NULL, by the device scalar *grad_scale_dev first (gradient clipping without a

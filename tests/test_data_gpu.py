@@ -1,0 +1,105 @@
+"""Device-resident dataset + sampler against the semantics of deep_sdf/data.py:61-110: NaN rows
+dropped, half positive then half negative rows per scene, drawn WITHOUT replacement from the right scene, the
+scarce-sign rule, determinism; and an epoch of the fused trainer fed from the store."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from deepsdf_b200 import _lib as L
+from deepsdf_b200.data import DeviceSDFSamples, subsample_counts
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _write_dataset(tmp_path, sizes, dtype=np.float32, nan_every=0):
+    """npz files in the reference's layout; row = (scene, index within file array, 0, +-sdf) so that a sampled row names
+    its own origin."""
+    d = tmp_path / "SdfSamples" / "ds" / "cls"
+    os.makedirs(d)
+    names = []
+    for s, (n_pos, n_neg) in enumerate(sizes):
+        pos = np.stack([np.full(n_pos, s), np.arange(n_pos), np.zeros(n_pos), 0.01 + np.arange(n_pos) * 1e-6], 1).astype(dtype)
+        neg = np.stack([np.full(n_neg, s), np.arange(n_neg), np.ones(n_neg), -0.01 - np.arange(n_neg) * 1e-6], 1).astype(dtype)
+        if nan_every:
+            pos[::nan_every, 3] = np.nan
+        np.savez(d / f"inst{s}.npz", pos=pos, neg=neg)
+        names.append(f"inst{s}")
+    return str(tmp_path), {"ds": {"cls": names}}
+
+
+def test_sampler_semantics(tmp_path):
+    sizes = [(500, 700), (90, 900), (800, 64), (300, 300)]
+    src, split = _write_dataset(tmp_path, sizes, dtype=np.float64, nan_every=7)
+    sps = 256
+    ds = DeviceSDFSamples(src, split, sps, 3, DEV)
+    assert len(ds) == 4
+    n_pos_eff = [n - len(range(0, n, 7)) for n, _ in sizes]             # NaN rows dropped (data.py:61-63)
+    assert ds.meta_host[:, 1].tolist() == n_pos_eff and ds.meta_host[:, 3].tolist() == [m for _, m in sizes]
+    ids = torch.tensor([2, 0, 1, 3], device=DEV)
+    b = ds.sample_batch(ids, seed=99).cpu().numpy().reshape(4, sps, 4)
+    assert not np.isnan(b).any()
+    for slot, scene in enumerate([2, 0, 1, 3]):
+        tp, tn = subsample_counts(n_pos_eff[scene], sizes[scene][1], sps)
+        assert tp + tn == sps
+        rows = b[slot]
+        assert (rows[:, 0] == scene).all()                               # right scene
+        assert (rows[:tp, 3] > 0).all() and (rows[tp:, 3] < 0).all()     # positives first, then negatives (data.py:105)
+        assert len(set(rows[:tp, 1].tolist())) == tp and len(set(rows[tp:, 1].tolist())) == tn    # without replacement
+        assert not (rows[:tp, 1] % 7 == 0).any()                         # the NaN rows (every 7th positive) never appear
+    # scarce-sign rule (data.py:92-97): scene 1 has 77 positives < 128 -> all of them + 179 negatives; scene 2: 64 negatives
+    assert subsample_counts(n_pos_eff[1], 900, sps) == (n_pos_eff[1], sps - n_pos_eff[1])
+    assert subsample_counts(n_pos_eff[2], 64, sps) == (sps - 64, 64)
+    # deterministic in the seed, different across seeds and scenes
+    b2 = ds.sample_batch(ids, seed=99).cpu().numpy().reshape(4, sps, 4)
+    b3 = ds.sample_batch(ids, seed=100).cpu().numpy().reshape(4, sps, 4)
+    assert np.array_equal(b, b2) and not np.array_equal(b, b3)
+    # the kernel's bijection is the exported host function
+    lib = L.lib()
+    tp0, _ = subsample_counts(n_pos_eff[0], 700, sps)
+    kept = [i for i in range(500) if i % 7]
+    want = [kept[lib.dsdf_sample_perm(i, len(kept), 99, 0, 0)] for i in range(tp0)]
+    assert b[1][:tp0, 1].astype(int).tolist() == want
+    # every row is reachable and equally likely: over many seeds the first positive pick covers the set evenly
+    picks = np.array([lib.dsdf_sample_perm(0, 50, s, 3, 0) for s in range(20000)])
+    cnt = np.bincount(picks, minlength=50)
+    assert cnt.min() > 300 and cnt.max() < 500                           # expectation 400
+
+
+def test_not_enough_rows_is_an_error(tmp_path):
+    src, split = _write_dataset(tmp_path, [(10, 20)])
+    with pytest.raises(L.DsdfError):
+        DeviceSDFSamples(src, split, 64, 3, DEV)
+
+
+def test_epoch_from_device_store_trains():
+    from deepsdf_b200.trainer import SceneTrainer
+    from oracle import decoder_oracle as O
+    rng = np.random.RandomState(0)
+    arrays = []
+    for s in range(6):
+        xyz = rng.uniform(-1, 1, (3000, 3)).astype(np.float32)
+        sdf = 0.25 * O.corner_spheres_sdf(xyz, 0.4 + 0.1 * s, limit=0.9).astype(np.float32)
+        rows = np.concatenate([xyz, sdf], 1)
+        arrays.append((rows[rows[:, 3] > 0], rows[rows[:, 3] <= 0]))
+    ds = DeviceSDFSamples(None, None, 1024, 3, DEV, arrays=arrays)
+    specs = {"NetworkSpecs": dict(dims=[512] * 8, dropout=list(range(8)), dropout_prob=0.2, norm_layers=list(range(8)),
+                                  latent_in=[4], weight_norm=True, xyz_in_all=False, use_tanh=False, latent_dropout=False,
+                                  geom_dimension=3),
+             "CodeLength": 16, "LearningRateSchedule": [{"Type": "Step", "Initial": 1e-4, "Interval": 500, "Factor": 0.5},
+                                                        {"Type": "Step", "Initial": 1e-3, "Interval": 500, "Factor": 0.5}],
+             "SamplesPerScene": 1024, "ScenesPerBatch": 3, "ClampingDistance": 0.1, "CodeRegularization": True,
+             "CodeRegularizationLambda": 1e-4, "CodeBound": 1.0}
+    tr = SceneTrainer(specs, 6, DEV, seed=1)
+    g = torch.Generator().manual_seed(0)
+    first = last = None
+    for epoch in range(1, 16):
+        losses = [float(l[0]) for l in tr.train_epoch(ds, epoch, generator=g)]
+        assert len(losses) == 2 and all(np.isfinite(losses))            # 6 scenes / 3 per batch, drop_last
+        first = first if first is not None else np.mean(losses)
+        last = np.mean(losses)
+    print(f"mean epoch loss {first:.5f} -> {last:.5f}")
+    assert last < 0.9 * first

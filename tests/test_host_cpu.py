@@ -69,3 +69,30 @@ def test_reference_export_keys_load():
     params = {k[len("param::"):]: torch.from_numpy(z[k]) for k in z.files if k.startswith("param::")}
     m = build_module(META["small_4x64_L2_tanh"]["spec"], params)
     assert torch.equal(m.lin4.parametrizations.weight.original1, params["lin4.parametrizations.weight.original1"])
+
+
+def test_sampler_host_logic(tmp_path):
+    """deep_sdf/data.py:15-33 file list, :88-99 take counts, and the sampler's row bijection (host copy of the kernel's)."""
+    from deepsdf_b200.data import get_instance_filenames, remove_nans_np, subsample_counts
+    split = {"dsA": {"c1": ["x", "y"], "c2": ["z"]}}
+    os.makedirs(tmp_path / "SdfSamples" / "dsA" / "c1")
+    np.savez(tmp_path / "SdfSamples" / "dsA" / "c1" / "x.npz", pos=np.zeros((1, 4)), neg=np.zeros((1, 4)))
+    assert get_instance_filenames(str(tmp_path), split) == [os.path.join("dsA", "c1", "x.npz"), os.path.join("dsA", "c1", "y.npz"),
+                                                            os.path.join("dsA", "c2", "z.npz")]      # missing files only warn
+    for n_pos, n_neg, sub in [(500, 700, 256), (77, 900, 256), (800, 64, 256), (128, 128, 256), (8000, 9000, 16000)]:
+        half = int(sub / 2)                                      # data.py:88-99 restated
+        if n_pos < half:
+            want = (n_pos, 2 * half - n_pos)
+        elif n_neg < half:
+            want = (2 * half - n_neg, n_neg)
+        else:
+            want = (half, half)
+        assert subsample_counts(n_pos, n_neg, sub) == want
+    rows = np.array([[0, 0, 0, 1.0], [0, 0, 0, np.nan], [1, 1, 1, -2.0]])
+    assert remove_nans_np(rows, 3).tolist() == [[0, 0, 0, 1.0], [1, 1, 1, -2.0]] and remove_nans_np(rows, 3).dtype == np.float32
+    lib = L.lib()
+    lib.dsdf_sample_perm.restype = C.c_uint32
+    lib.dsdf_sample_perm.argtypes = [C.c_uint32, C.c_uint32, C.c_uint64, C.c_int64, C.c_int32]
+    for n in (1, 2, 3, 17, 256, 1000, 65537):
+        assert sorted(lib.dsdf_sample_perm(i, n, 2024, 5, 1) for i in range(n)) == list(range(n))
+    assert [lib.dsdf_sample_perm(i, 1000, 1, 0, 0) for i in range(8)] != [lib.dsdf_sample_perm(i, 1000, 2, 0, 0) for i in range(8)]
