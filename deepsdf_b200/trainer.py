@@ -191,19 +191,23 @@ class SceneTrainer:
         d_i.copy_(scene_ids_host, non_blocking=True)
         return self.step(d_s, d_i, epoch, global_rows=global_rows, row0=row0)
 
-    def train_epoch(self, dataset, epoch: int, scenes_per_batch: Optional[int] = None, generator=None) -> List[torch.Tensor]:
+    def train_epoch(self, dataset, epoch: int, scenes_per_batch: Optional[int] = None, generator=None,
+                    max_iterations: Optional[int] = None, global_rows: Optional[int] = None, row0: int = 0) -> List[torch.Tensor]:
         """One epoch of train_deep_sdf.py:472-545 from a ``DeviceSDFSamples`` store: shuffled scene batches (drop_last),
         every batch subsampled on the device (``dsdf_sample_batch``) and stepped.  Returns the per-iteration loss tensors
-        (device, no synchronisation - the reference's ``.item()`` per chunk, :535, is the caller's choice)."""
+        (device, no synchronisation - the reference's ``.item()`` per chunk, :535, is the caller's choice).  Multi-GPU:
+        ``scenes_per_batch`` is this rank's share, ``global_rows`` the whole batch's rows, ``row0`` this rank's offset."""
         from .data import epoch_batches
         spb = scenes_per_batch or self.specs["ScenesPerBatch"]
         losses = []
         buf = None
         for it, ids in enumerate(epoch_batches(len(dataset), spb, generator)):
+            if max_iterations is not None and it >= max_iterations:
+                break
             ids_d = ids.to(self.device)
             seed = (self.seed * 0x51ED27 + epoch * 0x10001 + it) & 0x7FFFFFFFFFFFFFFF
             buf = dataset.sample_batch(ids_d, seed, out=buf)
-            losses.append(self.step(buf, ids_d, epoch).clone())
+            losses.append(self.step(buf, ids_d, epoch, global_rows=global_rows, row0=row0).clone())
         return losses
 
     # ------------------------------------------------------------------ checkpoint surface (train_deep_sdf.py:96-143)

@@ -103,3 +103,54 @@ def test_epoch_from_device_store_trains():
         last = np.mean(losses)
     print(f"mean epoch loss {first:.5f} -> {last:.5f}")
     assert last < 0.9 * first
+
+
+def test_train_entry_point_writes_reference_layout(tmp_path, monkeypatch):
+    """deepsdf_b200.train on a tiny experiment: reference experiment layout in, reference checkpoint formats out
+    (train_deep_sdf.py:96-143,179-200; deep_sdf/workspace.py:9-21) - loadable with DataParallel's ``module.`` prefix."""
+    from deepsdf_b200 import train as T
+    from oracle import decoder_oracle as O
+    from tests.util import build_module
+    rng = np.random.RandomState(0)
+    d = tmp_path / "data" / "SdfSamples" / "micro" / "cs"
+    os.makedirs(d)
+    names = []
+    for s in range(4):
+        xyz = rng.uniform(-1, 1, (2000, 3)).astype(np.float32)
+        sdf = 0.25 * O.corner_spheres_sdf(xyz, 0.4 + 0.1 * s, limit=0.9).astype(np.float32)
+        rows = np.concatenate([xyz, sdf], 1)
+        np.savez(d / f"cs_{s}.npz", pos=rows[rows[:, 3] > 0], neg=rows[rows[:, 3] <= 0])
+        names.append(f"cs_{s}")
+    os.makedirs(tmp_path / "data" / "splits")
+    with open(tmp_path / "data" / "splits" / "cs.json", "w") as f:
+        json.dump({"micro": {"cs": names}}, f)
+    exp = tmp_path / "exp"
+    os.makedirs(exp)
+    net = dict(dims=[512] * 8, dropout=list(range(8)), dropout_prob=0.2, norm_layers=list(range(8)), latent_in=[4],
+               weight_norm=True, xyz_in_all=False, use_tanh=False, latent_dropout=False, geom_dimension=3)
+    specs = {"Description": "test", "DataSource": str(tmp_path / "data"), "NetworkArch": "deep_sdf_decoder",
+             "TrainSplit": str(tmp_path / "data" / "splits" / "cs.json"), "NetworkSpecs": net, "CodeLength": 8, "NumEpochs": 3,
+             "SnapshotFrequency": 2, "AdditionalSnapshots": [], "LogFrequency": 1,
+             "LearningRateSchedule": [{"Type": "Step", "Initial": 1e-4, "Interval": 500, "Factor": 0.5},
+                                      {"Type": "Step", "Initial": 1e-3, "Interval": 500, "Factor": 0.5}],
+             "SamplesPerScene": 512, "ScenesPerBatch": 2, "ClampingDistance": 0.1, "CodeRegularization": True,
+             "CodeRegularizationLambda": 1e-4, "CodeBound": 1.0}
+    with open(exp / "specs.json", "w") as f:
+        json.dump(specs, f)
+    for k in ("WORLD_SIZE", "RANK", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    res = T.main_function(str(exp))
+    assert res["epochs"] == 3 and len(res["loss"]) == 3 * 2              # 4 scenes / 2 per batch
+    assert sorted(os.listdir(exp / "ModelParameters")) == ["2.pth", "latest.pth"]
+    ck = torch.load(exp / "ModelParameters" / "latest.pth", weights_only=False)
+    assert ck["epoch"] == 3 and all(k.startswith("module.") for k in ck["model_state_dict"])
+    dp = torch.nn.DataParallel(build_module(dict(latent_size=8, **net)))
+    dp.load_state_dict(ck["model_state_dict"], strict=True)               # what ws.load_model_parameters does
+    lat = torch.load(exp / "LatentCodes" / "latest.pth", weights_only=False)
+    assert lat["latent_codes"]["weight"].shape == (4, 8)                  # an nn.Embedding state_dict
+    emb = torch.nn.Embedding(4, 8)
+    emb.load_state_dict(lat["latent_codes"])
+    logs = torch.load(exp / "Logs.pth", weights_only=False)
+    assert set(logs) == {"epoch", "loss", "learning_rate", "timing", "latent_magnitude", "param_magnitude"}
+    assert len(logs["loss"]) == 6 and len(logs["learning_rate"]) == 3 and "lin0.bias" in logs["param_magnitude"]
+    assert os.path.isfile(exp / "OptimizerParameters" / "latest.pth")
