@@ -19,15 +19,16 @@ namespace dsdf {
 
 namespace {
 
-constexpr int J_STAGES = 4;
+constexpr int J_MAX_STAGES = 8;                          // ring depth is chosen at run time from the stage size
 constexpr int J_A_BYTES = TILE_M * 128;                 // [128 rows][64 K] bf16, SW128
 constexpr int J_B_ROWS_MAX = 272;
 constexpr int J_B_BYTES = J_B_ROWS_MAX * 128;           // [<=272 output columns][64 K] bf16, SW128
-constexpr int J_STAGE_BYTES = J_A_BYTES + J_B_BYTES;    // 51 200 (1024-aligned)
-constexpr int J_OFF_T = J_STAGES * J_STAGE_BYTES;
+constexpr int J_RING_BYTES = 3 * (J_A_BYTES + J_B_BYTES);   // 153 600: 3 stages at L = 256, 8 stages of 18 KB at L <= 13
+constexpr int J_OFF_T = J_RING_BYTES;
 constexpr int J_T_FLOATS = 32 * 33;                     // one padded 32x32 transpose block per epilogue warp
-constexpr int J_SMEM = J_OFF_T + 4 * J_T_FLOATS * 4 + 1024;
-constexpr int J_THREADS = 6 * 32;                       // TMA warp, MMA warp, 4 epilogue warps
+constexpr int J_EPI_WARPS = 8;                           // two per TMEM lane quadrant, alternating 32-column chunks
+constexpr int J_SMEM = J_OFF_T + J_EPI_WARPS * J_T_FLOATS * 4 + 1024;
+constexpr int J_THREADS = (2 + J_EPI_WARPS) * 32;        // TMA warp, MMA warp, 8 epilogue warps
 
 struct JacArgs {
   int32_t n_tiles;
@@ -35,6 +36,9 @@ struct JacArgs {
   int32_t lat_layer;
   int32_t jac_rows;        // padded output columns (multiple of 16)
   int32_t n_out;           // L + 3
+  int32_t stage_bytes;     // 16 KB dY tile + jac_rows x 128 B of the operand, 1024-aligned
+  int32_t n_stages;        // min(8, ring / stage_bytes)
+  int32_t tmem_base1;      // TMEM column of the odd tiles' accumulators: 256, or 224 when jac_rows = 272 (64 shared columns)
   int64_t n_rows;
   int64_t n_rows_pad;
   float* G;
@@ -49,15 +53,15 @@ input_grad_kernel(const __grid_constant__ CUtensorMap tmDys, const __grid_consta
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* s_t = reinterpret_cast<float*>(smem + J_OFF_T);
-  __shared__ uint64_t bar_full[J_STAGES], bar_empty[J_STAGES], bar_tmem_full, bar_tmem_empty;
+  __shared__ uint64_t bar_full[J_MAX_STAGES], bar_empty[J_MAX_STAGES], bar_tmem_full, bar_tmem_empty;
   __shared__ uint32_t tmem_slot;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < J_STAGES; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+    for (int s = 0; s < J_MAX_STAGES; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
     mbar_init(&bar_tmem_full, 1);
-    mbar_init(&bar_tmem_empty, 4);
+    mbar_init(&bar_tmem_empty, J_EPI_WARPS);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(&tmem_slot);
@@ -78,7 +82,7 @@ input_grad_kernel(const __grid_constant__ CUtensorMap tmDys, const __grid_consta
       for (int kc = 0; kc < args.k_chunks; ++kc) {
         mbar_wait_a(empty0 + stage * 8, phase ^ 1);
         if (elect_one()) {
-          const uint32_t bar = full0 + stage * 8, base = s_u + stage * J_STAGE_BYTES;
+          const uint32_t bar = full0 + stage * 8, base = s_u + stage * args.stage_bytes;
           mbar_arrive_expect_tx_a(bar, stage_tx);
           const int layer = kc < 8 ? 0 : args.lat_layer;
           tma_load_2d_a(base, &tmDys, bar, (kc & 7) * 64, int32_t(int64_t(layer) * args.n_rows_pad + int64_t(tile) * TILE_M));
@@ -86,7 +90,7 @@ input_grad_kernel(const __grid_constant__ CUtensorMap tmDys, const __grid_consta
             tma_load_2d_a(base + J_A_BYTES + rb * 128, &tmJ, bar, kc * 64, rb);
         }
         __syncwarp();
-        if (++stage == J_STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == uint32_t(args.n_stages)) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -99,26 +103,29 @@ input_grad_kernel(const __grid_constant__ CUtensorMap tmDys, const __grid_consta
     const uint32_t tfull = smem_u32(&bar_tmem_full), tempty = smem_u32(&bar_tmem_empty);
     uint32_t stage = 0, phase = 0, it = 0;
     for (int tile = blockIdx.x; tile < args.n_tiles; tile += gridDim.x, ++it) {
-      mbar_wait_a(tempty, (it & 1) ^ 1);          // the epilogue has drained the previous tile's accumulators
+      // Accumulators alternate between TMEM columns 0 and tmem_base1, so this tile's MMAs overlap the previous tile's
+      // epilogue; the two regions may share 32 columns, which that epilogue drains first and then signals here.
+      mbar_wait_a(tempty, (it & 1) ^ 1);
       tc_fence_after();
+      const uint32_t d_tmem = tmem_base + ((it & 1) ? uint32_t(args.tmem_base1) : 0u);
       for (int kc = 0; kc < args.k_chunks; ++kc) {
         mbar_wait_a(full0 + stage * 8, phase);
         tc_fence_after();
-        const uint64_t ad = s_base + uint64_t(stage * (J_STAGE_BYTES >> 4));
+        const uint64_t ad = s_base + uint64_t(stage * uint32_t(args.stage_bytes >> 4));
         const uint64_t bd = ad + uint64_t(J_A_BYTES >> 4);
         const uint64_t bd2 = bd + uint64_t((256 * 128) >> 4);
         if (elect_one()) {
 #pragma unroll
           for (int k4 = 0; k4 < 4; ++k4) {
             const uint32_t acc = (kc | k4) != 0 ? 1u : 0u;
-            umma_bf16_ss(tmem_base, ad + 2 * k4, bd + 2 * k4, idesc1, acc);
-            if (n2) umma_bf16_ss(tmem_base + 256, ad + 2 * k4, bd2 + 2 * k4, idesc2, acc);
+            umma_bf16_ss(d_tmem, ad + 2 * k4, bd + 2 * k4, idesc1, acc);
+            if (n2) umma_bf16_ss(d_tmem + 256, ad + 2 * k4, bd2 + 2 * k4, idesc2, acc);
           }
           umma_commit_a(empty0 + stage * 8);
           if (kc == args.k_chunks - 1) umma_commit_a(tfull);
         }
         __syncwarp();
-        if (++stage == J_STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == uint32_t(args.n_stages)) { stage = 0; phase ^= 1; }
       }
     }
   } else {
@@ -131,10 +138,22 @@ input_grad_kernel(const __grid_constant__ CUtensorMap tmDys, const __grid_consta
       mbar_wait_sleep(&bar_tmem_full, it & 1, 64);
       tc_fence_after();
       const int64_t row0 = int64_t(tile) * TILE_M + q * 32;
-      for (int c0 = 0; c0 < args.n_out; c0 += 32) {
+      const uint32_t t_row = tmem_row + ((it & 1) ? uint32_t(args.tmem_base1) : 0u);
+      // this warp's 32-column chunks: c = hsel, hsel + 2, ... ; even tiles walk them downwards, odd tiles upwards, so the
+      // FIRST chunk of every warp is the one that may overlap the other region - after it the next tile's MMAs may start
+      const int hsel = (warp - 2) >> 2;
+      const int n_chunks = (args.n_out + 31) >> 5;
+      const int mine = (n_chunks - hsel + 1) >> 1;                 // chunks hsel, hsel+2, ... < n_chunks
+      for (int k = 0; k < mine; ++k) {
+        const int c0 = 32 * (hsel + 2 * ((it & 1) ? k : mine - 1 - k));
         uint32_t r[32];
-        tmem_ld32(tmem_row + uint32_t(c0), r);
+        tmem_ld32(t_row + uint32_t(c0), r);
         tmem_ld_wait();
+        if (k == 0) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bar_tmem_empty);
+        }
 #pragma unroll
         for (int i = 0; i < 32; ++i) T[lane * 33 + i] = __uint_as_float(r[i]);
         __syncwarp();
@@ -146,9 +165,11 @@ input_grad_kernel(const __grid_constant__ CUtensorMap tmDys, const __grid_consta
         }
         __syncwarp();
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar_tmem_empty);
+      if (mine == 0) {                                             // a warp without chunks still takes part in the hand-over
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_tmem_empty);
+      }
     }
   }
 
@@ -241,6 +262,11 @@ extern "C" int dsdf_fused_input_grad(const dsdf_net_desc* desc, const void* pack
   a.lat_layer = lo.lat_layer;
   a.jac_rows = lo.jac_rows;
   a.n_out = n_out;
+  a.stage_bytes = (J_A_BYTES + lo.jac_rows * 128 + 1023) / 1024 * 1024;
+  a.n_stages = J_RING_BYTES / a.stage_bytes < J_MAX_STAGES ? J_RING_BYTES / a.stage_bytes : J_MAX_STAGES;
+  const int cols32 = (lo.jac_rows + 31) / 32 * 32;              // the epilogue reads whole 32-column chunks
+  DSDF_REQUIRE(cols32 <= 288, "latent_size too large for the input-gradient kernel");
+  a.tmem_base1 = cols32 <= 256 ? 256 : 512 - cols32;            // <= 64 shared columns = the first chunk of each warp set
   a.n_rows = n_rows;
   a.n_rows_pad = n_rows;
   a.G = G;
