@@ -10,6 +10,10 @@ LearningRateSchedule, SamplesPerScene, ScenesPerBatch, ClampingDistance, CodeReg
 CodeInitStdDev, GradientClipNorm, LogFrequency).  Scenes are block-partitioned over the ranks (``sharding``); every rank
 loads ITS scenes' npz files into HBM once (``DeviceSDFSamples``) and steps ``ScenesPerBatch / world_size`` scenes per
 iteration; the decoder gradient is all-reduced, latent codes never move until a checkpoint gathers them.
+``--strict-shuffle`` (or ``"SceneSharding": "replicated"`` in specs.json) is the strict mode of SURVEY.md 8(e): every rank
+holds all scenes and all latent rows, batches come from the reference's global shuffle, rank r steps the r-th share of
+each batch and the latent gradient is all-reduced with the decoder gradient - the N-GPU run then reproduces the 1-GPU
+loss curve up to summation order (tests/test_multirank_gpu.py).
 
 Rank 0 writes what the reference writes, loadable by the reference's own tools (``deep_sdf/workspace.py``):
   ModelParameters/<epoch|latest>.pth   {"epoch", "model_state_dict"} with DataParallel's ``module.`` key prefix  (:96-104)
@@ -53,7 +57,7 @@ def count_instances(split: dict) -> int:
 
 def gather_latents(trainer: SceneTrainer, num_scenes: int, world: int, rank: int) -> torch.Tensor:
     """All ranks' latent rows in global scene order (rank r owns the block ``partition_scenes(num_scenes, r, world)``)."""
-    if world == 1:
+    if world == 1 or trainer.replicated:
         return trainer.lat_vecs.detach().cpu().clone()
     import torch.distributed as dist
     most = max(len(sharding.partition_scenes(num_scenes, r, world)) for r in range(world))
@@ -77,7 +81,8 @@ def save_checkpoint(exp: str, name: str, trainer: SceneTrainer, all_latents: tor
         os.path.join(exp, optimizer_params_subdir, name))
 
 
-def main_function(experiment_directory: str, data_source: str = None, max_epochs: int = None) -> dict:
+def main_function(experiment_directory: str, data_source: str = None, max_epochs: int = None,
+                  strict_shuffle: bool = None, backend: str = "nccl") -> dict:
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -88,7 +93,8 @@ def main_function(experiment_directory: str, data_source: str = None, max_epochs
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        if not dist.is_initialized():
+            dist.init_process_group(backend, **({"device_id": dev} if backend == "nccl" else {}))
     logging.basicConfig(level=logging.INFO if rank == 0 else logging.WARNING, format="%(asctime)s %(message)s", datefmt="%H:%M:%S")
     with open(os.path.join(experiment_directory, specifications_filename)) as f:
         specs = json.load(f)
@@ -97,30 +103,36 @@ def main_function(experiment_directory: str, data_source: str = None, max_epochs
     with open(specs["TrainSplit"]) as f:
         train_split = json.load(f)
     num_scenes = count_instances(train_split)
-    mine = sharding.partition_scenes(num_scenes, rank, world)
+    if strict_shuffle is None:
+        strict_shuffle = get_spec_with_default(specs, "SceneSharding", "partition") == "replicated"
+    mine = range(num_scenes) if strict_shuffle else sharding.partition_scenes(num_scenes, rank, world)
     sps, spb = specs["SamplesPerScene"], specs["ScenesPerBatch"]
     if spb % world:
         raise SystemExit(f"ScenesPerBatch ({spb}) must be a multiple of the number of GPUs ({world})")
     spb_local = spb // world
     dataset = DeviceSDFSamples(data_source, split_subset(train_split, mine.start, mine.stop), sps, 3, dev)
     logging.info("There are {} scenes ({} on this GPU, {} rows resident)".format(num_scenes, len(dataset), dataset.total_rows))
-    trainer = SceneTrainer(specs, len(dataset), dev, rank=rank, world_size=world, seed=get_spec_with_default(specs, "Seed", 0))
+    trainer = SceneTrainer(specs, len(dataset), dev, rank=rank, world_size=world, seed=get_spec_with_default(specs, "Seed", 0),
+                           replicated=strict_shuffle)
     num_epochs = specs["NumEpochs"] if max_epochs is None else min(max_epochs, specs["NumEpochs"])
     checkpoints = sorted(set(list(range(specs["SnapshotFrequency"], specs["NumEpochs"] + 1, specs["SnapshotFrequency"]))
                              + list(specs.get("AdditionalSnapshots", []))))                     # :281-291
     log_frequency = get_spec_with_default(specs, "LogFrequency", 10)
     loss_log, lr_log, timing_log, lat_mag_log, param_mag_log = [], [], [], [], {}
-    gen = torch.Generator().manual_seed(1234 + rank)
-    its = len(dataset) // spb_local
-    if world > 1:                                      # every rank must take the same number of iterations per epoch
+    gen = torch.Generator().manual_seed(1234 + (0 if strict_shuffle else rank))
+    its = num_scenes // spb if strict_shuffle else len(dataset) // spb_local
+    if world > 1 and not strict_shuffle:               # every rank must take the same number of iterations per epoch
         import torch.distributed as dist
         t = torch.tensor([its], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         its = int(t.item())
     for epoch in range(1, num_epochs + 1):
         start = time.time()
-        losses = trainer.train_epoch(dataset, epoch, scenes_per_batch=spb_local, generator=gen, max_iterations=its,
-                                     global_rows=spb * sps, row0=sharding.row_offset(rank, spb_local * sps))
+        if strict_shuffle:
+            losses = trainer.train_epoch(dataset, epoch, scenes_per_batch=spb, generator=gen, max_iterations=its)
+        else:
+            losses = trainer.train_epoch(dataset, epoch, scenes_per_batch=spb_local, generator=gen, max_iterations=its,
+                                         global_rows=spb * sps, row0=sharding.row_offset(rank, spb_local * sps))
         ep = torch.stack([l[0] for l in losses]) if losses else torch.zeros(0, device=dev)
         if world > 1:
             import torch.distributed as dist
@@ -156,5 +168,8 @@ if __name__ == "__main__":
                     help="experiment directory with specs.json; checkpoints and logs are written there (reference layout)")
     ap.add_argument("--data", "-d", dest="data_source", default=None, help="overrides specs['DataSource']")
     ap.add_argument("--max-epochs", type=int, default=None)
+    ap.add_argument("--strict-shuffle", action="store_true", default=None,
+                    help="replicate scenes and latent codes on every GPU and shard the reference's global shuffle")
+    ap.add_argument("--backend", default="nccl", help="torch.distributed backend (gloo lets several ranks share one GPU)")
     a = ap.parse_args()
-    main_function(a.experiment_directory, a.data_source, a.max_epochs)
+    main_function(a.experiment_directory, a.data_source, a.max_epochs, a.strict_shuffle, a.backend)

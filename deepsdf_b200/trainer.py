@@ -17,6 +17,12 @@ samples of its scenes; only the 7.4 MB flat decoder gradient is exchanged.  The 
 rows (:519), so each rank's gradient is already scaled and the all-reduce is a plain sum.  Dropout streams are keyed by
 the global row id, so results do not depend on the number of ranks.
 
+``replicated=True`` is the strict mode of SURVEY.md 8(e): every rank keeps ALL latent rows (and the whole sample store),
+batches are drawn from the reference's GLOBAL scene shuffle (:369-375) with a generator shared by all ranks, rank r steps
+the r-th contiguous share of each batch, and the dense latent gradient rides in the same all-reduce as the decoder
+gradient (one flat buffer), so that every rank applies the identical Adam update to every latent row.  An N-rank run then
+walks the same batches, samples and dropout masks as the 1-rank run and differs only in floating-point summation order.
+
 Python here is plumbing (tensors, streams, torch.distributed); every arithmetic step is a kernel of libdsdf_b200.so.
 """
 from __future__ import annotations
@@ -75,8 +81,9 @@ def _flatten_into(tensors: Sequence[torch.Tensor], align: int = 64):
 
 class SceneTrainer:
     def __init__(self, specs: Dict, num_scenes: int, device, rank: int = 0, world_size: int = 1, process_group=None,
-                 seed: int = 0, decoder: Optional[Decoder] = None):
-        """``specs`` is a parsed ``specs.json``; ``num_scenes`` the number of scenes THIS rank owns."""
+                 seed: int = 0, decoder: Optional[Decoder] = None, replicated: bool = False):
+        """``specs`` is a parsed ``specs.json``; ``num_scenes`` the number of scenes THIS rank owns (``replicated``: all
+        scenes of the split, identical on every rank)."""
         self.specs = specs
         self.device = torch.device(device)
         self.rank, self.world_size, self.pg = rank, world_size, process_group
@@ -91,7 +98,11 @@ class SceneTrainer:
         # ---- flat parameter / gradient / Adam-moment buffers; the module's Parameters become views into ``flat_p``
         plist = self.decoder.flat_param_list()
         self.flat_p, self._offs = _flatten_into(plist)
-        self.flat_g = torch.zeros_like(self.flat_p)
+        self.replicated = bool(replicated)
+        # strict mode: decoder and latent gradients share one buffer = one all-reduce
+        n_lat = num_scenes * self.latent_size if (self.replicated and world_size > 1) else 0
+        self._gbuf = torch.zeros(self.flat_p.numel() + n_lat, dtype=torch.float32, device=self.flat_p.device)
+        self.flat_g = self._gbuf[:self.flat_p.numel()]
         self.exp_avg = torch.zeros_like(self.flat_p)
         self.exp_avg_sq = torch.zeros_like(self.flat_p)
         self._grad_views: List[torch.Tensor] = []
@@ -103,9 +114,9 @@ class SceneTrainer:
         # ---- latent codes of the scenes this rank owns (train_deep_sdf.py:385-390)
         self.num_scenes = num_scenes
         std = get_spec_with_default(specs, "CodeInitStdDev", 1.0) / math.sqrt(self.latent_size)
-        g = torch.Generator(device="cpu").manual_seed(seed * 7919 + 17 + rank)
+        g = torch.Generator(device="cpu").manual_seed(seed * 7919 + 17 + (0 if self.replicated else rank))
         self.lat_vecs = (torch.randn(num_scenes, self.latent_size, generator=g) * std).to(self.device)
-        self.lat_grad = torch.zeros_like(self.lat_vecs)
+        self.lat_grad = self._gbuf[self.flat_p.numel():].view(num_scenes, self.latent_size) if n_lat else torch.zeros_like(self.lat_vecs)
         self.lat_exp_avg = torch.zeros_like(self.lat_vecs)
         self.lat_exp_avg_sq = torch.zeros_like(self.lat_vecs)
         # ---- hyper-parameters
@@ -140,12 +151,14 @@ class SceneTrainer:
 
     # ------------------------------------------------------------------ one optimiser step
     def step(self, samples: torch.Tensor, scene_ids: torch.Tensor, epoch: int, global_rows: Optional[int] = None,
-             row0: int = 0) -> torch.Tensor:
+             row0: int = 0, batch_scene_ids: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One iteration of train_deep_sdf.py:481-545 (batch_split = 1) on this rank's share of the batch.
 
         samples    [S * SamplesPerScene, 4] fp32 device tensor, scene-major rows of (x, y, z, sdf) - exactly what the
                    reference's DataLoader yields after ``reshape(-1, 4)`` (:483); read in place, never split or copied
         scene_ids  [S] int64 device tensor: rows of ``lat_vecs`` (local numbering), unique within the batch
+        batch_scene_ids  strict mode only: the scene ids of the WHOLE batch (all ranks' shares), so that the Embedding
+                   max_norm renorm (:385) touches the same rows of every replica of ``lat_vecs``
         Returns the device tensor [2] = (loss incl. regulariser, data term) of this rank's rows, normalised by the
         global row count like the reference's ``chunk_loss`` (:519).
         """
@@ -161,16 +174,27 @@ class SceneTrainer:
         self.step_count += 1
         seed = (self.seed * 0x9E3779B1 + self.step_count) & 0x3FFFFFFFFFFFFFFF
         flat = samples.view(-1)
+        code_bound = self.code_bound
+        shared_lat = self.replicated and self.world_size > 1
+        if shared_lat:
+            if batch_scene_ids is None:
+                raise L.DsdfError("replicated latents: step() needs the whole batch's scene ids (batch_scene_ids)")
+            if code_bound:
+                eng.scene_bias(self.lat_vecs, batch_scene_ids, code_bound)     # renorm only; the bias it writes is scratch
+                code_bound = None
         loss = eng.loss_and_grads(self.lat_vecs, scene_ids, tile_scene, flat, flat[3:], clamp=self.clamp if self.enforce_minmax else 0.0,
-                                  reg_lambda_eff=lam, n_total=n_total, code_bound=self.code_bound, seed=seed,
+                                  reg_lambda_eff=lam, n_total=n_total, code_bound=code_bound, seed=seed,
                                   row0=row0, PG=self.PG, lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
                                   n_rows=N)
         # the decoder-gradient all-reduce (NCCL, its own stream) overlaps the latent Adam, which needs no exchange
         work = None
         if self.world_size > 1:
             import torch.distributed as dist
-            work = dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+            work = dist.all_reduce(self._gbuf, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
         lr_dec, lr_lat = self.learning_rates(epoch)
+        if shared_lat:                                   # the latent gradient is part of the exchange
+            work.wait()
+            work = None
         eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat)
         if work is not None:
             work.wait()
@@ -196,18 +220,30 @@ class SceneTrainer:
         """One epoch of train_deep_sdf.py:472-545 from a ``DeviceSDFSamples`` store: shuffled scene batches (drop_last),
         every batch subsampled on the device (``dsdf_sample_batch``) and stepped.  Returns the per-iteration loss tensors
         (device, no synchronisation - the reference's ``.item()`` per chunk, :535, is the caller's choice).  Multi-GPU:
-        ``scenes_per_batch`` is this rank's share, ``global_rows`` the whole batch's rows, ``row0`` this rank's offset."""
+        ``scenes_per_batch`` is this rank's share, ``global_rows`` the whole batch's rows, ``row0`` this rank's offset.
+        Strict mode (``replicated``): ``dataset`` holds every scene, ``generator`` is seeded identically on all ranks,
+        ``scenes_per_batch`` is the GLOBAL batch; the share, ``global_rows`` and ``row0`` follow from the rank."""
         from .data import epoch_batches
         spb = scenes_per_batch or self.specs["ScenesPerBatch"]
+        shared_lat = self.replicated and self.world_size > 1
+        if shared_lat and spb % self.world_size:
+            raise L.DsdfError("replicated latents: scenes_per_batch must be a multiple of the number of ranks")
+        share = spb // self.world_size if shared_lat else spb
         losses = []
         buf = None
         for it, ids in enumerate(epoch_batches(len(dataset), spb, generator)):
             if max_iterations is not None and it >= max_iterations:
                 break
             ids_d = ids.to(self.device)
+            mine = ids_d[self.rank * share:(self.rank + 1) * share].contiguous() if shared_lat else ids_d
             seed = (self.seed * 0x51ED27 + epoch * 0x10001 + it) & 0x7FFFFFFFFFFFFFFF
-            buf = dataset.sample_batch(ids_d, seed, out=buf)
-            losses.append(self.step(buf, ids_d, epoch, global_rows=global_rows, row0=row0).clone())
+            buf = dataset.sample_batch(mine, seed, out=buf)
+            if shared_lat:
+                sps = buf.shape[0] // share
+                loss = self.step(buf, mine, epoch, global_rows=spb * sps, row0=self.rank * share * sps, batch_scene_ids=ids_d)
+            else:
+                loss = self.step(buf, mine, epoch, global_rows=global_rows, row0=row0)
+            losses.append(loss.clone())
         return losses
 
     # ------------------------------------------------------------------ checkpoint surface (train_deep_sdf.py:96-143)

@@ -1,0 +1,98 @@
+"""Multi-rank training on the GPU, runnable on a ONE-GPU box: two ``gloo`` ranks share ``cuda:0``
+(gloo all-reduces CUDA tensors through the host; NCCL wants one device per rank and is exercised by ``bench.py --gpus N``).
+
+* strict mode (``--strict-shuffle``): the 2-rank run must reproduce the 1-rank loss curve, decoder and latent codes up to
+  floating-point summation order - same global shuffle, same drawn samples, same dropout masks (keyed by global row);
+* partition mode: both ranks own half the scenes; the run must train (loss falls) and write the gathered latent table.
+"""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _make_experiment(tmp_path, n_scenes=8, epochs=3):
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "make_tiny_experiment.py"), str(tmp_path), str(n_scenes)])
+    sp = os.path.join(str(tmp_path), "exp", "specs.json")
+    with open(sp) as f:
+        specs = json.load(f)
+    specs.update(NumEpochs=epochs, SnapshotFrequency=epochs, LogFrequency=1, ScenesPerBatch=4, SamplesPerScene=1024)
+    with open(sp, "w") as f:
+        json.dump(specs, f)
+    return os.path.join(str(tmp_path), "exp")
+
+
+def _clone_experiment(exp, name):
+    dst = os.path.join(os.path.dirname(exp), name)
+    os.makedirs(dst)
+    with open(os.path.join(exp, "specs.json")) as f, open(os.path.join(dst, "specs.json"), "w") as g:
+        g.write(f.read())
+    return dst
+
+
+def _run(exp, world, extra=(), port=29611):
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), LOCAL_RANK="0", MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port), PYTHONPATH=ROOT)
+        procs.append(subprocess.Popen([sys.executable, "-m", "deepsdf_b200.train", "-e", exp, "--backend", "gloo", *extra],
+                                      env=env, cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+    outs = []
+    for p in procs:
+        try:
+            out, _ = p.communicate(timeout=240)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        outs.append(out.decode(errors="replace"))
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o[-3000:]
+
+
+def _load(exp, epoch):
+    logs = torch.load(os.path.join(exp, "Logs.pth"), weights_only=False)
+    model = torch.load(os.path.join(exp, "ModelParameters", f"{epoch}.pth"), weights_only=False)["model_state_dict"]
+    lat = torch.load(os.path.join(exp, "LatentCodes", f"{epoch}.pth"), weights_only=False)["latent_codes"]["weight"]
+    return np.asarray(logs["loss"]), model, lat
+
+
+def _assert_close(a, b, atol, hard, what):
+    d = (a.float() - b.float()).abs()
+    assert float(d.max()) <= hard + 1e-6, (what, float(d.max()))
+    assert float((d > atol).float().mean()) <= 2e-3, (what, float((d > atol).float().mean()))
+
+
+def test_strict_shuffle_two_ranks_reproduce_one_rank(tmp_path):
+    exp1 = _make_experiment(tmp_path)
+    exp2 = _clone_experiment(exp1, "exp2")
+    _run(exp1, 1, ["--strict-shuffle"], port=29611)
+    _run(exp2, 2, ["--strict-shuffle"], port=29612)
+    l1, m1, z1 = _load(exp1, 3)
+    l2, m2, z2 = _load(exp2, 3)
+    assert l1.shape == l2.shape == (6,)                      # 8 scenes / 4 per batch x 3 epochs
+    # bf16 tensor-core math is identical per row; only the fp32 reduction trees (per-rank partial sums) differ
+    np.testing.assert_allclose(l2, l1, rtol=2e-5)
+    assert z1.shape == z2.shape == (8, 16)
+    # Adam's first steps move every element by ~lr * sign(g): an element whose gradient is within rounding noise of zero
+    # may step the other way, so the bound is "all but a sliver agree to 2e-5, none differs by more than steps * 2 lr"
+    _assert_close(z2, z1, 2e-5, 6 * 2 * 1e-3, "latent codes")
+    for k in m1:
+        _assert_close(m2[k], m1[k], 2e-5, 6 * 2 * 1e-4, k)
+
+
+def test_partition_mode_two_ranks_train(tmp_path):
+    exp = _make_experiment(tmp_path, epochs=6)
+    _run(exp, 2, port=29613)
+    loss, model, lat = _load(exp, 6)
+    assert loss.shape == (12,)                               # each rank owns 4 scenes and steps 2 per iteration: 2 its x 6 epochs
+    assert np.all(np.isfinite(loss)) and loss[-1] < loss[0]
+    assert lat.shape == (8, 16) and torch.isfinite(lat).all()
+    assert all(k.startswith("module.") for k in model)
