@@ -80,3 +80,111 @@ class LatentOptimizer:
             if record_every and (e % record_every == 0 or e == num_iterations - 1):
                 hist.append(loss.clone())
         return hist
+
+
+# ---------------------------------------------------------------------------------------------- command line
+reconstructions_subdir, reconstruction_codes_subdir, reconstruction_meshes_subdir = "Reconstructions", "Codes", "Meshes"
+
+
+def load_decoder(experiment_directory: str, checkpoint: str, device):
+    """deep_sdf/workspace.py:48-83 ``load_experiment_specifications`` + ``load_model_parameters``: returns (decoder in
+    eval mode on ``device``, specs, saved epoch).  Checkpoints written under nn.DataParallel carry a ``module.`` prefix."""
+    import json
+    import os
+    from .networks.deep_sdf_decoder import Decoder
+    with open(os.path.join(experiment_directory, "specs.json")) as f:
+        specs = json.load(f)
+    decoder = Decoder(specs["CodeLength"], **specs["NetworkSpecs"])
+    data = torch.load(os.path.join(experiment_directory, "ModelParameters", checkpoint + ".pth"), map_location="cpu", weights_only=False)
+    sd = {(k[len("module."):] if k.startswith("module.") else k): v for k, v in data["model_state_dict"].items()}
+    decoder.load_state_dict(sd)
+    return decoder.to(device).eval(), specs, data["epoch"]
+
+
+def reconstruct_split(experiment_directory: str, checkpoint: str = "latest", data_source: Optional[str] = None,
+                      split_filename: Optional[str] = None, iters: int = 800, num_samples: int = 8000, skip: bool = False,
+                      shapes_per_batch: int = 1024, resolution: int = 0, seed: int = 0, rank: int = 0, world: int = 1,
+                      device="cuda") -> dict:
+    """Upstream ``reconstruct.py -e <experiment> -c <checkpoint> -d <data> -s <split>``: optimise one latent code per
+    instance of the split against the frozen decoder and write ``Reconstructions/<epoch>/Codes/<dataset>/<class>/
+    <instance>.pth`` (a [1, 1, L] tensor like upstream's ``latent.unsqueeze(0)``; path helpers: deep_sdf/workspace.py:122-149).
+    All shapes of a batch are optimised together; ranks take disjoint blocks of the instance list (no collective).
+    Per-iteration samples come from the device store with the training sampler (half positive / half negative rows
+    without replacement, deep_sdf/data.py:88-99) - upstream shuffles once and takes random contiguous windows
+    (deep_sdf/data.py:113-139), the same distribution.  ``resolution`` > 0 also evaluates create_mesh's grid for every shape
+    and writes ``Meshes/.../<instance>.sdf.npy`` ([N,N,N] fp32); marching cubes / ply stay on the host (skimage absent)."""
+    import json
+    import os
+    import numpy as np
+    from . import sharding
+    from .data import DeviceSDFSamples, sdf_samples_subdir
+    from .mesh import create_mesh_sdf
+    dev = torch.device(device)
+    decoder, specs, saved_epoch = load_decoder(experiment_directory, checkpoint, dev)
+    data_source = data_source or specs["DataSource"]
+    split_filename = split_filename or specs.get("TestSplit") or specs["TrainSplit"]
+    with open(split_filename) as f:
+        split = json.load(f)
+    instances = [(d, c, i) for d in split for c in split[d] for i in split[d][c]]
+    mine = sharding.partition_scenes(len(instances), rank, world)
+    clamp = specs.get("ClampingDistance", 0.1)
+    root = os.path.join(experiment_directory, reconstructions_subdir, str(saved_epoch))
+    todo = []
+    for k in mine:
+        d, c, i = instances[k]
+        code_fn = os.path.join(root, reconstruction_codes_subdir, d, c, i + ".pth")
+        if skip and os.path.isfile(code_fn):
+            continue
+        todo.append((d, c, i, code_fn))
+    errs = {}
+    for b0 in range(0, len(todo), shapes_per_batch):
+        part = todo[b0:b0 + shapes_per_batch]
+        arrays = []
+        for d, c, i, _ in part:
+            npz = np.load(os.path.join(data_source, sdf_samples_subdir, d, c, i + ".npz"))
+            arrays.append((npz["pos"], npz["neg"]))
+        store = DeviceSDFSamples(None, None, num_samples, 3, dev, arrays=arrays)
+        S = len(part)
+        opt = LatentOptimizer(decoder, S, num_samples=num_samples, clamp_dist=clamp, lr=5e-3, l2reg=True, init_std=0.01,
+                              seed=seed + b0 + 7919 * rank)
+        ids = torch.arange(S, dtype=torch.int64, device=dev)
+        adjust_every, buf, loss = max(1, int(iters / 2)), None, None
+        for e in range(iters):
+            buf = store.sample_batch(ids, (seed * 0x9E3779B1 + e) & 0x7FFFFFFFFFFFFFFF, out=buf)
+            loss = opt.step(buf.view(S, num_samples, 4), 5e-3 * (0.1 ** (e // adjust_every)))
+        final = loss.cpu() if loss is not None else torch.zeros(S)
+        lat = opt.latents.detach().cpu()
+        for j, (d, c, i, code_fn) in enumerate(part):
+            os.makedirs(os.path.dirname(code_fn), exist_ok=True)
+            torch.save(lat[j].reshape(1, 1, -1).clone(), code_fn)
+            errs[os.path.join(d, c, i)] = float(final[j])
+            if resolution > 0:
+                mesh_fn = os.path.join(root, reconstruction_meshes_subdir, d, c, i + ".sdf.npy")
+                os.makedirs(os.path.dirname(mesh_fn), exist_ok=True)
+                np.save(mesh_fn, create_mesh_sdf(decoder, lat[j], N=resolution).reshape(resolution, resolution, resolution).cpu().numpy())
+    return {"epoch": saved_epoch, "loss": errs}
+
+
+if __name__ == "__main__":
+    import argparse
+    import os
+    ap = argparse.ArgumentParser(description="Use a trained DeepSDF decoder to reconstruct given SDF samples (fused B200 path)")
+    ap.add_argument("--experiment", "-e", dest="experiment_directory", required=True)
+    ap.add_argument("--checkpoint", "-c", default="latest")
+    ap.add_argument("--data", "-d", dest="data_source", default=None)
+    ap.add_argument("--split", "-s", dest="split_filename", default=None)
+    ap.add_argument("--iters", type=int, default=800)
+    ap.add_argument("--num-samples", type=int, default=8000)
+    ap.add_argument("--skip", action="store_true", help="skip instances whose code file already exists")
+    ap.add_argument("--shapes-per-batch", type=int, default=1024)
+    ap.add_argument("--resolution", type=int, default=0, help="also write the [N,N,N] SDF volume of every reconstruction")
+    ap.add_argument("--seed", type=int, default=0)
+    a = ap.parse_args()
+    if not torch.cuda.is_available():
+        raise SystemExit("deepsdf_b200.reconstruct needs a CUDA device (sm_100a); there is no CPU path")
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    torch.cuda.set_device(local)
+    res = reconstruct_split(a.experiment_directory, a.checkpoint, a.data_source, a.split_filename, a.iters, a.num_samples,
+                            a.skip, a.shapes_per_batch, a.resolution, a.seed, rank, world, torch.device("cuda", local))
+    print("rank {}: reconstructed {} shapes of epoch {}, mean loss {:.5f}".format(
+        rank, len(res["loss"]), res["epoch"], sum(res["loss"].values()) / max(1, len(res["loss"]))))

@@ -154,3 +154,40 @@ def test_train_entry_point_writes_reference_layout(tmp_path, monkeypatch):
     assert set(logs) == {"epoch", "loss", "learning_rate", "timing", "latent_magnitude", "param_magnitude"}
     assert len(logs["loss"]) == 6 and len(logs["learning_rate"]) == 3 and "lin0.bias" in logs["param_magnitude"]
     assert os.path.isfile(exp / "OptimizerParameters" / "latest.pth")
+
+
+def test_reconstruct_cli_writes_codes_and_improves(tmp_path, monkeypatch):
+    """deepsdf_b200.reconstruct on the checkpoint of a short training run: Reconstructions/<epoch>/Codes/<dataset>/<class>/
+    <instance>.pth ([1,1,L], workspace.py:137-149) for every instance of the split; the optimised code must fit its shape's
+    samples better than the N(0, 0.01) starting code does; --skip leaves existing codes untouched."""
+    import subprocess
+    import sys
+    from deepsdf_b200 import reconstruct as R
+    from deepsdf_b200 import train as T
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call([sys.executable, os.path.join(root, "tools", "make_tiny_experiment.py"), str(tmp_path), "6"])
+    exp = str(tmp_path / "exp")
+    with open(os.path.join(exp, "specs.json")) as f:
+        specs = json.load(f)
+    specs.update(NumEpochs=30, SnapshotFrequency=30, LogFrequency=30, ScenesPerBatch=6, SamplesPerScene=2048)
+    specs["LearningRateSchedule"][0]["Initial"] = 5e-4
+    with open(os.path.join(exp, "specs.json"), "w") as f:
+        json.dump(specs, f)
+    for k in ("WORLD_SIZE", "RANK", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    T.main_function(exp)
+    short = R.reconstruct_split(exp, "latest", iters=1, num_samples=1000, seed=3)
+    res = R.reconstruct_split(exp, "latest", iters=200, num_samples=1000, resolution=32, seed=3)
+    assert res["epoch"] == 30 and len(res["loss"]) == 6
+    codes = tmp_path / "exp" / "Reconstructions" / "30" / "Codes" / "micro" / "cs"
+    assert sorted(os.listdir(codes)) == [f"cs_{i}.pth" for i in range(6)]
+    z = torch.load(codes / "cs_0.pth", weights_only=False)
+    assert z.shape == (1, 1, 16) and torch.isfinite(z).all()
+    vol = np.load(tmp_path / "exp" / "Reconstructions" / "30" / "Meshes" / "micro" / "cs" / "cs_0.sdf.npy")
+    assert vol.shape == (32, 32, 32) and np.isfinite(vol).all()
+    l0, l1 = np.mean(list(short["loss"].values())), np.mean(list(res["loss"].values()))
+    print(f"reconstruction loss: first iteration {l0:.5f} -> after 200 iterations {l1:.5f}")
+    assert l1 < l0
+    stamp = os.path.getmtime(codes / "cs_0.pth")
+    again = R.reconstruct_split(exp, "latest", iters=5, num_samples=1000, skip=True)
+    assert again["loss"] == {} and os.path.getmtime(codes / "cs_0.pth") == stamp
