@@ -13,7 +13,7 @@ import torch
 
 MAX_LAYERS = 16
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdsdf_b200.so")
+LIB_PATH = os.environ.get("DSDF_B200_LIB") or os.path.join(_HERE, "libdsdf_b200.so")   # the override is for A/B timing of two builds
 
 
 class NetDesc(C.Structure):

@@ -57,10 +57,10 @@ __device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float d
   for (int i = 0; i < 16; ++i) v[i] = (gate16 & (1u << i)) ? v[i] : 0.0f;
   const uint32_t base = sA + (c0 >> 6) * A_CHUNK_BYTES + row * 128u;
   const uint32_t piece0 = (c0 & 63u) >> 3;
-  sts_u32x4(base + ((piece0 ^ (row & 7u)) << 4), pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
-            pack_bf16x2(v[6], v[7]));
-  sts_u32x4(base + (((piece0 + 1) ^ (row & 7u)) << 4), pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]),
-            pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+  const uint32_t p0 = pack_bf16x2(v[0], v[1]), p1 = pack_bf16x2(v[2], v[3]), p2 = pack_bf16x2(v[4], v[5]), p3 = pack_bf16x2(v[6], v[7]);
+  const uint32_t p4 = pack_bf16x2(v[8], v[9]), p5 = pack_bf16x2(v[10], v[11]), p6 = pack_bf16x2(v[12], v[13]), p7 = pack_bf16x2(v[14], v[15]);
+  sts_u32x4(base + ((piece0 ^ (row & 7u)) << 4), p0, p1, p2, p3);
+  sts_u32x4(base + (((piece0 + 1) ^ (row & 7u)) << 4), p4, p5, p6, p7);
 }
 
 }  // namespace
@@ -113,6 +113,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const uint32_t full_leader = mapa_u32(smem_u32(&bar_full[0]), 0);
     const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]), sB_u = smem_u32(sB);
     uint32_t stage = 0, phase = 0;
+    const uint64_t pol_w = l2_policy_evict_last();
     for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
       for (int t = nh - 2; t >= 0; --t) {
         const int n_halves = args.prog[t + 1].n_halves, k_chunks = args.prog[t + 1].k_chunks;
@@ -122,7 +123,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
             mbar_wait_a(empty0 + stage * 8, phase ^ 1);
             if (elect_one()) {
               if (leader) mbar_arrive_expect_tx_a(full0 + stage * 8, 2 * B_STAGE_BYTES);
-              tma_load_2d_pair_a(sB_u + stage * B_STAGE_BYTES, &tmW, full_leader + stage * 8, kc * 64, row_base + h * HALF_N);
+              tma_load_2d_pair_hint_a(sB_u + stage * B_STAGE_BYTES, &tmW, full_leader + stage * 8, kc * 64, row_base + h * HALF_N, pol_w);
             }
             __syncwarp();
             if (++stage == B_STAGES) { stage = 0; phase ^= 1; }
@@ -200,6 +201,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const uint32_t wr0 = smem_u32(&bar_q_written[0]), rl0 = smem_u32(&bar_q_released[0]), sA_u = smem_u32(sA);
     uint32_t cnt = 0;
     int pending = -1;
+    const uint64_t pol_s = l2_policy_evict_first();
     for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
       const int tile = 2 * tp + int(rank);
       const bool tile_ok = tile < args.n_tiles;
@@ -211,10 +213,8 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           mbar_wait_a(wr0 + Q * 8, (cnt >> Q) & 1u);
           if (elect_one()) {
             if (do_store) {
-              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-                           ::"l"(&tmDys), "r"(sA_u + (2 * Q) * A_CHUNK_BYTES), "r"(Q * 128), "r"(grow0) : "memory");
-              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-                           ::"l"(&tmDys), "r"(sA_u + (2 * Q + 1) * A_CHUNK_BYTES), "r"(Q * 128 + 64), "r"(grow0) : "memory");
+              tma_store_2d_hint_a(&tmDys, sA_u + (2 * Q) * A_CHUNK_BYTES, Q * 128, grow0, pol_s);
+              tma_store_2d_hint_a(&tmDys, sA_u + (2 * Q + 1) * A_CHUNK_BYTES, Q * 128 + 64, grow0, pol_s);
               tma_store_commit();
               asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
               if (pending >= 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(rl0 + pending * 8) : "memory");
@@ -310,58 +310,81 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
 
         // ---- column sums of this warp's 32 columns, once all 16 warps have written that quarter
         {
-          // warp w owns columns [32w, 32w+32): lane = (row set, bf16x2 word).  Lanes 0-15 walk the rows with bit 2
-          // clear, lanes 16-31 the same rows ^ 4: the SW128 XOR then puts the two half-warps on disjoint bank groups.
+          // warp w owns columns [32w, 32w+32) = four 16-byte pieces of one 64-column chunk.  lane = (piece, row class r0):
+          // it walks the 16 rows r0 + 8i of its piece with LDS.128 at constant offsets (the SW128 XOR depends on r & 7 = r0
+          // only; the eight row classes of a piece cover all 32 banks, so the loads are conflict-free), then the eight
+          // row classes are folded with a halving butterfly (fixed order).
           const int cw = warp * 32;
           const bool cols_valid = cw < n_halves * 256;
           const bool want_xyz = args.xyzsum_slot[t] >= 0;
           const bool do_sums = want_xyz || args.colsum_slot[t] >= 0;
-          const int word = lane & 15, rpar = lane >> 4;
-          float s0 = 0.f, s1 = 0.f, sx0 = 0.f, sx1 = 0.f, sy0 = 0.f, sy1 = 0.f, sz0 = 0.f, sz1 = 0.f;
+          const uint32_t r0 = uint32_t(lane) & 7u, pl = uint32_t(lane) >> 3;
+          float s[8], sx[8], sy[8], sz[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) { s[k] = 0.f; sx[k] = 0.f; sy[k] = 0.f; sz[k] = 0.f; }
           if (cols_valid) {
             mbar_wait(&bar_q_written[warp >> 2], ((wpar >> (warp >> 2)) & 1u) ^ 1u);
           }
           if (cols_valid && do_sums) {
-            const uint32_t cb = smem_u32(sA) + uint32_t(cw >> 6) * A_CHUNK_BYTES;
-            const uint32_t xb = smem_u32(s_xyz);
-            const uint32_t colw = uint32_t(cw & 63) / 2 + word;            // bf16x2 word index within the 64-column chunk row
+            const uint32_t piece = uint32_t(warp & 1) * 4u + pl;
+            const uint32_t a0 = smem_u32(sA) + uint32_t(cw >> 6) * A_CHUNK_BYTES + r0 * 128u + ((piece ^ r0) << 4);
+            const uint32_t xb = smem_u32(s_xyz) + r0 * 4u;
             if (!want_xyz) {
-#pragma unroll 8
-              for (int i = 0; i < TILE_M / 2; ++i) {
-                const uint32_t r = (uint32_t(i & 3) | (uint32_t(i >> 2) << 3)) ^ (uint32_t(rpar) << 2);
-                const uint32_t w = lds_u32(cb + r * 128u + ((((colw >> 2) ^ (r & 7u)) << 4) | ((colw & 3u) << 2)));
-                s0 += bf16_lo_to_f32(w); s1 += bf16_hi_to_f32(w);
+#pragma unroll
+              for (int i = 0; i < TILE_M / 8; ++i) {
+                uint32_t w0, w1, w2, w3;
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(a0 + uint32_t(i) * 1024u));
+                s[0] += bf16_lo_to_f32(w0); s[1] += bf16_hi_to_f32(w0); s[2] += bf16_lo_to_f32(w1); s[3] += bf16_hi_to_f32(w1);
+                s[4] += bf16_lo_to_f32(w2); s[5] += bf16_hi_to_f32(w2); s[6] += bf16_lo_to_f32(w3); s[7] += bf16_hi_to_f32(w3);
               }
             } else {
 #pragma unroll 4
-              for (int i = 0; i < TILE_M / 2; ++i) {
-                const uint32_t r = (uint32_t(i & 3) | (uint32_t(i >> 2) << 3)) ^ (uint32_t(rpar) << 2);
-                const uint32_t w = lds_u32(cb + r * 128u + ((((colw >> 2) ^ (r & 7u)) << 4) | ((colw & 3u) << 2)));
-                const float lo = bf16_lo_to_f32(w), hi = bf16_hi_to_f32(w);
-                const float x = lds_f32(xb + r * 4u), y = lds_f32(xb + (TILE_M + r) * 4u), z = lds_f32(xb + (2 * TILE_M + r) * 4u);
-                s0 += lo; s1 += hi;
-                sx0 += x * lo; sx1 += x * hi; sy0 += y * lo; sy1 += y * hi; sz0 += z * lo; sz1 += z * hi;
+              for (int i = 0; i < TILE_M / 8; ++i) {
+                uint32_t w[4];
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(a0 + uint32_t(i) * 1024u));
+                const float x = lds_f32(xb + uint32_t(i) * 32u), y = lds_f32(xb + uint32_t(TILE_M + 8 * i) * 4u),
+                            z = lds_f32(xb + uint32_t(2 * TILE_M + 8 * i) * 4u);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const float lo = bf16_lo_to_f32(w[k]), hi = bf16_hi_to_f32(w[k]);
+                  s[2 * k] += lo; s[2 * k + 1] += hi;
+                  sx[2 * k] += x * lo; sx[2 * k + 1] += x * hi;
+                  sy[2 * k] += y * lo; sy[2 * k + 1] += y * hi;
+                  sz[2 * k] += z * lo; sz[2 * k + 1] += z * hi;
+                }
               }
             }
           }
           if (cols_valid) { __syncwarp(); if (lane == 0) mbar_arrive(&bar_q_released[warp >> 2]); }
-          // combine the two row sets (fixed order)
-          s0 += __shfl_down_sync(0xffffffffu, s0, 16); s1 += __shfl_down_sync(0xffffffffu, s1, 16);
-          if (want_xyz) {
-            sx0 += __shfl_down_sync(0xffffffffu, sx0, 16); sx1 += __shfl_down_sync(0xffffffffu, sx1, 16);
-            sy0 += __shfl_down_sync(0xffffffffu, sy0, 16); sy1 += __shfl_down_sync(0xffffffffu, sy1, 16);
-            sz0 += __shfl_down_sync(0xffffffffu, sz0, 16); sz1 += __shfl_down_sync(0xffffffffu, sz1, 16);
-          }
-          if (tile_ok && rpar == 0 && do_sums) {
+          // fold the eight row classes: after the three steps lane (piece, r0) holds column 8*piece + 4*b0 + 2*b1 + b2 of r0
+          auto fold8 = [&](float (&v)[8]) -> float {
+            const bool b0 = lane & 1, b1 = lane & 2, b2 = lane & 4;
+            float t4[4], t2[2];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const float keep = b0 ? v[k + 4] : v[k], send = b0 ? v[k] : v[k + 4];
+              t4[k] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+            }
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              const float keep = b1 ? t4[k + 2] : t4[k], send = b1 ? t4[k] : t4[k + 2];
+              t2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+            const float keep = b2 ? t2[1] : t2[0], send = b2 ? t2[0] : t2[1];
+            return keep + __shfl_xor_sync(0xffffffffu, send, 4);
+          };
+          const float cs = fold8(s);
+          float cx = 0.f, cy = 0.f, cz = 0.f;
+          if (want_xyz) { cx = fold8(sx); cy = fold8(sy); cz = fold8(sz); }
+          if (tile_ok && cols_valid && do_sums) {
             float* part = args.tile_part + size_t(tile) * args.part_stride;
-            const int col = cw + word * 2;
-            if (args.colsum_slot[t] >= 0)
-              *reinterpret_cast<float2*>(part + args.colsum_slot[t] * FH + col) = make_float2(s0, s1);
+            const int col = cw + int(pl) * 8 + ((lane & 1) << 2) + (lane & 2) + ((lane & 4) >> 2);
+            if (args.colsum_slot[t] >= 0) part[args.colsum_slot[t] * FH + col] = cs;
             if (want_xyz) {
               const int sl = args.xyzsum_slot[t];
-              *reinterpret_cast<float2*>(part + (sl + 0) * FH + col) = make_float2(sx0, sx1);
-              *reinterpret_cast<float2*>(part + (sl + 1) * FH + col) = make_float2(sy0, sy1);
-              *reinterpret_cast<float2*>(part + (sl + 2) * FH + col) = make_float2(sz0, sz1);
+              part[(sl + 0) * FH + col] = cx;
+              part[(sl + 1) * FH + col] = cy;
+              part[(sl + 2) * FH + col] = cz;
             }
           }
         }

@@ -166,6 +166,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       const uint32_t full_leader = mapa_u32(smem_u32(&bar_full[0]), 0);
       const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]), sB_u = smem_u32(sB);
       uint32_t stage = 0, phase = 0;
+      const uint64_t pol_w = l2_policy_evict_last();    // 3.4 MB of weights, re-read by every tile
       for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
         for (int l = 0; l < nh; ++l) {
           if (!args.prog[l].has_mma) continue;
@@ -176,7 +177,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
               mbar_wait_a(empty0 + stage * 8, phase ^ 1);
               if (elect_one()) {
                 if (leader) mbar_arrive_expect_tx_a(full0 + stage * 8, 2 * P_STAGE_BYTES);
-                tma_load_2d_pair_a(sB_u + stage * P_STAGE_BYTES, &tmW, full_leader + stage * 8, kc * 64, row_base + h * HALF_N);
+                tma_load_2d_pair_hint_a(sB_u + stage * P_STAGE_BYTES, &tmW, full_leader + stage * 8, kc * 64, row_base + h * HALF_N, pol_w);
               }
               __syncwarp();
               if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
@@ -267,6 +268,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       const uint32_t wr0 = smem_u32(&bar_q_written[0]), st0 = smem_u32(&bar_q_stashed[0]), sA_u = smem_u32(sA);
       uint32_t cnt = 0;            // bit Q: parity of the number of quarter-Q hand-overs so far
       int pending = -1;            // quarter whose store is still in flight (its q_stashed arrive is owed)
+      const uint64_t pol_s = l2_policy_evict_first();   // the stash streams out: it must not push the weight blocks out of L2
       for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
         const int tile = 2 * tp + int(rank);
         const bool tile_ok = tile < args.n_tiles;
@@ -277,10 +279,8 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
             mbar_wait_a(wr0 + Q * 8, (cnt >> Q) & 1u);
             if (elect_one()) {
               if (tile_ok) {
-                asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-                             ::"l"(&tmActs), "r"(sA_u + (2 * Q) * A_CHUNK_BYTES), "r"(Q * 128), "r"(grow0) : "memory");
-                asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-                             ::"l"(&tmActs), "r"(sA_u + (2 * Q + 1) * A_CHUNK_BYTES), "r"(Q * 128 + 64), "r"(grow0) : "memory");
+                tma_store_2d_hint_a(&tmActs, sA_u + (2 * Q) * A_CHUNK_BYTES, Q * 128, grow0, pol_s);
+                tma_store_2d_hint_a(&tmActs, sA_u + (2 * Q + 1) * A_CHUNK_BYTES, Q * 128 + 64, grow0, pol_s);
                 tma_store_commit();
                 // keep one store in flight: everything but the group just committed has been read out of shared memory
                 asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
