@@ -82,8 +82,10 @@ def test_strict_shuffle_two_ranks_reproduce_one_rank(tmp_path):
     np.testing.assert_allclose(l2, l1, rtol=2e-5)
     assert z1.shape == z2.shape == (8, 16)
     # Adam's first steps move every element by ~lr * sign(g): an element whose gradient is within rounding noise of zero
-    # may step the other way, so the bound is "all but a sliver agree to 2e-5, none differs by more than steps * 2 lr"
-    _assert_close(z2, z1, 2e-5, 6 * 2 * 1e-3, "latent codes")
+    # may step the other way, so the bound is "all but a sliver agree to atol, none differs by more than steps * 2 lr".
+    # A summation-order difference of 1e-7 in a decoder weight can flip its bf16 rounding in the next step's pack, which
+    # moves the latent gradients by ~1e-3 relative: the codes (lr 1e-3, 6 steps) agree to ~1e-5, bounded here by 1e-4.
+    _assert_close(z2, z1, 1e-4, 6 * 2 * 1e-3, "latent codes")
     for k in m1:
         _assert_close(m2[k], m1[k], 2e-5, 6 * 2 * 1e-4, k)
 
