@@ -65,9 +65,11 @@ def _load(exp, epoch):
 
 
 def _assert_close(a, b, atol, hard, what, frac=2e-3):
+    """All but a sliver (``frac`` of the elements, at least three) agree to ``atol``; none differs by more than ``hard``."""
     d = (a.float() - b.float()).abs()
     assert float(d.max()) <= hard + 1e-6, (what, float(d.max()))
-    assert float((d > atol).float().mean()) <= frac, (what, float((d > atol).float().mean()))
+    n_out = int((d > atol).sum())
+    assert n_out <= max(3, int(frac * d.numel())), (what, n_out, d.numel())
 
 
 def test_strict_shuffle_two_ranks_reproduce_one_rank(tmp_path):
@@ -85,7 +87,7 @@ def test_strict_shuffle_two_ranks_reproduce_one_rank(tmp_path):
     # may step the other way, so the bound is "all but a sliver agree to atol, none differs by more than steps * 2 lr".
     # A summation-order difference of 1e-7 in a decoder weight can flip its bf16 rounding in the next step's pack, which
     # moves the latent gradients by ~1e-3 relative: the codes (lr 1e-3, 6 steps) agree to ~1e-5, bounded here by 1e-4.
-    _assert_close(z2, z1, 1e-4, 6 * 2 * 1e-3, "latent codes", frac=0.03)      # 128 elements: at most three sign flips
+    _assert_close(z2, z1, 1e-4, 6 * 2 * 1e-3, "latent codes")
     for k in m1:
         _assert_close(m2[k], m1[k], 2e-5, 6 * 2 * 1e-4, k)
 
