@@ -96,3 +96,25 @@ def test_sampler_host_logic(tmp_path):
     for n in (1, 2, 3, 17, 256, 1000, 65537):
         assert sorted(lib.dsdf_sample_perm(i, n, 2024, 5, 1) for i in range(n)) == list(range(n))
     assert [lib.dsdf_sample_perm(i, 1000, 1, 0, 0) for i in range(8)] != [lib.dsdf_sample_perm(i, 1000, 2, 0, 0) for i in range(8)]
+
+
+def test_torchscript_export_reproduces_reference_cpp_model(tmp_path):
+    """deepsdf_b200.export (create_libtorch_executable.py:4-23): the exported TorchScript graph of a decoder carrying the
+    weights of the reference's experiments/corner_spheres_only_small_network/cpp_model.pt must give that file's outputs."""
+    from deepsdf_b200 import export as E
+    z = np.load(os.path.join(ROOT, "tests", "golden", "small_net_export.npz"))
+    params = {k[len("param::"):]: torch.from_numpy(z[k]) for k in z.files if k.startswith("param::")}
+    m = build_module(META["small_4x64_L2_tanh"]["spec"], params)
+    x = torch.from_numpy(z["input"])
+    sm = E.to_torchscript(m, x[:1], str(tmp_path / "cpp_model.pt"))
+    assert np.abs(sm(x).numpy() - z["output"]).max() <= 1e-6
+    back = torch.jit.load(str(tmp_path / "cpp_model.pt"))                     # what the C++ consumer does
+    assert torch.equal(back(x), sm(x))
+    # a LayerNorm network and a latent_in network go through the same graph builder
+    for name in ("layernorm_4x48_L3", "mid_6x128_L1"):
+        spec = META[name]["spec"]
+        mod = build_module(spec)
+        g = E.exported_module(mod)
+        xin = torch.randn(5, spec["latent_size"] + 3)
+        want = O.decoder_forward(O.OracleSpec(**spec), {k: v.detach() for k, v in mod.state_dict().items()}, xin, training=False)
+        assert g(xin).shape == (5, 1) and float((g(xin) - want).abs().max()) <= 1e-6
