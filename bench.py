@@ -346,7 +346,7 @@ def run_gpu(args):
         "roofline": roofline,
         "cpu_baseline": cpu,
         "clocks": clk,
-        "grid": extras.get("grid"), "latent_opt": extras.get("latent_opt"), "sampler": extras.get("sampler"), "extras_error": extras.get("error"),
+        "grid": extras.get("grid"), "latent_opt": extras.get("latent_opt"), "sampler": extras.get("sampler"), "isosurface": extras.get("isosurface"), "extras_error": extras.get("error"),
         "loss_last_step": loss_dev,
         "loss_last_step_e2e": [float(x) for x in last],
     }
@@ -407,6 +407,25 @@ def run_extras(trainer, dev, rank, world, barrier, max_over_ranks):
     del xyz, ts, sdf, G
     eng._bufs, eng._bufs_key = {}, None
     torch.cuda.empty_cache()
+
+    # iso-surface of a device-resident 512^3 volume (the tail of create_mesh, mesh.py:88-155): analytic sphere, rank 0's GPU
+    try:
+        from deepsdf_b200.mesh import extract_isosurface
+        gl = torch.linspace(-1, 1, NG, device=dev)
+        vol = (torch.sqrt(gl[:, None, None] ** 2 + gl[None, :, None] ** 2 + gl[None, None, :] ** 2) - 0.6).contiguous()
+        tri = extract_isosurface(vol, (-1, -1, -1), 2.0 / (NG - 1))
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); tri = extract_isosurface(vol, (-1, -1, -1), 2.0 / (NG - 1)); b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b)
+        out["isosurface"] = {"N": NG, "ms": ms, "triangles": int(tri.shape[0]), "voxels_per_s": NG ** 3 / (ms / 1e3),
+                             "volume_GBps": 2 * vol.numel() * 4 / (ms / 1e3) / 1e9,
+                             "what": "marching tetrahedra, count + scan + emit, volume read twice (algorithmic bytes = 2 x 4 B/voxel)"}
+        del vol, tri, gl
+        torch.cuda.empty_cache()
+    except Exception as exc:  # noqa: BLE001
+        out["isosurface"] = {"error": repr(exc)[:200]}
 
     # device-resident dataset + sampler (deep_sdf/data.py:75-110 on the GPU): 64 scenes x 16384 of 100000 stored rows
     from deepsdf_b200.data import DeviceSDFSamples

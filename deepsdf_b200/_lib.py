@@ -71,6 +71,9 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_grid_points": (C.c_int, [i32, i64, i64, vp, vp]),
         "dsdf_sample_batch": (C.c_int, [vp, vp, vp, i32, i32, u64, vp, vp]),
         "dsdf_sample_perm": (u32, [u32, u32, u64, i64, i32]),
+        "dsdf_iso_num_blocks": (i64, [i32, i32, i32]),
+        "dsdf_iso_count": (C.c_int, [vp, i32, i32, i32, f32, vp, vp]),
+        "dsdf_iso_emit": (C.c_int, [vp, i32, i32, i32, f32, P(f32), P(f32), vp, vp, vp]),
         "dsdf_selftest_umma_pair": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp]),
         "dsdf_selftest_umma": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint,
                                          C.c_uint, vp]),

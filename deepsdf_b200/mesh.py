@@ -1,5 +1,5 @@
-"""Grid evaluation of ``deep_sdf/mesh.py:26-73`` ``create_mesh`` (the SDF volume; marching cubes / ply export stay on
-the host and are out of scope) with the optional derivative outputs the optimisation / analysis consumers need
+"""Grid evaluation of ``deep_sdf/mesh.py:26-73`` ``create_mesh`` (the SDF volume), the iso-surface + ply tail of it
+(``convert_sdf_samples_to_ply``, mesh.py:88-155, on the device) and the optional derivative outputs the optimisation / analysis consumers need
 (``deep_sdf/mesh.py:405-454``): dSDF/dxyz and dSDF/dlatent for every grid point.
 
 The N^3 grid is generated on the device chunk by chunk (``dsdf_grid_points``), every chunk runs the fused forward (and,
@@ -73,3 +73,76 @@ def create_mesh_sdf(decoder, latent_vec: torch.Tensor, N: int = 256, max_batch: 
     if not with_grad:
         return sdf.view(shape)
     return sdf.view(shape), dxyz.view(*shape, 3), dlat.view(*shape, -1)
+
+
+# ---------------------------------------------------------------------------------------------- iso-surface + ply
+def extract_isosurface(volume: torch.Tensor, voxel_grid_origin=(-1.0, -1.0, -1.0), voxel_size=1.0, level: float = 0.0) -> torch.Tensor:
+    """Triangle soup [T, 3, 3] (device) of the ``level`` set of ``volume`` [nx, ny, nz] (fp32 CUDA tensor in create_mesh's
+    ordering): vertex = voxel_grid_origin + grid_coordinate * voxel_size, normals towards increasing SDF.  Marching
+    tetrahedra in ``libdsdf_b200.so`` (``csrc/isosurface.cu``) - the role of ``skimage.measure.marching_cubes`` in
+    ``convert_sdf_samples_to_ply`` (deep_sdf/mesh.py:113-115), with the volume never leaving the device."""
+    import ctypes as C
+    L.require_cuda(volume)
+    if volume.dim() != 3 or volume.dtype != torch.float32:
+        raise L.DsdfError("extract_isosurface needs a 3-D fp32 volume")
+    volume = volume.contiguous()
+    nx, ny, nz = (int(s) for s in volume.shape)
+    if not isinstance(voxel_size, (list, tuple)):
+        voxel_size = [voxel_size] * 3                                            # mesh.py:111-112
+    lib, dev = L.lib(), volume.device
+    nb = int(lib.dsdf_iso_num_blocks(nx, ny, nz))
+    if nb == 0:
+        return torch.zeros(0, 3, 3, device=dev)
+    counts = torch.empty(nb, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        L.check(lib.dsdf_iso_count(volume.data_ptr(), nx, ny, nz, float(level), counts.data_ptr(), L.stream_ptr(dev)))
+        incl = torch.cumsum(counts, 0, dtype=torch.int64)                        # plumbing: scan of the per-block counts
+        offsets = (incl - counts).contiguous()
+        total = int(incl[-1])
+        verts = torch.empty(total, 3, 3, device=dev)
+        if total:
+            o3 = (C.c_float * 3)(*[float(x) for x in voxel_grid_origin])
+            v3 = (C.c_float * 3)(*[float(x) for x in voxel_size])
+            L.check(lib.dsdf_iso_emit(volume.data_ptr(), nx, ny, nz, float(level), o3, v3, offsets.data_ptr(), verts.data_ptr(),
+                                      L.stream_ptr(dev)))
+    return verts
+
+
+def write_ply(ply_filename_out: str, triangles, offset=None, scale=None) -> None:
+    """Binary little-endian ply with the elements ``convert_sdf_samples_to_ply`` writes through plyfile (mesh.py:131-146):
+    ``vertex`` (float x, y, z) and ``face`` (list uchar int vertex_indices); ``scale`` / ``offset`` as in mesh.py:123-127."""
+    import numpy as np
+    tri = triangles.detach().cpu().numpy() if isinstance(triangles, torch.Tensor) else np.asarray(triangles)
+    pts = tri.reshape(-1, 3).astype(np.float32)
+    if scale is not None:
+        pts = pts / scale
+    if offset is not None:
+        pts = pts - offset
+    n_faces = pts.shape[0] // 3
+    verts = np.zeros(pts.shape[0], dtype=[("x", "<f4"), ("y", "<f4"), ("z", "<f4")])
+    verts["x"], verts["y"], verts["z"] = pts[:, 0], pts[:, 1], pts[:, 2]
+    faces = np.zeros(n_faces, dtype=[("n", "u1"), ("vertex_indices", "<i4", (3,))])
+    faces["n"] = 3
+    faces["vertex_indices"] = np.arange(3 * n_faces, dtype=np.int32).reshape(n_faces, 3)
+    header = ("ply\nformat binary_little_endian 1.0\nelement vertex {}\nproperty float x\nproperty float y\nproperty float z\n"
+              "element face {}\nproperty list uchar int vertex_indices\nend_header\n").format(pts.shape[0], n_faces)
+    with open(ply_filename_out, "wb") as f:
+        f.write(header.encode("ascii"))
+        f.write(verts.tobytes())
+        f.write(faces.tobytes())
+
+
+def convert_sdf_samples_to_ply(pytorch_3d_sdf_tensor: torch.Tensor, voxel_grid_origin, voxel_size, ply_filename_out: str,
+                               offset=None, scale=None) -> int:
+    """Same signature as deep_sdf/mesh.py:88-95, for a DEVICE tensor (create_mesh_sdf's result): iso-surface at level 0 on
+    the GPU, then the ply file.  Returns the number of triangles."""
+    tri = extract_isosurface(pytorch_3d_sdf_tensor.to(torch.float32), voxel_grid_origin, voxel_size, 0.0)
+    write_ply(ply_filename_out, tri, offset, scale)
+    return int(tri.shape[0])
+
+
+def create_mesh(decoder, latent_vec: torch.Tensor, filename: str, N: int = 256, max_batch: int = 1 << 21, offset=None, scale=None) -> int:
+    """deep_sdf/mesh.py:26-85 end to end on the device: grid evaluation (fused forward) + iso-surface + ``<filename>.ply``."""
+    sdf = create_mesh_sdf(decoder, latent_vec, N=N, max_batch=max_batch)
+    voxel_size = 2.0 / (N - 1)                                                   # mesh.py:33-35
+    return convert_sdf_samples_to_ply(sdf, [-1.0, -1.0, -1.0], voxel_size, filename + ".ply", offset, scale)

@@ -111,14 +111,15 @@ def reconstruct_split(experiment_directory: str, checkpoint: str = "latest", dat
     All shapes of a batch are optimised together; ranks take disjoint blocks of the instance list (no collective).
     Per-iteration samples come from the device store with the training sampler (half positive / half negative rows
     without replacement, deep_sdf/data.py:88-99) - upstream shuffles once and takes random contiguous windows
-    (deep_sdf/data.py:113-139), the same distribution.  ``resolution`` > 0 also evaluates create_mesh's grid for every shape
-    and writes ``Meshes/.../<instance>.sdf.npy`` ([N,N,N] fp32); marching cubes / ply stay on the host (skimage absent)."""
+    (deep_sdf/data.py:113-139), the same distribution.  ``resolution`` > 0 also meshes every reconstruction like upstream
+    (``create_mesh``: grid evaluation + iso-surface, both on the device) into ``Meshes/.../<instance>.ply``
+    (deep_sdf/workspace.py:122-135)."""
     import json
     import os
     import numpy as np
     from . import sharding
     from .data import DeviceSDFSamples, sdf_samples_subdir
-    from .mesh import create_mesh_sdf
+    from .mesh import create_mesh
     dev = torch.device(device)
     decoder, specs, saved_epoch = load_decoder(experiment_directory, checkpoint, dev)
     data_source = data_source or specs["DataSource"]
@@ -159,9 +160,9 @@ def reconstruct_split(experiment_directory: str, checkpoint: str = "latest", dat
             torch.save(lat[j].reshape(1, 1, -1).clone(), code_fn)
             errs[os.path.join(d, c, i)] = float(final[j])
             if resolution > 0:
-                mesh_fn = os.path.join(root, reconstruction_meshes_subdir, d, c, i + ".sdf.npy")
+                mesh_fn = os.path.join(root, reconstruction_meshes_subdir, d, c, i)
                 os.makedirs(os.path.dirname(mesh_fn), exist_ok=True)
-                np.save(mesh_fn, create_mesh_sdf(decoder, lat[j], N=resolution).reshape(resolution, resolution, resolution).cpu().numpy())
+                create_mesh(decoder, lat[j], mesh_fn, N=resolution)                      # writes <instance>.ply
     return {"epoch": saved_epoch, "loss": errs}
 
 
@@ -177,7 +178,7 @@ if __name__ == "__main__":
     ap.add_argument("--num-samples", type=int, default=8000)
     ap.add_argument("--skip", action="store_true", help="skip instances whose code file already exists")
     ap.add_argument("--shapes-per-batch", type=int, default=1024)
-    ap.add_argument("--resolution", type=int, default=0, help="also write the [N,N,N] SDF volume of every reconstruction")
+    ap.add_argument("--resolution", type=int, default=0, help="also mesh every reconstruction on an N^3 grid (Meshes/.../<instance>.ply)")
     ap.add_argument("--seed", type=int, default=0)
     a = ap.parse_args()
     if not torch.cuda.is_available():

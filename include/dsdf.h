@@ -214,6 +214,20 @@ int dsdf_sample_batch(const float* store, const int64_t* meta, const int64_t* sc
 /* the bijection itself, on the host: source row of batch position i within the scene's positive / negative rows */
 uint32_t dsdf_sample_perm(uint32_t i, uint32_t n, uint64_t seed, int64_t scene, int32_t negative);
 
+/* ------------------------------------------------------------------------------------------------
+ * Iso-surface of the device-resident SDF volume (the tail of create_mesh: deep_sdf/mesh.py:88-155 hands a host copy of
+ * the [N,N,N] tensor to skimage.measure.marching_cubes).  Marching TETRAHEDRA over the six Kuhn tetrahedra of every cube
+ * (csrc/isosurface.cu): a watertight triangle soup, not skimage's Lewiner triangulation.
+ * volume[(ix*ny + iy)*nz + iz] fp32 (create_mesh's ordering), inside <=> value < level.
+ *   1. dsdf_iso_count  -> block_counts[dsdf_iso_num_blocks(nx,ny,nz)] (int32 triangles per block of 256 cubes)
+ *   2. the caller forms block_offsets = exclusive prefix sum (int64) and allocates verts [3 * n_triangles][3] fp32
+ *   3. dsdf_iso_emit   -> verts: triangle t = rows 3t, 3t+1, 3t+2, normal towards increasing SDF;
+ *                         vertex = origin3 + grid_coordinate * voxel3 (origin3 / voxel3 are HOST arrays of 3 floats). */
+int64_t dsdf_iso_num_blocks(int32_t nx, int32_t ny, int32_t nz);
+int dsdf_iso_count(const float* volume, int32_t nx, int32_t ny, int32_t nz, float level, int32_t* block_counts, void* stream);
+int dsdf_iso_emit(const float* volume, int32_t nx, int32_t ny, int32_t nz, float level, const float* origin3,
+                  const float* voxel3, const int64_t* block_offsets, float* verts, void* stream);
+
 /* torch.optim.Adam update of one flat fp32 tensor (dense, no weight decay); step counts from 1; g is multiplied by
  * grad_scale and, if grad_scale_dev != NULL, by the device scalar *grad_scale_dev first (gradient clipping without a
  * host round trip). */
