@@ -68,9 +68,12 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_pack_weights": (C.c_int, [P(NetDesc), P(Params), vp, vp]),
         "dsdf_scene_prepare": (C.c_int, [P(NetDesc), vp, vp, vp, i32, f32, vp, vp]),
         "dsdf_fused_forward": (C.c_int, [P(NetDesc), vp, vp, vp, vp, i32, i64, vp, P(TrainIO), vp]),
+        "dsdf_fused_forward_rows": (C.c_int, [P(NetDesc), vp, vp, i32, i64, vp, P(TrainIO), vp]),
         "dsdf_grid_points": (C.c_int, [i32, i64, i64, vp, vp]),
         "dsdf_sample_batch": (C.c_int, [vp, vp, vp, i32, i32, u64, vp, vp]),
         "dsdf_sample_perm": (u32, [u32, u32, u64, i64, i32]),
+        "dsdf_tile_queries": (C.c_int, [vp, i32, vp, i32, i32, i64, i64, P(f32), vp, vp]),
+        "dsdf_cap_sdf": (C.c_int, [vp, vp, i64, i32, vp, i32, i64, i32, P(i32), P(C.c_double), P(C.c_double), P(i32), vp]),
         "dsdf_iso_num_blocks": (i64, [i32, i32, i32]),
         "dsdf_iso_count": (C.c_int, [vp, i32, i32, i32, f32, vp, vp]),
         "dsdf_iso_emit": (C.c_int, [vp, i32, i32, i32, f32, P(f32), P(f32), vp, vp, vp]),

@@ -47,10 +47,11 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"
 //   sb       shared-memory bias (already multiplied by the dropout scale); swx xyz weight rows (same scaling) or null
 //   keep16   low 16 bits: Philox keep bits of these columns (all ones when the layer has no dropout)
 // Returns the 16 gate bits (relu AND keep); adds this row's share of the last-layer dot product to ydot.
-template <bool kTrain>
+template <bool kTrain, bool kRowLat>
 __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, float ascale, uint32_t sb, bool has_xyz, uint32_t swx,
                                                float x, float y, float z, uint32_t keep16, bool is_last, uint32_t swl, uint32_t sA,
-                                               uint32_t row, uint32_t c0, float& ydot) {
+                                               uint32_t row, uint32_t c0, float& ydot, const float* wl, int n_rl,
+                                               const float (&rl)[4]) {
   // sb / swx / swl / sA are SHARED-space byte addresses (of this pass's first column where they are per column)
   float v[16];
   if (has_acc) {
@@ -84,6 +85,21 @@ __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, flo
       v[4 * k + 3] += x * wx.w + y * wy.w + z * wz.w;
     }
   }
+  if (kRowLat && wl != nullptr) {
+    // row-latent mode: this row's own code times the latent weight columns (fp32, read through L1: the mode serves a few
+    // hundred thousand rows per call, shared memory has no room for the table, and only two layers come here)
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+      if (d < n_rl) {
+        const float s = rl[d] * ascale;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float4 w = __ldg(reinterpret_cast<const float4*>(wl + size_t(d) * FH) + k);
+          v[4 * k + 0] += s * w.x; v[4 * k + 1] += s * w.y; v[4 * k + 2] += s * w.z; v[4 * k + 3] += s * w.w;
+        }
+      }
+    }
+  }
   uint32_t gate = 0;
   if (kTrain) {
     uint32_t sg = 0;
@@ -114,7 +130,7 @@ __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, flo
 
 }  // namespace
 
-template <bool kTrain>
+template <bool kTrain, bool kRowLat>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1)
 chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmActs,
                      const __grid_constant__ FwdArgs args) {
@@ -329,8 +345,14 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         const float* pt = args.xyz + (int64_t(tile_c) * TILE_M + rt) * args.xyz_stride;
         px = __ldg(pt); py = __ldg(pt + 1); pz = __ldg(pt + 2);
       }
-      const int scene = __ldg(args.tile_scene + tile_c);
+      const int scene = kRowLat ? 0 : __ldg(args.tile_scene + tile_c);
       float ydot = 0.0f;
+      float rl[4] = {0.f, 0.f, 0.f, 0.f};
+      if (kRowLat && valid) {
+        const float* pl = args.row_lat + (int64_t(tile_c) * TILE_M + rt) * args.row_lat_stride;
+#pragma unroll
+        for (int d = 0; d < 4; ++d) if (d < args.row_lat_dim) rl[d] = __ldg(pl + d);
+      }
 
       for (int l = 0; l < nh; ++l) {
         const ChainLayer& L = args.prog[l];
@@ -342,7 +364,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         const uint32_t sb = smem_u32(s_bias) + uint32_t(l & 1) * FH * 4;
         // ---- before the accumulators are ready: stage this layer's bias (+ xyz weights), draw the first keep words
         {
-          const float* src = (L.bias_slot >= 0) ? (args.cbias + (size_t(scene) * 2 + L.bias_slot) * FH) : args.bias[l];
+          const float* src = (L.bias_slot >= 0 && !kRowLat) ? (args.cbias + (size_t(scene) * 2 + L.bias_slot) * FH) : args.bias[l];
           s_bias[(l & 1) * FH + tid] = __ldg(src + tid) * ascale;
           if (L.has_xyz) {
             const float* wsrc = args.wxyz[l];
@@ -367,14 +389,17 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           gdst = args.bitmask + ((size_t(l) * tiles_alloc + tile) * MASK_WORDS + j) * TILE_M + rt;   // word 4*Q + j at + 4*Q*128
 
         // One 128-column quarter: two 16-column passes straight from TMEM into the A tile.
+        const float* wl_layer = (kRowLat && L.bias_slot >= 0) ? args.wlat + size_t(L.bias_slot) * args.row_lat_dim * FH : nullptr;
         auto quarter = [&](int Q, uint32_t keep) {
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
           // the previous layer's stash of this quarter must have been read out of the tile
           if (stash && ((wany >> Q) & 1u)) mbar_wait(&bar_q_stashed[Q], ((wpar >> Q) & 1u) ^ 1u);
-          const uint32_t g0 = epi_pass16<kTrain>(tmem_row + c0, has_acc, ascale, sb + c0 * 4, has_xyz, swx + c0 * 4, px, py, pz, keep,
-                                                 last, swl + c0 * 4, sA_a, rt, c0, ydot);
-          const uint32_t g1 = epi_pass16<kTrain>(tmem_row + c0 + 16, has_acc, ascale, sb + (c0 + 16) * 4, has_xyz, swx + (c0 + 16) * 4,
-                                                 px, py, pz, keep >> 16, last, swl + (c0 + 16) * 4, sA_a, rt, c0 + 16, ydot);
+          const uint32_t g0 = epi_pass16<kTrain, kRowLat>(tmem_row + c0, has_acc, ascale, sb + c0 * 4, has_xyz, swx + c0 * 4, px, py, pz,
+                                                          keep, last, swl + c0 * 4, sA_a, rt, c0, ydot,
+                                                          wl_layer ? wl_layer + c0 : nullptr, args.row_lat_dim, rl);
+          const uint32_t g1 = epi_pass16<kTrain, kRowLat>(tmem_row + c0 + 16, has_acc, ascale, sb + (c0 + 16) * 4, has_xyz,
+                                                          swx + (c0 + 16) * 4, px, py, pz, keep >> 16, last, swl + (c0 + 16) * 4, sA_a, rt,
+                                                          c0 + 16, ydot, wl_layer ? wl_layer + c0 + 16 : nullptr, args.row_lat_dim, rl);
           if (kTrain && gdst != nullptr) gdst[size_t(Q) * 4 * TILE_M] = g0 | (g1 << 16);
           fence_proxy_async_smem();
           tc_fence_before();
@@ -469,10 +494,12 @@ static int resident_pairs(K kern, int n_sms) {
 }
 
 int launch_chain_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, const FwdArgs& args, int n_sms, cudaStream_t stream) {
-  auto kern = args.training ? chain_forward_kernel<true> : chain_forward_kernel<false>;
+  const bool rows = args.row_lat != nullptr;
+  auto kern = rows ? (args.training ? chain_forward_kernel<true, true> : chain_forward_kernel<false, true>)
+                   : (args.training ? chain_forward_kernel<true, false> : chain_forward_kernel<false, false>);
   DSDF_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
-  static int max_pairs[2] = {0, 0};
-  int& mp = max_pairs[args.training ? 1 : 0];
+  static int max_pairs[4] = {0, 0, 0, 0};
+  int& mp = max_pairs[(args.training ? 1 : 0) + (rows ? 2 : 0)];
   if (mp == 0) mp = resident_pairs(kern, n_sms);
   const int n_pairs = (args.n_tiles + 1) / 2;
   int grid_pairs = mp;
@@ -484,8 +511,8 @@ int launch_chain_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, cons
 }
 
 int chain_forward_resident_pairs(int n_sms) {
-  cudaFuncSetAttribute(chain_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM);
-  return resident_pairs(chain_forward_kernel<true>, n_sms);
+  cudaFuncSetAttribute(chain_forward_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM);
+  return resident_pairs(chain_forward_kernel<true, false>, n_sms);
 }
 
 }  // namespace dsdf

@@ -64,6 +64,11 @@ struct FwdArgs {
   int32_t dy_unit;                          // gt == null: dy_out = d sdf / d(pre-tanh output)  (input-gradient path)
   const int32_t* tile_rows;                 // [n_tiles] valid rows of each tile (ragged scenes padded to 128), or null
   uint32_t philox_rk[16];                   // Philox round keys of `seed` (common.cuh philox_round_keys)
+  // row-latent mode (every row brings its own latent code, L <= 4: the microstructure consumers of deep_sdf/mesh.py:457-497)
+  const float* row_lat;                     // row r's code at row_lat + r*row_lat_stride, or null (scene mode)
+  int32_t row_lat_stride;
+  int32_t row_lat_dim;                      // L
+  const float* wlat;                        // fp32 [2][L][512]: latent columns of lin0 / the latent_in layer, transposed
 };
 
 struct BwdArgs {

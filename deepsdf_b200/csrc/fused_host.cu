@@ -258,9 +258,9 @@ extern "C" int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, f
   return 0;
 }
 
-extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const float* cbias,
-                                  const int32_t* tile_scene, const float* xyz, int32_t xyz_stride, int64_t n_rows,
-                                  float* sdf_out, const dsdf_train_io* tr, void* stream) {
+static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const float* cbias, const int32_t* tile_scene,
+                              const float* xyz, int32_t xyz_stride, int64_t n_rows, float* sdf_out, const dsdf_train_io* tr,
+                              const float* row_lat, int32_t row_lat_stride, void* stream) {
   if (int e = require_sm100()) return e;
   FusedLayout lo;
   if (int e = fused_layout(desc, &lo)) return e;
@@ -306,6 +306,16 @@ extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, c
   a.dropout_on = tr->dropout_off ? 0 : 1;
   a.dy_unit = tr->dy_unit;
   a.tile_rows = tr->tile_rows;
+  if (row_lat != nullptr) {
+    DSDF_REQUIRE(desc->latent_size <= 4, "row-latent mode supports latent_size <= 4");
+    DSDF_REQUIRE(row_lat_stride >= desc->latent_size, "row_lat_stride must be >= latent_size");
+    a.row_lat = row_lat;
+    a.row_lat_stride = row_lat_stride;
+    a.row_lat_dim = desc->latent_size;
+    a.wlat = reinterpret_cast<const float*>(p + lo.off_wlatT);
+  } else {
+    DSDF_REQUIRE(cbias != nullptr && tile_scene != nullptr, "scene mode needs cbias and tile_scene");
+  }
   if (a.training) {
     DSDF_REQUIRE(tr->n_rows_pad == a.n_rows_pad, "n_rows_pad must be n_rows rounded up to 128");
     if (a.gt) DSDF_REQUIRE(a.dy_out && a.tile_loss, "training with gt needs dy_out and tile_loss");
@@ -317,4 +327,16 @@ extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, c
   const uint64_t acts_rows = tr->acts ? uint64_t(lo.num_hidden) * a.n_rows_pad : uint64_t(lo.fwd_rows);
   if (int e = make_tmap_bf16_2d(&tmActs, acts_ptr, FH, acts_rows, FH * 2, 64, TILE_M)) return e;
   return launch_chain_forward(tmW, tmActs, a, sm_count(), static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const float* cbias,
+                                  const int32_t* tile_scene, const float* xyz, int32_t xyz_stride, int64_t n_rows,
+                                  float* sdf_out, const dsdf_train_io* tr, void* stream) {
+  return fused_forward_impl(desc, pack, cbias, tile_scene, xyz, xyz_stride, n_rows, sdf_out, tr, nullptr, 0, stream);
+}
+
+extern "C" int dsdf_fused_forward_rows(const dsdf_net_desc* desc, const void* pack, const float* queries, int32_t ldq,
+                                       int64_t n_rows, float* sdf_out, const dsdf_train_io* tr, void* stream) {
+  DSDF_REQUIRE(desc != nullptr && queries != nullptr && ldq >= desc->latent_size + 3, "queries must be [n_rows][ldq >= L + 3]");
+  return fused_forward_impl(desc, pack, nullptr, nullptr, queries + desc->latent_size, ldq, n_rows, sdf_out, tr, queries, ldq, stream);
 }

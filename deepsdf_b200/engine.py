@@ -188,6 +188,44 @@ class FusedEngine:
                                               G.stride(0), st))
         return sdf, G
 
+    def sdf_and_input_grad_rows(self, queries: torch.Tensor, G: Optional[torch.Tensor] = None, sdf: Optional[torch.Tensor] = None,
+                                with_grad: bool = True):
+        """Eval-mode SDF [N] (and G [N, L+3] = dSDF/d[latent, xyz]) of ``queries`` [N, L+3] whose rows carry their OWN latent
+        code (``decode_sdf(decoder, None, queries)``, deep_sdf/utils.py:62-63 / mesh.py:490-497), L <= 4, N % 128 == 0.
+        One ``G`` replaces the per-(latent, control point) jvp loop of mesh.py:405-422: the jvp along a control point is
+        ``G[:, i_lat] * basis[:, i_cpt]``."""
+        L.require_cuda(queries)
+        N, width = queries.shape
+        Lz = self.spec.latent_size
+        if N == 0 or (with_grad and N % TILE):
+            raise L.DsdfError("sdf_and_input_grad_rows needs a positive multiple of 128 rows (pad the queries)")
+        assert queries.dtype == torch.float32 and queries.is_contiguous() and width == Lz + 3
+        sdf = sdf if sdf is not None else torch.empty(N, device=self.device)
+        io = L.TrainIO()
+        io.b_last = self._b_last().data_ptr()
+        lib, desc, st = self.lib, self.desc, self._st()
+        if not with_grad:
+            with torch.cuda.device(self.device):
+                L.check(lib.dsdf_fused_forward_rows(C.byref(desc), self.pack.data_ptr(), queries.data_ptr(), width, N, sdf.data_ptr(),
+                                                    C.byref(io), st))
+            return sdf, None
+        b = self.grad_buffers(N)
+        G = G if G is not None else torch.empty(N, Lz + 3, device=self.device)
+        assert G.dtype == torch.float32 and G.shape[0] == N and G.shape[1] >= Lz + 3 and G.stride(1) == 1
+        io.training, io.dropout_off, io.dy_unit = 1, 1, 1
+        io.dy_out = b["dy"].data_ptr()
+        io.bitmask = b["bitmask"].data_ptr()
+        io.n_rows_pad = N
+        lat = self.lat_layer
+        store = 1 | ((1 << lat) if lat > 0 else 0)
+        xyz_ptr = queries.data_ptr() + 4 * Lz
+        with torch.cuda.device(self.device):
+            L.check(lib.dsdf_fused_forward_rows(C.byref(desc), self.pack.data_ptr(), queries.data_ptr(), width, N, sdf.data_ptr(),
+                                                C.byref(io), st))
+            L.check(lib.dsdf_fused_dgrad(C.byref(desc), self.pack.data_ptr(), C.byref(self._tb), xyz_ptr, width, N, 0, store, 0, st))
+            L.check(lib.dsdf_fused_input_grad(C.byref(desc), self.pack.data_ptr(), C.byref(self._tb), N, G.data_ptr(), G.stride(0), st))
+        return sdf, G
+
     def grid_points(self, N: int, i0: int, n: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Rows [i0, i0+n) of create_mesh's N^3 sample grid (deep_sdf/mesh.py:37-53) as [n,3] fp32."""
         out = out if out is not None else torch.empty(n, 3, device=self.device)

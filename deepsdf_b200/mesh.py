@@ -146,3 +146,50 @@ def create_mesh(decoder, latent_vec: torch.Tensor, filename: str, N: int = 256, 
     sdf = create_mesh_sdf(decoder, latent_vec, N=N, max_batch=max_batch)
     voxel_size = 2.0 / (N - 1)                                                   # mesh.py:33-35
     return convert_sdf_samples_to_ply(sdf, [-1.0, -1.0, -1.0], voxel_size, filename + ".ply", offset, scale)
+
+
+# ---------------------------------------------------------------------------------------------- microstructure evaluation
+location_lookup = {"x0": (0, -1), "x1": (0, 1), "y0": (1, -1), "y1": (1, 1), "z0": (2, -1), "z1": (2, 1)}   # mesh.py:157-164
+
+
+def evaluate_network_sdf(decoder, lat_vec_red: torch.Tensor, samples_orig: torch.Tensor, tiling, cap_border_dict=None,
+                         with_grad: bool = False):
+    """The decoder part of ``prepare_samples`` + ``evaluate_network`` (deep_sdf/mesh.py:457-514) for per-vertex latent codes:
+
+      samples   = tiling transform of ``samples_orig`` [N_tot, >=3] into one unit cell              (mesh.py:470-477)
+      sdf       = decode_sdf(decoder, None, hstack([lat_vec_red, samples]))                          (mesh.py:490-495)
+      sdf       = border caps of ``cap_border_dict`` ({"x0": {"cap": +-1, "measure": m}, ...}) and the unit-cube cap  (:499-514)
+
+    Returns ``(sdf [N_tot], dsdf_dlat [N_tot, L] or None)``.  ``dsdf_dlat`` is what the per-(latent, control point) jvp loop
+    of mesh.py:405-422 needs: d sdf / d control point c of code component i = ``dsdf_dlat[:, i] * basis[:, c]`` (zero where a
+    cap decides the value).  FlexiCubes / splinepy (the mesh from ``sdf`` and the spline basis) are not part of this path.
+    Three kernels of libdsdf_b200.so around the fused forward / dgrad / input-gradient launches; nothing leaves the device."""
+    import ctypes as C
+    eng = fused_engine_for(decoder)
+    if eng is None or eng.spec.latent_size > 4:
+        raise L.DsdfError("evaluate_network_sdf needs an 8x512-class decoder with CodeLength <= 4")
+    dev, Lz = eng.device, eng.spec.latent_size
+    so = samples_orig.detach().to(dev, torch.float32).contiguous()
+    lat = lat_vec_red.detach().to(dev, torch.float32).contiguous()
+    n = so.shape[0]
+    if lat.shape != (n, Lz) or so.shape[1] < 3:
+        raise L.DsdfError("lat_vec_red must be [N_tot, L] and samples_orig [N_tot, >= 3]")
+    n_pad = (n + TILE - 1) // TILE * TILE
+    queries = torch.empty(n_pad, Lz + 3, device=dev)
+    lib, st = L.lib(), L.stream_ptr(dev)
+    t3 = (C.c_float * 3)(*[float(t) for t in tiling])
+    with torch.cuda.device(dev):
+        L.check(lib.dsdf_tile_queries(so.data_ptr(), so.stride(0), lat.data_ptr(), lat.stride(0), Lz, n, n_pad, t3, queries.data_ptr(), st))
+    sdf, G = eng.sdf_and_input_grad_rows(queries, with_grad=with_grad)
+    caps = list((cap_border_dict or {}).items())
+    dims = (C.c_int32 * 6)(*([location_lookup[k][0] for k, _ in caps] + [0] * (6 - len(caps))))
+    mult = (C.c_double * 6)(*([float(location_lookup[k][1]) for k, _ in caps] + [0.0] * (6 - len(caps))))
+    meas = (C.c_double * 6)(*([float(v["measure"]) for _, v in caps] + [0.0] * (6 - len(caps))))
+    capv = (C.c_int32 * 6)(*([int(v["cap"]) for _, v in caps] + [1] * (6 - len(caps))))
+    for _, v in caps:
+        if v["cap"] not in (-1, 1):
+            raise ValueError("Cap must be -1 or 1")                                   # mesh.py:509
+    with torch.cuda.device(dev):
+        L.check(lib.dsdf_cap_sdf(sdf.data_ptr(), G.data_ptr() if G is not None else None, G.stride(0) if G is not None else 0, Lz,
+                                 so.data_ptr(), so.stride(0), n, len(caps), dims, mult, meas, capv, st))
+    return sdf[:n], (G[:n, :Lz] if G is not None else None)

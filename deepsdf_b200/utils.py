@@ -3,8 +3,9 @@
 ``decode_sdf(decoder, latent_vector, queries)`` keeps the reference's meaning: ``latent_vector`` ([L] or [1, L]) is
 broadcast over ``queries`` [n, 3]; with ``latent_vector=None`` the queries already carry their latent columns
 ([n, L+3]).  For the 8x512-class decoders and a broadcast latent the call runs on the fused tcgen05 forward (the latent
-collapses into one per-scene bias vector, nothing of size [n, L+3] is materialised); everything else goes through the
-module's generic CUDA path.  No CPU path.
+collapses into one per-scene bias vector, nothing of size [n, L+3] is materialised); per-row codes of length <= 4 (the
+microstructure consumers) run on the same kernel in row-latent mode; everything else goes through the module's generic
+CUDA path.  No CPU path.
 """
 from __future__ import annotations
 
@@ -36,6 +37,14 @@ def fused_engine_for(decoder):
 def decode_sdf(decoder, latent_vector, queries):
     num_samples = queries.shape[0]
     if latent_vector is None:
+        # rows carry their own codes (mesh.py:490-497): short codes run on the fused forward in row-latent mode
+        dec = decoder.module if isinstance(decoder, torch.nn.DataParallel) else decoder
+        plain = not (torch.is_grad_enabled() and queries.requires_grad) and not decoder.training and num_samples > 0
+        if plain and queries.is_cuda and getattr(dec, "latent_size", 99) <= 4:
+            eng = fused_engine_for(decoder)
+            if eng is not None:
+                q = queries.detach().to(eng.device, torch.float32).contiguous()
+                return eng.sdf_and_input_grad_rows(q, with_grad=False)[0].unsqueeze(1)
         return decoder(queries)
     needs_grad = torch.is_grad_enabled() and (latent_vector.requires_grad or queries.requires_grad)
     eng = None if (needs_grad or decoder.training or num_samples == 0) else fused_engine_for(decoder)

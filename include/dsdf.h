@@ -178,6 +178,13 @@ int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_pa
                       const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows, const float* lat_table,
                       const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total, float reg_lambda_eff,
                       float inv_n, const dsdf_param_grads* pgrads, float* lat_grad, float* loss_out, void* stream);
+/* Row-latent forward: every row brings its own latent code (queries[r] = [latent(L), xyz(3)], row stride ldq floats) - the
+ * microstructure consumers of deep_sdf/mesh.py:457-497, whose codes come from a spline over the domain (L = 1 or 2;
+ * supported: L <= 4).  Same kernel and same dsdf_train_io as dsdf_fused_forward; the latent columns of lin0 and of the
+ * latent_in layer are applied per row in fp32 like the xyz columns.  Followed by dsdf_fused_dgrad (xyz = queries + L,
+ * xyz_stride = ldq) and dsdf_fused_input_grad it yields G = dSDF/d[latent, xyz] for per-point codes. */
+int dsdf_fused_forward_rows(const dsdf_net_desc* desc, const void* pack, const float* queries, int32_t ldq, int64_t n_rows,
+                            float* sdf_out, const dsdf_train_io* tr, void* stream);
 /* ------------------------------------------------------------------------------------------------
  * Input gradient (the derivative consumers of deep_sdf/mesh.py:405-454 and analysis/: dSDF/dlatent, dSDF/dxyz).
  * After  dsdf_fused_forward(training=1, dropout_off=1, dy_unit=1)  and  dsdf_fused_dgrad(store_mask = layer 0 |
@@ -213,6 +220,21 @@ int dsdf_sample_batch(const float* store, const int64_t* meta, const int64_t* sc
                       int32_t samples_per_scene, uint64_t seed, float* batch_out, void* stream);
 /* the bijection itself, on the host: source row of batch position i within the scene's positive / negative rows */
 uint32_t dsdf_sample_perm(uint32_t i, uint32_t n, uint64_t seed, int64_t scene, int32_t negative);
+
+/* ------------------------------------------------------------------------------------------------
+ * Pre/post kernels of the microstructure evaluation (deep_sdf/mesh.py:457-514, csrc/microstructure.cu).
+ * dsdf_tile_queries: queries[r] = [lat[r, 0:L], T(x), T(y), T(z)] with the tiling transform of prepare_samples
+ *   (mesh.py:470-477: p = 2/t, T(x) = (2/p) * |((x - t%2) mod 2p) - p| - 1) of samples_orig [n][ld_s]; rows [n, n_pad) are
+ *   zero-filled (pad to 128-row tiles).  tiling3: HOST array of 3 floats.
+ * dsdf_cap_sdf: the border caps of evaluate_network (mesh.py:499-514) applied in place to sdf [n]: for every entry
+ *   border = (x[dim] - multiplier*(1-measure)) * -multiplier; cap == -1: sdf = max(sdf, -border), cap == +1: sdf =
+ *   min(sdf, border); then sdf = max(sdf, distance outside the unit cube).  Where a cap decides the value the latent
+ *   derivative vanishes: if G != NULL its columns [0, L) of that row are zeroed.  dims/multipliers/measures/caps: HOST. */
+int dsdf_tile_queries(const float* samples_orig, int32_t ld_s, const float* lat, int32_t ld_l, int32_t latent_size, int64_t n,
+                      int64_t n_pad, const float* tiling3, float* queries, void* stream);
+int dsdf_cap_sdf(float* sdf, float* G, int64_t ldg, int32_t latent_size, const float* samples_orig, int32_t ld_s, int64_t n,
+                 int32_t n_caps, const int32_t* dims, const double* multipliers, const double* measures, const int32_t* caps,
+                 void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Iso-surface of the device-resident SDF volume (the tail of create_mesh: deep_sdf/mesh.py:88-155 hands a host copy of
