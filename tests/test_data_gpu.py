@@ -191,3 +191,38 @@ def test_reconstruct_cli_writes_codes_and_improves(tmp_path, monkeypatch):
     stamp = os.path.getmtime(codes / "cs_0.pth")
     again = R.reconstruct_split(exp, "latest", iters=5, num_samples=1000, skip=True)
     assert again["loss"] == {} and os.path.getmtime(codes / "cs_0.pth") == stamp
+
+
+def test_sampler_properties_at_config5_size():
+    """BASELINE.json config #5: 4096 scenes x 100 000 stored rows (6.5 GB resident), SamplesPerScene 16000, 64 scenes per
+    batch.  Size-independent properties of one sampled batch: every row comes from its scene and from the right sign
+    half, no stored row is drawn twice (the keyed bijection), the draw is a function of the seed only."""
+    n_sc, n_rows, sps, spb = 4096, 100000, 16000, 64
+    n_pos = 45000                                                         # 45 000 positives, 55 000 negatives per scene
+    ds = object.__new__(DeviceSDFSamples)                                 # the store is built on the device: rows encode their origin
+    ds.subsample, ds.geom_dimension, ds.device = sps, 3, torch.device(DEV)
+    ds.npyfiles = [f"<scene {i}>" for i in range(n_sc)]
+    idx = torch.arange(n_rows, device=DEV, dtype=torch.float32)
+    one = torch.stack([torch.zeros_like(idx), idx, torch.zeros_like(idx), torch.where(idx < n_pos, 0.05, -0.05)], 1)
+    ds.store = one.repeat(n_sc, 1)                                        # [409.6 M, 4] fp32
+    ds.store[:, 0] = torch.arange(n_sc, device=DEV, dtype=torch.float32).repeat_interleave(n_rows)
+    off = torch.arange(n_sc, dtype=torch.int64) * n_rows
+    ds.meta_host = torch.stack([off, torch.full_like(off, n_pos), off + n_pos, torch.full_like(off, n_rows - n_pos)], 1).numpy()
+    ds.meta = torch.from_numpy(ds.meta_host).to(DEV)
+    ds.total_rows = n_sc * n_rows
+    assert ds.store.shape == (n_sc * n_rows, 4) and ds.store.numel() * 4 > 6.5e9
+    ids = torch.sort(torch.randperm(n_sc, generator=torch.Generator().manual_seed(1))[:spb]).values.to(DEV)
+    b = ds.sample_batch(ids, seed=1234)
+    assert b.shape == (spb * sps, 4)
+    v = b.view(spb, sps, 4)
+    assert torch.equal(v[:, :, 0], ids.float()[:, None].expand(-1, sps))                     # right scene, scene-major
+    half = sps // 2
+    assert bool((v[:, :half, 3] > 0).all()) and bool((v[:, half:, 3] < 0).all())             # pos half then neg half
+    assert bool((v[:, :half, 1] < n_pos).all()) and bool((v[:, half:, 1] >= n_pos).all())
+    srt = torch.sort(v[:, :, 1], dim=1).values
+    assert bool((srt[:, 1:] != srt[:, :-1]).all())                                           # without replacement
+    assert torch.equal(ds.sample_batch(ids, seed=1234), b) and not torch.equal(ds.sample_batch(ids, seed=1235), b)
+    # the draw is spread over the whole stored range, not a prefix
+    assert float(v[:, :half, 1].max()) > 0.99 * n_pos and float(v[:, half:, 1].max()) > 0.99 * n_rows
+    del ds, b, v, one
+    torch.cuda.empty_cache()
