@@ -89,3 +89,24 @@ def test_grid_slabs_tile_the_volume():
     assert torch.equal(torch.cat([p[1] for p in parts], 0), dxyz)
     assert torch.equal(torch.cat([p[2] for p in parts], 0), dlat)
     assert whole.shape == (N, N, N) and dxyz.shape == (N, N, N, 3) and dlat.shape == (N, N, N, 16)
+
+
+def test_grid_512_slabs_equal_whole_volume():
+    """BASELINE.json config #4 size: the 512^3 grid evaluated as 8 z-slabs (what 8 GPUs do) is bit-identical to the
+    one-piece evaluation, and the grid points are the reference's (mesh.py:37-53) at the volume's corners."""
+    from deepsdf_b200.mesh import create_mesh_sdf
+    from deepsdf_b200.sharding import slab_for_rank
+    kw, ospec, params, mod = _module("big_8x512_L16")
+    lat = torch.randn(16, generator=torch.Generator().manual_seed(4)) * 0.1
+    N = 512
+    whole = create_mesh_sdf(mod, lat, N=N)
+    assert whole.shape == (N, N, N) and bool(torch.isfinite(whole).all())
+    for r in range(8):
+        i0, i1 = slab_for_rank(N, r, 8)
+        part = create_mesh_sdf(mod, lat, N=N, slab=(i0, i1), max_batch=1 << 20)
+        assert torch.equal(part, whole[i0:i1]), r
+    corners = torch.tensor([[-1.0, -1.0, -1.0], [1.0, 1.0, 1.0], [-1.0, 1.0, -1.0]])
+    q = torch.cat([lat.expand(3, -1), corners], 1)
+    want = O.decoder_forward(ospec, params, q, training=False).squeeze(1)
+    got = torch.stack([whole[0, 0, 0], whole[-1, -1, -1], whole[0, -1, 0]]).cpu()
+    assert float((got - want).abs().max()) <= 2e-3
