@@ -182,6 +182,8 @@ def evaluate_network_sdf(decoder, lat_vec_red: torch.Tensor, samples_orig: torch
         L.check(lib.dsdf_tile_queries(so.data_ptr(), so.stride(0), lat.data_ptr(), lat.stride(0), Lz, n, n_pad, t3, queries.data_ptr(), st))
     sdf, G = eng.sdf_and_input_grad_rows(queries, with_grad=with_grad)
     caps = list((cap_border_dict or {}).items())
+    if len(caps) > 6 or any(k not in location_lookup for k, _ in caps):
+        raise L.DsdfError("cap_border_dict takes the six keys of location_lookup (x0, x1, y0, y1, z0, z1)")
     dims = (C.c_int32 * 6)(*([location_lookup[k][0] for k, _ in caps] + [0] * (6 - len(caps))))
     mult = (C.c_double * 6)(*([float(location_lookup[k][1]) for k, _ in caps] + [0.0] * (6 - len(caps))))
     meas = (C.c_double * 6)(*([float(v["measure"]) for _, v in caps] + [0.0] * (6 - len(caps))))
