@@ -430,11 +430,13 @@ __device__ __forceinline__ uint32_t dropout_keep_word_rk(const uint32_t* rk, uin
   const Philox4 a = philox4x32_rk(uint32_t(row), uint32_t(row >> 32), layer, 2u * g32, rk);
   const Philox4 b = philox4x32_rk(uint32_t(row), uint32_t(row >> 32), layer, 2u * g32 + 1u, rk);
   const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-  uint32_t lt = 0u, eq = 0xFFFFFFFFu;
+  // bit-sliced U < thr as a ripple from the least significant plane: lt_b = (~w_b & t_b) | (~(w_b ^ t_b) & lt_{b-1}) with
+  // t_b = all-ones where bit b of thr is set - ONE three-input LOP3 per plane (the masks are kernel-uniform)
+  uint32_t lt = 0u;
 #pragma unroll
-  for (int bit = 7; bit >= 0; --bit) {
-    if ((thr >> bit) & 1u) { lt |= eq & ~w[bit]; eq &= w[bit]; }
-    else { eq &= ~w[bit]; }
+  for (int bit = 0; bit < 8; ++bit) {
+    const uint32_t t = 0u - ((thr >> bit) & 1u);
+    lt = (~w[bit] & t) | (~(w[bit] ^ t) & lt);
   }
   return ~lt;
 }
