@@ -44,13 +44,14 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"
 
 // Post-process 16 consecutive columns [c0, c0+16) of one row and write them (bf16) into the SW128 activation tile.
 //   has_acc  read the fp32 accumulators from TMEM (taddr) - false for the MMA-less first layer
+//   st0/st1  shared addresses of the two 16-byte pieces of the activation tile that receive the 16 columns
 //   sb       shared-memory bias (already multiplied by the dropout scale); swx xyz weight rows (same scaling) or null
 //   keep16   low 16 bits: Philox keep bits of these columns (all ones when the layer has no dropout)
 // Returns the 16 gate bits (relu AND keep); adds this row's share of the last-layer dot product to ydot.
 template <bool kTrain, bool kRowLat>
 __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, float ascale, uint32_t sb, bool has_xyz, uint32_t swx,
-                                               float x, float y, float z, uint32_t keep16, bool is_last, uint32_t swl, uint32_t sA,
-                                               uint32_t row, uint32_t c0, float& ydot, const float* wl, int n_rl,
+                                               float x, float y, float z, uint32_t keep16, bool is_last, uint32_t swl,
+                                               uint32_t st0, uint32_t st1, float& ydot, const float* wl, int n_rl,
                                                const float (&rl)[4]) {
   // sb / swx / swl / sA are SHARED-space byte addresses (of this pass's first column where they are per column)
   float v[16];
@@ -119,12 +120,9 @@ __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, flo
       ydot += v[4 * k + 0] * w.x + v[4 * k + 1] * w.y + v[4 * k + 2] * w.z + v[4 * k + 3] * w.w;
     }
   }
-  const uint32_t base = sA + (c0 >> 6) * A_CHUNK_BYTES + row * 128u;
-  const uint32_t piece0 = (c0 & 63u) >> 3;
-  sts_u32x4(base + ((piece0 ^ (row & 7u)) << 4), pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
-            pack_bf16x2(v[6], v[7]));
-  sts_u32x4(base + (((piece0 + 1) ^ (row & 7u)) << 4), pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]),
-            pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+  // st0 / st1: the two 16-byte pieces of this row's SW128 line that hold these 16 columns (addresses formed once per thread)
+  sts_u32x4(st0, pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  sts_u32x4(st1, pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
   return gate;
 }
 
@@ -138,10 +136,9 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + P_OFF_B;
-  float* s_bias = reinterpret_cast<float*>(smem + P_OFF_BIAS);
-  float* s_wxyz = reinterpret_cast<float*>(smem + P_OFF_WXYZ);
-  float* s_wlast = reinterpret_cast<float*>(smem + P_OFF_WLAST);
-  float* s_ypart = reinterpret_cast<float*>(smem + P_OFF_YPART);
+  // the same base as a 32-bit shared-space address: everything the epilogue touches is addressed from it with explicit
+  // ld/st.shared, so no generic pointer (and no re-derivation of its alignment) lives in the hot loop
+  const uint32_t smem_a = (smem_u32(smem_raw) + 1023u) & ~1023u;
   __shared__ uint64_t bar_full[P_STAGES], bar_empty[P_STAGES], bar_tmem_full[2], bar_free_q0, bar_free_lo, bar_a_ready[4];
   __shared__ uint64_t bar_q_written[4], bar_q_stashed[4];   // activation stash hand-over (training), per 128-column quarter
   __shared__ uint32_t tmem_slot;
@@ -328,7 +325,11 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     const uint32_t rt = q * 32 + lane; // row within the tile == TMEM lane
     const uint32_t tmem_row = tmem_base + (uint32_t(q * 32) << 16);
     const uint32_t ready_leader = mapa_u32(smem_u32(&bar_a_ready[0]), 0);   // + 8*quarter
-    s_wlast[tid] = __ldg(args.w_last + tid);
+    sts_f32(smem_a + P_OFF_WLAST + uint32_t(tid) * 4u, __ldg(args.w_last + tid));
+    // this thread's store addresses inside a quarter: row line + 64-column chunk of its slice + swizzled 16-byte piece
+    const uint32_t st_row = smem_a + rt * 128u + uint32_t(j >> 1) * A_CHUNK_BYTES;
+    const uint32_t st_ps = (uint32_t(j & 1) << 6) ^ ((rt & 7u) << 4);
+    const uint32_t st_a0 = st_row + st_ps, st_a1 = st_row + (st_ps ^ 16u), st_a2 = st_row + (st_ps ^ 32u), st_a3 = st_row + (st_ps ^ 48u);
     uint32_t mma_iter = 0;
     const bool stash = kTrain && args.store_acts != 0;
     uint32_t wpar = 0, wany = 0;        // per quarter: parity of / any hand-overs to the stash warp so far
@@ -361,16 +362,17 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         const bool drop = kTrain && L.dropout != 0 && args.dropout_on != 0;
         const bool has_acc = L.has_mma != 0;
         const float ascale = drop ? args.drop_scale : 1.0f;
-        const uint32_t sb = smem_u32(s_bias) + uint32_t(l & 1) * FH * 4;
+        const uint32_t sb = smem_a + P_OFF_BIAS + uint32_t(l & 1) * FH * 4;
         // ---- before the accumulators are ready: stage this layer's bias (+ xyz weights), draw the first keep words
         {
           const float* src = (L.bias_slot >= 0 && !kRowLat) ? (args.cbias + (size_t(scene) * 2 + L.bias_slot) * FH) : args.bias[l];
-          s_bias[(l & 1) * FH + tid] = __ldg(src + tid) * ascale;
+          sts_f32(sb + uint32_t(tid) * 4u, __ldg(src + tid) * ascale);
           if (L.has_xyz) {
             const float* wsrc = args.wxyz[l];
-            s_wxyz[tid] = __ldg(wsrc + tid) * ascale;
-            s_wxyz[FH + tid] = __ldg(wsrc + FH + tid) * ascale;
-            s_wxyz[2 * FH + tid] = __ldg(wsrc + 2 * FH + tid) * ascale;
+            const uint32_t wx = smem_a + P_OFF_WXYZ + uint32_t(tid) * 4u;
+            sts_f32(wx, __ldg(wsrc + tid) * ascale);
+            sts_f32(wx + FH * 4, __ldg(wsrc + FH + tid) * ascale);
+            sts_f32(wx + 2 * FH * 4, __ldg(wsrc + 2 * FH + tid) * ascale);
           }
         }
         const uint64_t grow = args.row0 + uint64_t(int64_t(tile_c) * TILE_M + rt);
@@ -381,7 +383,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         }
         epi_bar();
         const bool has_xyz = L.has_xyz != 0;
-        const uint32_t swx = smem_u32(s_wxyz), swl = smem_u32(s_wlast), sA_a = smem_u32(sA);
+        const uint32_t swx = smem_a + P_OFF_WXYZ, swl = smem_a + P_OFF_WLAST;
         uint32_t par = 0;
         if (has_acc) { par = mma_iter & 1; ++mma_iter; }
         uint32_t* gdst = nullptr;
@@ -394,12 +396,14 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
           // the previous layer's stash of this quarter must have been read out of the tile
           if (stash && ((wany >> Q) & 1u)) mbar_wait(&bar_q_stashed[Q], ((wpar >> Q) & 1u) ^ 1u);
+          const uint32_t qoff = uint32_t(Q) * 2u * A_CHUNK_BYTES;        // a quarter = two 64-column chunks
           const uint32_t g0 = epi_pass16<kTrain, kRowLat>(tmem_row + c0, has_acc, ascale, sb + c0 * 4, has_xyz, swx + c0 * 4, px, py, pz,
-                                                          keep, last, swl + c0 * 4, sA_a, rt, c0, ydot,
+                                                          keep, last, swl + c0 * 4, st_a0 + qoff, st_a1 + qoff, ydot,
                                                           wl_layer ? wl_layer + c0 : nullptr, args.row_lat_dim, rl);
           const uint32_t g1 = epi_pass16<kTrain, kRowLat>(tmem_row + c0 + 16, has_acc, ascale, sb + (c0 + 16) * 4, has_xyz,
-                                                          swx + (c0 + 16) * 4, px, py, pz, keep >> 16, last, swl + (c0 + 16) * 4, sA_a, rt,
-                                                          c0 + 16, ydot, wl_layer ? wl_layer + c0 + 16 : nullptr, args.row_lat_dim, rl);
+                                                          swx + (c0 + 16) * 4, px, py, pz, keep >> 16, last, swl + (c0 + 16) * 4,
+                                                          st_a2 + qoff, st_a3 + qoff, ydot, wl_layer ? wl_layer + c0 + 16 : nullptr,
+                                                          args.row_lat_dim, rl);
           if (kTrain && gdst != nullptr) gdst[size_t(Q) * 4 * TILE_M] = g0 | (g1 << 16);
           fence_proxy_async_smem();
           tc_fence_before();
@@ -437,10 +441,11 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
 
       const int64_t lrow = int64_t(tile_c) * TILE_M + rt;
       // ---- final layer: combine the four column slices, tanh, loss
-      s_ypart[j * TILE_M + rt] = ydot;
+      sts_f32(smem_a + P_OFF_YPART + (uint32_t(j) * TILE_M + rt) * 4u, ydot);
       epi_bar();
       if (j == 0) {
-        const float yv = ((s_ypart[rt] + s_ypart[TILE_M + rt]) + (s_ypart[2 * TILE_M + rt] + s_ypart[3 * TILE_M + rt])) + __ldg(args.b_last);
+        const uint32_t yp = smem_a + P_OFF_YPART + rt * 4u;
+        const float yv = ((lds_f32(yp) + lds_f32(yp + TILE_M * 4)) + (lds_f32(yp + 2 * TILE_M * 4) + lds_f32(yp + 3 * TILE_M * 4))) + __ldg(args.b_last);
         const float t1 = tanhf(yv);
         float t = t1, dt = 1.0f - t1 * t1;
         if (args.use_tanh) { t = tanhf(t1); dt *= (1.0f - t * t); }
