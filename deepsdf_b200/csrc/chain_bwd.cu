@@ -36,8 +36,9 @@ __device__ __forceinline__ void bwd_bar() { asm volatile("bar.sync 1, %0;" ::"n"
 
 // 16 columns [c0, c0+16) of one row: v = accumulators (or dy * w_last), gated and scaled, packed to bf16 into the A tile
 __device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float dyv, uint32_t swl, uint32_t gate16, float scale,
-                                           uint32_t sA, uint32_t row, uint32_t c0) {
-  // swl / sA: SHARED-space byte addresses (explicit ld/st.shared: no generic-address descriptors in the hot loop)
+                                           uint32_t st0, uint32_t st1) {
+  // swl / st0 / st1: SHARED-space byte addresses (explicit ld/st.shared); st0, st1 = the two 16-byte pieces of this row's
+  // SW128 line that receive the 16 columns, formed once per thread
   float v[16];
   if (has_acc) {
     uint32_t r[16];
@@ -55,12 +56,10 @@ __device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float d
   }
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = (gate16 & (1u << i)) ? v[i] : 0.0f;
-  const uint32_t base = sA + (c0 >> 6) * A_CHUNK_BYTES + row * 128u;
-  const uint32_t piece0 = (c0 & 63u) >> 3;
   const uint32_t p0 = pack_bf16x2(v[0], v[1]), p1 = pack_bf16x2(v[2], v[3]), p2 = pack_bf16x2(v[4], v[5]), p3 = pack_bf16x2(v[6], v[7]);
   const uint32_t p4 = pack_bf16x2(v[8], v[9]), p5 = pack_bf16x2(v[10], v[11]), p6 = pack_bf16x2(v[12], v[13]), p7 = pack_bf16x2(v[14], v[15]);
-  sts_u32x4(base + ((piece0 ^ (row & 7u)) << 4), p0, p1, p2, p3);
-  sts_u32x4(base + (((piece0 + 1) ^ (row & 7u)) << 4), p4, p5, p6, p7);
+  sts_u32x4(st0, p0, p1, p2, p3);
+  sts_u32x4(st1, p4, p5, p6, p7);
 }
 
 }  // namespace
@@ -72,8 +71,8 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + B_OFF_B;
-  float* s_wlast = reinterpret_cast<float*>(smem + B_OFF_WLAST);
-  float* s_xyz = reinterpret_cast<float*>(smem + B_OFF_XYZ);
+  // 32-bit shared-space base for everything the epilogue touches (see chain_fwd.cu)
+  const uint32_t smem_a = (smem_u32(smem_raw) + 1023u) & ~1023u;
   __shared__ uint64_t bar_full[B_STAGES], bar_empty[B_STAGES], bar_tmem_full[2], bar_free_q0, bar_free_lo, bar_a_ready[4];
   // per 128-column quarter of the dY tile: written by all 16 epilogue warps -> read by the stash warp (TMA store) and by
   // the four warps that own its column sums -> released for the next chain link
@@ -244,8 +243,11 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const uint32_t rt = q * 32 + lane;
     const uint32_t tmem_row = tmem_base + (uint32_t(q * 32) << 16);
     const uint32_t ready_leader = mapa_u32(smem_u32(&bar_a_ready[0]), 0);
-    s_wlast[tid] = __ldg(args.w_last + tid);
-    const uint32_t swl_a = smem_u32(s_wlast), sA_a = smem_u32(sA);
+    sts_f32(smem_a + B_OFF_WLAST + uint32_t(tid) * 4u, __ldg(args.w_last + tid));
+    const uint32_t swl_a = smem_a + B_OFF_WLAST, xyz_a = smem_a + B_OFF_XYZ;
+    const uint32_t st_row = smem_a + rt * 128u + uint32_t(j >> 1) * A_CHUNK_BYTES;
+    const uint32_t st_ps = (uint32_t(j & 1) << 6) ^ ((rt & 7u) << 4);
+    const uint32_t st_a0 = st_row + st_ps, st_a1 = st_row + (st_ps ^ 16u), st_a2 = st_row + (st_ps ^ 32u), st_a3 = st_row + (st_ps ^ 48u);
     uint32_t mma_iter = 0;
     uint32_t wpar = 0, wany = 0;        // per quarter: parity of / any hand-overs so far
     const int tiles_alloc = int(args.n_rows_pad / TILE_M);
@@ -259,9 +261,9 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       const float dyv = valid ? __ldg(args.dy + lrow) : 0.0f;
       if (j == 0) {
         const float* pt = args.xyz + lrow * args.xyz_stride;
-        s_xyz[rt] = valid ? __ldg(pt + 0) : 0.0f;
-        s_xyz[TILE_M + rt] = valid ? __ldg(pt + 1) : 0.0f;
-        s_xyz[2 * TILE_M + rt] = valid ? __ldg(pt + 2) : 0.0f;
+        sts_f32(xyz_a + rt * 4u, valid ? __ldg(pt + 0) : 0.0f);
+        sts_f32(xyz_a + (TILE_M + rt) * 4u, valid ? __ldg(pt + 1) : 0.0f);
+        sts_f32(xyz_a + (2 * TILE_M + rt) * 4u, valid ? __ldg(pt + 2) : 0.0f);
       }
       bwd_bar();      // s_xyz visible to the column-sum passes of this tile
 
@@ -284,8 +286,9 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
           // the previous dY tile's quarter must have been stashed and column-summed before it is overwritten
           if ((wany >> Q) & 1u) mbar_wait(&bar_q_released[Q], ((wpar >> Q) & 1u) ^ 1u);
-          bwd_pass16(tmem_row + c0, has_acc, dyv, swl_a + c0 * 4, gate, scale, sA_a, rt, c0);
-          bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, swl_a + (c0 + 16) * 4, gate >> 16, scale, sA_a, rt, c0 + 16);
+          const uint32_t qoff = uint32_t(Q) * 2u * A_CHUNK_BYTES;
+          bwd_pass16(tmem_row + c0, has_acc, dyv, swl_a + c0 * 4, gate, scale, st_a0 + qoff, st_a1 + qoff);
+          bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, swl_a + (c0 + 16) * 4, gate >> 16, scale, st_a2 + qoff, st_a3 + qoff);
           fence_proxy_async_smem();
           tc_fence_before();
           __syncwarp();
@@ -327,8 +330,8 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           }
           if (cols_valid && do_sums) {
             const uint32_t piece = uint32_t(warp & 1) * 4u + pl;
-            const uint32_t a0 = smem_u32(sA) + uint32_t(cw >> 6) * A_CHUNK_BYTES + r0 * 128u + ((piece ^ r0) << 4);
-            const uint32_t xb = smem_u32(s_xyz) + r0 * 4u;
+            const uint32_t a0 = smem_a + uint32_t(cw >> 6) * A_CHUNK_BYTES + r0 * 128u + ((piece ^ r0) << 4);
+            const uint32_t xb = xyz_a + r0 * 4u;
             if (!want_xyz) {
 #pragma unroll
               for (int i = 0; i < TILE_M / 8; ++i) {
