@@ -18,6 +18,8 @@
 // The final 512 -> 1 layer, tanh, clamp, L1 loss and dL/dy are fused into the last epilogue; in training every layer's
 // activation tile is TMA-stored (bf16) for wgrad together with its 1-bit gates.
 // Replaces Decoder.forward (deep_sdf/networks/deep_sdf_decoder.py:76-111) and train_deep_sdf.py:511-519.
+#include <type_traits>
+
 #include "common.cuh"
 #include "fused.cuh"
 #include "host_util.h"
@@ -48,12 +50,16 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"
 //   sb       shared-memory bias (already multiplied by the dropout scale); swx xyz weight rows (same scaling) or null
 //   keep16   low 16 bits: Philox keep bits of these columns (all ones when the layer has no dropout)
 // Returns the 16 gate bits (relu AND keep); adds this row's share of the last-layer dot product to ydot.
-template <bool kTrain, bool kRowLat>
-__device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc, float ascale, uint32_t sb, bool has_xyz, uint32_t swx,
-                                               float x, float y, float z, uint32_t keep16, bool is_last, uint32_t swl,
+// kPlain: the common hidden layer (accumulators present, no per-row xyz / latent columns, not the last layer) as a
+// compile-time variant, so that its passes carry no flag handling (R2P takes all seven predicates; layer-invariant
+// conditions kept as run-time flags end up in a bit-field register that every pass re-tests).
+template <bool kTrain, bool kRowLat, bool kPlain>
+__device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc_rt, float ascale, uint32_t sb, bool has_xyz_rt, uint32_t swx,
+                                               float x, float y, float z, uint32_t keep16, bool is_last_rt, uint32_t swl,
                                                uint32_t st0, uint32_t st1, float& ydot, const float* wl, int n_rl,
                                                const float (&rl)[4]) {
   // sb / swx / swl / sA are SHARED-space byte addresses (of this pass's first column where they are per column)
+  const bool has_acc = kPlain ? true : has_acc_rt, has_xyz = kPlain ? false : has_xyz_rt, is_last = kPlain ? false : is_last_rt;
   float v[16];
   if (has_acc) {
     uint32_t r[16];
@@ -392,18 +398,19 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
 
         // One 128-column quarter: two 16-column passes straight from TMEM into the A tile.
         const float* wl_layer = (kRowLat && L.bias_slot >= 0) ? args.wlat + size_t(L.bias_slot) * args.row_lat_dim * FH : nullptr;
-        auto quarter = [&](int Q, uint32_t keep) {
+        auto quarter_v = [&](int Q, uint32_t keep, auto PLAIN) {
+          constexpr bool kPlain = decltype(PLAIN)::value;
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
           // the previous layer's stash of this quarter must have been read out of the tile
           if (stash && ((wany >> Q) & 1u)) mbar_wait(&bar_q_stashed[Q], ((wpar >> Q) & 1u) ^ 1u);
           const uint32_t qoff = uint32_t(Q) * 2u * A_CHUNK_BYTES;        // a quarter = two 64-column chunks
-          const uint32_t g0 = epi_pass16<kTrain, kRowLat>(tmem_row + c0, has_acc, ascale, sb + c0 * 4, has_xyz, swx + c0 * 4, px, py, pz,
-                                                          keep, last, swl + c0 * 4, st_a0 + qoff, st_a1 + qoff, ydot,
-                                                          wl_layer ? wl_layer + c0 : nullptr, args.row_lat_dim, rl);
-          const uint32_t g1 = epi_pass16<kTrain, kRowLat>(tmem_row + c0 + 16, has_acc, ascale, sb + (c0 + 16) * 4, has_xyz,
-                                                          swx + (c0 + 16) * 4, px, py, pz, keep >> 16, last, swl + (c0 + 16) * 4,
-                                                          st_a2 + qoff, st_a3 + qoff, ydot, wl_layer ? wl_layer + c0 + 16 : nullptr,
-                                                          args.row_lat_dim, rl);
+          const uint32_t g0 = epi_pass16<kTrain, kRowLat, kPlain>(tmem_row + c0, has_acc, ascale, sb + c0 * 4, has_xyz, swx + c0 * 4, px,
+                                                                  py, pz, keep, last, swl + c0 * 4, st_a0 + qoff, st_a1 + qoff, ydot,
+                                                                  wl_layer ? wl_layer + c0 : nullptr, args.row_lat_dim, rl);
+          const uint32_t g1 = epi_pass16<kTrain, kRowLat, kPlain>(tmem_row + c0 + 16, has_acc, ascale, sb + (c0 + 16) * 4, has_xyz,
+                                                                  swx + (c0 + 16) * 4, px, py, pz, keep >> 16, last, swl + (c0 + 16) * 4,
+                                                                  st_a2 + qoff, st_a3 + qoff, ydot,
+                                                                  wl_layer ? wl_layer + c0 + 16 : nullptr, args.row_lat_dim, rl);
           if (kTrain && gdst != nullptr) gdst[size_t(Q) * 4 * TILE_M] = g0 | (g1 << 16);
           fence_proxy_async_smem();
           tc_fence_before();
@@ -413,6 +420,12 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
             if (lane == 0) mbar_arrive(&bar_q_written[Q]);
             wpar ^= 1u << Q; wany |= 1u << Q;
           }
+        };
+        // one run-time dispatch per quarter instead of flag tests in every 16-column pass
+        const bool plain = has_acc && !has_xyz && !last;
+        auto quarter = [&](int Q, uint32_t keep) {
+          if (plain) quarter_v(Q, keep, std::true_type{});
+          else quarter_v(Q, keep, std::false_type{});
         };
 
         // ---- half 0: ready while the tensor cores still compute half 1.  Activation chunks 0,1 may be overwritten once
