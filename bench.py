@@ -180,6 +180,24 @@ def cpu_train_step_rate(n_scenes: int, steps: int, warmup: int):
     return n / (ms / 1e3), ms, threads
 
 
+def cpu_grid_rate(n_grid: int):
+    """Oracle port of create_mesh's chunk loop (deep_sdf/mesh.py:37-73, 32768-row chunks, no marching cubes) on the host
+    cores at a bounded resolution: the CPU figure printed beside the 512^3 grid queries/s."""
+    from oracle import decoder_oracle as O
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    spec = O.OracleSpec(latent_size=SPECS["CodeLength"], **SPECS["NetworkSpecs"])
+    params = O.make_params(spec, 0)
+    g = torch.Generator().manual_seed(1)
+    lat = torch.randn(spec.latent_size, generator=g) / (spec.latent_size ** 0.5)
+    O.create_mesh_sdf(spec, params, lat, 16)                  # warm-up
+    t0 = time.perf_counter()
+    O.create_mesh_sdf(spec, params, lat, n_grid)
+    dt = time.perf_counter() - t0
+    return {"queries_per_s": n_grid ** 3 / dt, "cores": threads, "kind": "port", "ms": 1e3 * dt,
+            "sample": f"N = {n_grid} grid ({n_grid ** 3} queries) through the oracle's create_mesh loop, SDF only, PyTorch CPU fp32"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -332,6 +350,8 @@ def run_gpu(args):
         cpu = {"value": rate, "unit": "samples/s", "cores": threads, "kind": "port",
                "sample": f"{n_sc} scenes x {SAMPLES_PER_SCENE} rows per step, 1 warm-up + 2 timed steps, oracle port of train_deep_sdf.py:483-545 (PyTorch CPU fp32)",
                "ms_per_step": ms_cpu}
+        if isinstance(extras.get("grid"), dict):
+            extras["grid"]["cpu_baseline"] = cpu_grid_rate(64)
 
     line = {
         "metric": "train SDF samples/s (fwd+bwd+optimizer)", "value": value, "unit": "samples/s", "n_gpus": world,
