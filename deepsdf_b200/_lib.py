@@ -58,6 +58,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_last_error": (C.c_char_p, []),
         "dsdf_check_device": (C.c_int, []),
         "dsdf_dropout_effective_p": (f32, [f32]),
+        "dsdf_dropout_scale": (f32, [f32]),
         "dsdf_dropout_mask": (C.c_int, [u64, u32, u64, i64, i32, f32, vp, vp]),
         "dsdf_generic_workspace_bytes": (sz, [P(NetDesc), i64]),
         "dsdf_generic_forward": (C.c_int, [P(NetDesc), P(Params), vp, i64, i32, u64, u64, vp, vp, sz, vp]),

@@ -22,6 +22,7 @@ extern "C" int dsdf_abi_version(void) { return DSDF_ABI_VERSION; }
 extern "C" const char* dsdf_last_error(void) { return g_last_error; }
 extern "C" int dsdf_check_device(void) { return require_sm100(); }
 extern "C" float dsdf_dropout_effective_p(float p) { return float(dropout_threshold(p)) / 256.0f; }
+extern "C" float dsdf_dropout_scale(float p) { return dropout_scale(p); }
 
 extern "C" int dsdf_dropout_mask(uint64_t seed, uint32_t layer, uint64_t row0, int64_t n_rows, int32_t width, float p,
                                  uint8_t* mask_out, void* stream) {

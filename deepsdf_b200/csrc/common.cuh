@@ -447,6 +447,12 @@ __host__ __device__ __forceinline__ uint32_t dropout_threshold(float p) {
   int t = int(p * 256.0f + 0.5f);
   return uint32_t(t < 0 ? 0 : (t > 255 ? 255 : t));
 }
+// Inverted-dropout scale of the survivors, 1 / (1 - effective p) with effective p = thr/256 (NOT the nominal p: the keep
+// probability is quantised to (256 - thr)/256, and E[keep * scale] must be exactly 1 so that train- and eval-mode
+// activations agree in expectation like F.dropout's, deep_sdf_decoder.py:105-106)
+__host__ __device__ __forceinline__ float dropout_scale(float p) {
+  return 256.0f / float(256u - dropout_threshold(p));
+}
 // keep word of columns [32*g32, 32*g32 + 32) of (row, layer): bit i set <=> column 32*g32 + i is kept
 __host__ __device__ __forceinline__ uint32_t dropout_keep_word(uint64_t seed, uint32_t layer, uint64_t row, uint32_t g32, uint32_t thr) {
   const Philox4 a = philox4x32(uint32_t(row), uint32_t(row >> 32), layer, 2u * g32, uint32_t(seed), uint32_t(seed >> 32));

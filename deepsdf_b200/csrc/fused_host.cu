@@ -292,7 +292,7 @@ static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const
   a.use_tanh = desc->use_tanh;
   a.training = tr->training;
   a.drop_thr = dropout_threshold(desc->dropout_prob);
-  a.drop_scale = 1.0f / (1.0f - desc->dropout_prob);   // F.dropout scaling with the nominal p
+  a.drop_scale = dropout_scale(desc->dropout_prob);    // 1 / (1 - effective p): E[keep * scale] == 1
   a.seed = tr->seed;
   philox_round_keys(tr->seed, a.philox_rk);
   a.row0 = tr->row0;

@@ -368,9 +368,9 @@ extern "C" int dsdf_generic_forward(const dsdf_net_desc* d, const dsdf_params* p
   const int nl = d->num_linear, L = d->latent_size, D = d->geom_dim, LD = L + D;
   if (int e = fold_all(d, p, ws, g, st)) return e;
   const uint32_t thr = dropout_threshold(d->dropout_prob);
-  const float scale = 1.f / (1.f - d->dropout_prob);   // F.dropout scaling 1/(1-p) with the nominal p
+  const float scale = dropout_scale(d->dropout_prob);   // 1 / (1 - effective p), see common.cuh
   const uint32_t thr_lat = dropout_threshold(0.2f);
-  const float scale_lat = 1.f / (1.f - 0.2f);
+  const float scale_lat = dropout_scale(0.2f);
   // x0 = [dropout(latent), xyz]  (deep_sdf_decoder.py:77-84)
   const int ndrop = (d->latent_dropout && training && LD > D) ? L : 0;
   copy_cols_kernel<<<nblk(N * LD, 256), 256, 0, st>>>(input, LD, 0, ws + g.x[0], LD, 0, N, LD, 0, ndrop, seed, row0, thr_lat, scale_lat);
@@ -420,9 +420,9 @@ extern "C" int dsdf_generic_backward(const dsdf_net_desc* d, const dsdf_params* 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nl = d->num_linear, L = d->latent_size, D = d->geom_dim, LD = L + D;
   const uint32_t thr = dropout_threshold(d->dropout_prob);
-  const float scale = 1.f / (1.f - d->dropout_prob);   // F.dropout scaling 1/(1-p) with the nominal p
+  const float scale = dropout_scale(d->dropout_prob);   // 1 / (1 - effective p), see common.cuh
   const uint32_t thr_lat = dropout_threshold(0.2f);
-  const float scale_lat = 1.f / (1.f - 0.2f);
+  const float scale_lat = dropout_scale(0.2f);
   if (grad_input) DSDF_CHECK_CUDA(cudaMemsetAsync(grad_input, 0, size_t(N) * LD * sizeof(float), st));
   float* dy = ws + g.da;      // dY of the current layer, ld = ldy
   float* dx = ws + g.db;

@@ -121,7 +121,7 @@ extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, con
   a.w_last = reinterpret_cast<const float*>(p + lo.off_wlast);
   a.dy = bufs->dy;
   a.bitmask = bufs->bitmask;
-  const float sc = 1.0f / (1.0f - desc->dropout_prob);
+  const float sc = dropout_scale(desc->dropout_prob);
   for (int l = 0; l < lo.num_hidden; ++l) {
     a.scale[l] = (training && ((desc->dropout_mask >> l) & 1)) ? sc : 1.0f;
     const bool sums = (sum_mask >> l) & 1u;

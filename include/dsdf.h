@@ -82,6 +82,9 @@ int dsdf_dropout_mask(uint64_t seed, uint32_t layer, uint64_t row0, int64_t n_ro
                       uint8_t* mask_out, void* stream);
 /* effective drop probability round(p*256)/256 actually applied (host function) */
 float dsdf_dropout_effective_p(float p);
+/* the factor survivors are multiplied by: 1 / (1 - dsdf_dropout_effective_p(p)), so that E[keep * scale] == 1 exactly and
+ * train- and eval-mode activations agree in expectation like F.dropout's (deep_sdf_decoder.py:105-106).  Host function. */
+float dsdf_dropout_scale(float p);
 
 /* ------------------------------------------------------------------------------------------------
  * Generic path: any NetworkSpecs (small nets, LayerNorm, xyz_in_all, geom_dim != 3).  fp32 CUDA-core kernels.

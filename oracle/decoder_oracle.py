@@ -31,6 +31,13 @@ import torch
 import torch.nn.functional as F
 
 
+def kernel_dropout_scale(p: float) -> float:
+    """1 / (1 - effective p) of the CUDA kernels' 8-bit Philox dropout (csrc/common.cuh dropout_scale): the keep
+    probability is (256 - round(256 p)) / 256.  Not reference semantics - only for tests that share the kernels' masks."""
+    thr = min(255, max(0, int(p * 256.0 + 0.5)))
+    return 256.0 / (256 - thr)
+
+
 # --------------------------------------------------------------------------------------
 # network description (deep_sdf_decoder.py:10-73)
 # --------------------------------------------------------------------------------------
@@ -47,6 +54,11 @@ class OracleSpec:
     xyz_in_all: Optional[bool] = None
     use_tanh: bool = False
     latent_dropout: bool = False
+    # Inverted-dropout scale of the survivors.  None = the reference's F.dropout: 1 / (1 - p) (deep_sdf_decoder.py:105-106).
+    # The CUDA kernels draw 8-bit Philox numbers, so their keep probability is (256 - round(256 p)) / 256 and they scale
+    # by its reciprocal; a test that hands the kernels' masks to the oracle sets this to the same number
+    # (kernel_dropout_scale) so that both sides evaluate the same function.
+    dropout_scale: Optional[float] = None
     # derived
     full_dims: List[int] = field(default_factory=list)
     in_dims: List[int] = field(default_factory=list)
@@ -72,6 +84,14 @@ class OracleSpec:
     @property
     def num_linear(self) -> int:
         return len(self.full_dims) - 1
+
+    def drop_scale(self) -> float:
+        return float(self.dropout_scale) if self.dropout_scale is not None else 1.0 / (1.0 - self.dropout_prob)
+
+    def latent_drop_scale(self) -> float:
+        # latent_dropout uses p = 0.2 whatever dropout_prob says (deep_sdf_decoder.py:81); with the kernels' masks the
+        # scale follows the same 8-bit quantisation as dropout_scale
+        return kernel_dropout_scale(0.2) if self.dropout_scale is not None else 1.0 / (1.0 - 0.2)
 
     def is_weight_normed(self, layer: int) -> bool:
         # deep_sdf_decoder.py:50
@@ -168,7 +188,7 @@ def decoder_forward(spec: OracleSpec, params: Dict[str, torch.Tensor], inp: torc
         if training:
             if latent_mask is None:
                 raise ValueError("training with latent_dropout needs latent_mask")
-            lat = lat * latent_mask / (1.0 - 0.2)                          # :81 F.dropout(p=0.2)
+            lat = lat * latent_mask * spec.latent_drop_scale()             # :81 F.dropout(p=0.2)
         x = torch.cat([lat, xyz], 1)                                      # :82
     else:
         x = inp                                                           # :84
@@ -189,7 +209,7 @@ def decoder_forward(spec: OracleSpec, params: Dict[str, torch.Tensor], inp: torc
             if spec.dropout is not None and layer in spec.dropout and training and spec.dropout_prob > 0:
                 if masks is None or layer not in masks:                   # :105-106
                     raise ValueError(f"training forward needs an explicit mask for layer {layer}")
-                x = x * masks[layer] / (1.0 - spec.dropout_prob)
+                x = x * masks[layer] * spec.drop_scale()
     return torch.tanh(x)                                                  # :108-109 (self.th always exists)
 
 
@@ -457,11 +477,11 @@ def decoder_forward_bf16_operands(spec: OracleSpec, params, lat_rows: torch.Tens
         if gates is not None:
             h = h * gates[l]
             if drop:
-                h = h / (1.0 - spec.dropout_prob)
+                h = h * spec.drop_scale()
         else:
             h = torch.relu(h)
             if drop:
-                h = h * masks[l] / (1.0 - spec.dropout_prob)
+                h = h * masks[l] * spec.drop_scale()
         a = _RoundBF16.apply(h)
     y = h @ effective_weight(spec, params, nh).t() + params[f"lin{nh}.bias"]
     if spec.use_tanh:

@@ -29,6 +29,7 @@ def _setup(name, out_scale=0.025, p_drop=None):
     if p_drop is not None:
         kw["dropout_prob"] = p_drop
     ospec = O.OracleSpec(**kw)
+    ospec.dropout_scale = O.kernel_dropout_scale(ospec.dropout_prob)      # the kernels' masks are handed to the oracle
     params = sdf_scale_params(ospec, META[name]["seed"], out_scale=out_scale)
     mod = build_module(kw, params, DEV)
     return kw, ospec, params, mod, FusedEngine(mod)
@@ -127,7 +128,7 @@ def test_fused_train_step_grads(name, drop):
                 x = torch.cat([x, torch.cat([table_o[row_scene], xyz], 1)], 1)
             x = torch.relu(torch.nn.functional.linear(x, O.effective_weight(ospec, params, l), params[f"lin{l}.bias"]))
             if drop > 0:
-                x = x * masks[l] / (1.0 - drop)
+                x = x * masks[l] * ospec.drop_scale()
             flips += int(((x > 0).float() != gates[l]).sum())
             tot += x.numel()
     print(f"   gates differing from the fp32 forward: {flips} of {tot} ({flips / tot:.2e})")

@@ -96,6 +96,7 @@ def test_training_mode_with_shared_dropout_masks(name):
     m, pre, table, rows, xyz, gt = _inputs(name)
     kw = m["spec"]
     ospec = O.OracleSpec(**kw)
+    ospec.dropout_scale = O.kernel_dropout_scale(float(ospec.dropout_prob))   # shared masks: the kernels' survivor scale
     params = O.make_params(ospec, m["seed"])
     mod = build_module(kw, params, DEV).train()
     inp_cpu = torch.cat([table[rows], xyz], 1)

@@ -26,6 +26,7 @@ def test_loss_curve_50_epochs_within_one_percent():
              "SamplesPerScene": 1024, "ScenesPerBatch": 4, "ClampingDistance": 0.1, "CodeRegularization": True,
              "CodeRegularizationLambda": 1e-4, "CodeBound": 1.0}
     ospec = O.OracleSpec(**kw)
+    ospec.dropout_scale = O.kernel_dropout_scale(0.2)          # shared masks: same survivor scale as the kernels
     params = sdf_scale_params(ospec, 7, out_scale=0.025)
     S_total, S, sps, epochs = 6, 4, 1024, 50
     rng = np.random.RandomState(1)

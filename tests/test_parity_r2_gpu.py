@@ -1,0 +1,297 @@
+"""Round-2 parity evidence for the fused tcgen05 path on TRAINED weights and UNFILTERED batches.
+
+What the round-1 tests left open, and what each test here pins down:
+
+  * test_unfiltered_gradients_vs_fp32_reference   gradients of a realistic, unconditioned batch (8 scenes x 1024 rows, the
+        config #2 network after a few hundred optimiser steps) against the PURE fp32 oracle (the reference's arithmetic)
+        and against the operand-precision oracle WITHOUT any gate hand-over.  The measured relative norms are printed
+        per tensor and asserted at the level actually achieved; DESIGN.md section 5 quotes them beside the north star's 1e-2.
+  * test_gate_words_are_what_the_stash_and_philox_say   independent verification of the 1-bit gates the backward consumes:
+        gate bit == (stashed activation != 0), gate implies the Philox keep bit, padded columns carry no gate.
+  * test_sdf_parity_trained_weights_natural_scale   SDF of a 64^3 create_mesh grid on the trained decoder (|sdf| up to the
+        natural output range, far outside the clamp band) against the fp32 oracle.
+  * test_dropout_keep_rate_and_scale_are_unbiased / test_dropout_train_mode_expectation_equals_eval   the inverted-dropout
+        scale is 1 / (1 - effective p): E[keep * scale] == 1 and E[train-mode pre-activation] == eval-mode value.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from deepsdf_b200 import _lib as L
+from oracle import decoder_oracle as O
+from tests.util import build_module, unpack_gate_bits
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+NET = dict(dims=[512] * 8, dropout=list(range(8)), dropout_prob=0.2, norm_layers=list(range(8)), latent_in=[4],
+           xyz_in_all=False, use_tanh=False, latent_dropout=False, weight_norm=True, geom_dimension=3)
+LAT = 256
+SPECS = {"NetworkSpecs": NET, "CodeLength": LAT,
+         "LearningRateSchedule": [{"Type": "Step", "Initial": 0.0005, "Interval": 500, "Factor": 0.5},
+                                  {"Type": "Step", "Initial": 0.001, "Interval": 500, "Factor": 0.5}],
+         "SamplesPerScene": 2048, "ScenesPerBatch": 8, "ClampingDistance": 0.1, "CodeRegularization": True,
+         "CodeRegularizationLambda": 1e-4, "CodeBound": 1.0}
+S_TOTAL, STORED = 16, 8192
+_CACHE = {}
+
+
+def _scene_data(seed=3):
+    """[S_TOTAL, STORED, 4] (x, y, z, sdf) of the corner-spheres family at its NATURAL scale (sdf in about -0.5 .. 0.9),
+    evaluation_scripts/04_simple_geom_creation.py:24-29 / sdf_sampler/microstructures.py:23-36."""
+    rng = np.random.RandomState(seed)
+    xyz = rng.uniform(-1, 1, (S_TOTAL, STORED, 3)).astype(np.float32)
+    sdf = np.stack([O.corner_spheres_sdf(xyz[s], 0.4 + 0.6 * s / (S_TOTAL - 1), limit=0.9) for s in range(S_TOTAL)])
+    return torch.from_numpy(np.concatenate([xyz, sdf.reshape(S_TOTAL, STORED, 1).astype(np.float32)], -1))
+
+
+def trained():
+    """The config #2 decoder (8x512, L = 256) after 300 optimiser steps of the fused trainer on the analytic family:
+    (ospec, params (CPU fp32 clones), module, trainer, latent table (CPU), data)."""
+    if "t" in _CACHE:
+        return _CACHE["t"]
+    from deepsdf_b200.trainer import SceneTrainer
+    data = _scene_data()
+    tr = SceneTrainer(SPECS, S_TOTAL, DEV, seed=5)
+    g = torch.Generator().manual_seed(9)
+    data_d = data.to(DEV)
+    losses = []
+    for it in range(300):
+        ids = torch.randperm(S_TOTAL, generator=g)[:8].sort().values
+        sel = torch.randperm(STORED, generator=g)[:2048].to(DEV)
+        batch = data_d[ids.to(DEV)][:, sel].reshape(-1, 4).contiguous()
+        loss = tr.step(batch, ids.to(DEV), epoch=1 + it // 2)
+        if it % 50 == 0 or it == 299:
+            losses.append(float(loss[0].cpu()))
+    print("training losses (every 50 steps):", ["%.4f" % x for x in losses])
+    assert losses[-1] < 0.6 * losses[0]
+    kw = dict(latent_size=LAT, **NET)
+    ospec = O.OracleSpec(**kw)
+    ospec.dropout_scale = O.kernel_dropout_scale(NET["dropout_prob"])
+    mod = tr.decoder
+    params = {k: v.detach().cpu().clone() for k, v in mod.state_dict().items()}
+    _CACHE["t"] = (ospec, params, mod, tr, tr.lat_vecs.detach().cpu().clone(), data)
+    return _CACHE["t"]
+
+
+def _masks(eng, ospec, seed, n, p):
+    out = {}
+    for l in range(ospec.num_linear - 1):
+        buf = torch.empty(n, ospec.out_dims[l], dtype=torch.uint8, device=DEV)
+        L.check(eng.lib.dsdf_dropout_mask(seed, l, 0, n, ospec.out_dims[l], p, buf.data_ptr(), None))
+        out[l] = buf.cpu().float()
+    return out
+
+
+def _unfiltered_batch(data, scenes, rows, seed):
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.tensor(sorted(scenes), dtype=torch.int64)
+    sel = torch.randperm(STORED, generator=g)[:rows]
+    batch = data[ids][:, sel].reshape(-1, 4).contiguous()
+    return ids, batch
+
+
+def test_unfiltered_gradients_vs_fp32_reference():
+    ospec, params, mod, tr, table, data = trained()
+    eng = tr.engine
+    scenes, rows = [0, 2, 3, 5, 8, 11, 13, 15], 1024
+    ids, batch = _unfiltered_batch(data, scenes, rows, seed=21)
+    N = batch.shape[0]
+    tile_scene = torch.arange(len(scenes), dtype=torch.int32).repeat_interleave(rows // 128)
+    row_scene = ids.repeat_interleave(rows)
+    seed, clampd, lam_eff = 991, 0.1, 1e-4 * 0.5
+    masks = _masks(eng, ospec, seed, N, NET["dropout_prob"])
+    tab_d = table.clone().to(DEV)
+    grads, PG = eng.alloc_grads()
+    lat_grad = torch.zeros_like(tab_d)
+    smp = batch.to(DEV)
+    flat = smp.view(-1)
+    eng.repack()
+    loss = eng.loss_and_grads(tab_d, ids.to(DEV), tile_scene.to(DEV), flat, flat[3:], clamp=clampd, reg_lambda_eff=lam_eff,
+                              n_total=N, code_bound=1.0, seed=seed, row0=0, PG=PG, lat_grad=lat_grad, point_stride=4,
+                              gt_stride=4, n_rows=N)
+    torch.cuda.synchronize()
+    loss_v = [float(x) for x in loss.cpu()]
+    table_o = table.clone()
+    O.embedding_renorm_(table_o, row_scene, 1.0)
+    xyz, gt = batch[:, :3].contiguous(), batch[:, 3].contiguous()
+    # (1) the reference's own arithmetic: fp32 everywhere, its own relu gates, the shared dropout masks
+    P = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    Z = table_o.clone().requires_grad_(True)
+    bv = Z[row_scene]
+    pred = O.decoder_forward(ospec, P, torch.cat([bv, xyz], 1), training=True, masks=masks)
+    data_t = (pred.clamp(-clampd, clampd) - gt.reshape(-1, 1).clamp(-clampd, clampd)).abs().sum() / N
+    total = data_t + lam_eff * torch.sum(torch.norm(bv, dim=1)) / N
+    total.backward()
+    raw = pred.detach().squeeze(1)
+    print(f"unfiltered batch: {N} rows, |pred| max {raw.abs().max():.3f}, inside the clamp band {float((raw.abs() < clampd).float().mean()):.2f}, "
+          f"|pred - gt| < 1e-3 for {int(((raw.clamp(-clampd, clampd) - gt.clamp(-clampd, clampd)).abs() < 1e-3).sum())} rows")
+    print(f"loss: kernel {loss_v[0]:.6f} / data {loss_v[1]:.6f}   fp32 reference {float(total):.6f} / {float(data_t):.6f}")
+    assert abs(loss_v[0] - float(total)) <= 5e-3 * abs(float(total))
+    # (2) exact gradient of a bf16-operand forward with ITS OWN gates (no hand-over from the kernel)
+    _, gq, zq, _ = O.train_loss_and_grads_bf16_operands(ospec, params, table_o, row_scene, xyz, gt, clampd, lam_eff, N,
+                                                        masks=masks, gates=None)
+    names = mod.flat_param_names()
+    worst32 = worstq = 0.0
+    mincos = 1.0
+    print(f"   {'tensor':48s} rel-norm vs fp32   cos      rel-norm vs bf16-operand oracle (own gates)")
+    for n_, g in zip(names, grads):
+        g = g.cpu()
+        r32 = P[n_].grad
+        rel32 = float((g - r32).norm() / (r32.norm() + 1e-30))
+        cos32 = float((g.flatten() @ r32.flatten()) / (g.norm() * r32.norm() + 1e-30))
+        relq = float((g - gq[n_]).norm() / (gq[n_].norm() + 1e-30))
+        # what two fp32-exact gradients of the SAME function at two operand precisions differ by (the floor of this comparison)
+        floor = float((gq[n_] - r32).norm() / (r32.norm() + 1e-30))
+        print(f"   {n_:48s} {rel32:.3e}   {cos32:.5f}   {relq:.3e}   (bf16-operand oracle vs fp32 oracle: {floor:.3e})")
+        worst32, worstq, mincos = max(worst32, rel32), max(worstq, relq), min(mincos, cos32)
+    lrel32 = float((lat_grad.cpu() - Z.grad).norm() / Z.grad.norm())
+    lrelq = float((lat_grad.cpu() - zq).norm() / zq.norm())
+    print(f"   latent gradient: vs fp32 {lrel32:.3e}, vs bf16-operand oracle {lrelq:.3e}")
+    print(f"   WORST: vs fp32 {worst32:.3e} (min cos {mincos:.5f}); vs bf16-operand oracle without gate hand-over {worstq:.3e}")
+    # asserted at the level this arithmetic achieves on an unconditioned batch (numbers in DESIGN.md section 5)
+    assert worst32 <= 0.25 and mincos >= 0.97 and lrel32 <= 0.25
+    assert worstq <= 0.25 and lrelq <= 0.25
+
+
+def test_gate_words_are_what_the_stash_and_philox_say():
+    ospec, params, mod, tr, table, data = trained()
+    eng = tr.engine
+    scenes, rows = [1, 4, 6, 7, 9, 10], 512
+    ids, batch = _unfiltered_batch(data, scenes, rows, seed=33)
+    N = batch.shape[0]
+    tile_scene = torch.arange(len(scenes), dtype=torch.int32).repeat_interleave(rows // 128)
+    seed = 4711
+    masks = _masks(eng, ospec, seed, N, NET["dropout_prob"])
+    tab_d = table.clone().to(DEV)
+    grads, PG = eng.alloc_grads()
+    lat_grad = torch.zeros_like(tab_d)
+    flat = batch.to(DEV).view(-1)
+    eng.repack()
+    eng.loss_and_grads(tab_d, ids.to(DEV), tile_scene.to(DEV), flat, flat[3:], clamp=0.1, reg_lambda_eff=0.0, n_total=N,
+                       code_bound=1.0, seed=seed, row0=0, PG=PG, lat_grad=lat_grad, point_stride=4, gt_stride=4, n_rows=N)
+    torch.cuda.synchronize()
+    nh = ospec.num_linear - 1
+    gates = unpack_gate_bits(eng._bufs["bitmask"], ospec, N)
+    acts = eng._bufs["acts"].view(torch.bfloat16)[:nh * N * 512].view(nh, N, 512).float().cpu()
+    words = eng._bufs["bitmask"].view(torch.int32)[:nh * (N // 128) * 16 * 128].reshape(nh, N // 128, 16, 128).cpu()
+    tot = 0
+    for l in range(nh):
+        od = ospec.out_dims[l]
+        gate, keep, nz = gates[l].bool(), masks[l].bool(), acts[l][:, :od] != 0
+        assert not (gate & ~keep).any(), f"layer {l}: a gate is open where Philox dropped the unit"
+        assert not (nz & ~gate).any(), f"layer {l}: a stashed activation is non-zero behind a closed gate"
+        # gate open with a stashed zero: only a positive pre-activation that rounds to bf16 zero could do that
+        lost = int((gate & ~nz).sum())
+        assert lost <= 1e-6 * gate.numel() + 1, (l, lost)
+        tot += gate.numel()
+        if od < 512:     # padded columns of a narrow layer: no gate bits, zero activations
+            full = ((words[l].permute(0, 2, 1).reshape(N, 16).numpy().astype(np.uint32)[:, :, None] >> np.arange(32, dtype=np.uint32)) & 1).reshape(N, 512)
+            assert not full[:, od:].any() and not (acts[l][:, od:] != 0).any()
+        frac = float(gate.float().mean())
+        print(f"layer {l}: open gates {frac:.3f} (keep rate {float(keep.float().mean()):.4f})")
+        assert 0.05 < frac < 0.8
+    # and against the fp32 oracle's own gates: they differ only where a pre-activation sits within bf16 noise of zero
+    with torch.no_grad():
+        tab_o = table.clone()
+        row_scene = ids.repeat_interleave(rows)
+        O.embedding_renorm_(tab_o, row_scene, 1.0)
+        inp = torch.cat([tab_o[row_scene], batch[:, :3]], 1)
+        x, flips = inp, 0
+        for l in range(nh):
+            if l in ospec.latent_in:
+                x = torch.cat([x, inp], 1)
+            x = torch.relu(torch.nn.functional.linear(x, O.effective_weight(ospec, params, l), params[f"lin{l}.bias"]))
+            x = x * masks[l] * ospec.drop_scale()
+            flips += int(((x > 0) != gates[l].bool()).sum())
+    print(f"gates differing from the fp32 reference forward: {flips} of {tot} ({flips / tot:.2e})")
+    assert flips / tot <= 1e-2
+
+
+def test_sdf_parity_trained_weights_natural_scale():
+    from deepsdf_b200.mesh import create_mesh_sdf
+    ospec, params, mod, tr, table, data = trained()
+    mod.eval()
+    NG = 64
+    lat = table[5].clone()
+    if float(lat.norm()) > 1.0:
+        lat = lat / float(lat.norm())
+    vol = create_mesh_sdf(mod, lat, N=NG).reshape(-1).cpu()
+    mod.train()
+    idx = torch.arange(NG ** 3)
+    vs = 2.0 / (NG - 1)
+    xyz = torch.stack([(idx // (NG * NG)) * vs - 1, ((idx // NG) % NG) * vs - 1, (idx % NG) * vs - 1], 1).float()   # mesh.py:45-52
+    ref = torch.empty(NG ** 3)
+    with torch.no_grad():
+        for s in range(0, NG ** 3, 32768):
+            q = xyz[s:s + 32768]
+            ref[s:s + 32768] = O.decoder_forward(ospec, params, torch.cat([lat.expand(q.shape[0], -1), q], 1)).squeeze(1)
+    err = (vol - ref).abs()
+    band = ref.abs() <= 0.1
+    print(f"64^3 grid, trained 8x512 L=256: sdf range [{float(ref.min()):.3f}, {float(ref.max()):.3f}], std {float(ref.std()):.3f}; "
+          f"{float(band.float().mean()):.2f} of the points inside the clamp band")
+    print(f"   all points : max abs err {float(err.max()):.3e}, mean {float(err.mean()):.3e}, p99 {float(err.kthvalue(int(0.99 * err.numel())).values):.3e}")
+    print(f"   |sdf|<=0.1 : max abs err {float(err[band].max()):.3e}, mean {float(err[band].mean()):.3e}")
+    if (~band).any():
+        rel = err[~band] / ref[~band].abs()
+        print(f"   |sdf|> 0.1 : max abs err {float(err[~band].max()):.3e}, mean {float(err[~band].mean()):.3e}, max relative {float(rel.max()):.3e}")
+        assert float(rel.max()) <= 5e-2
+    # sign agreement away from the surface: what marching cubes consumes
+    far = ref.abs() > 2e-3
+    assert bool(((vol > 0) == (ref > 0))[far].all())
+    assert float(err[band].max()) <= 2e-3            # the north star's tolerance where the loss is sensitive
+    assert float(err.mean()) <= 1e-3
+    assert float(err.max()) <= 1e-2
+
+
+def test_dropout_keep_rate_and_scale_are_unbiased():
+    lib = L.lib()
+    for p in (0.2, 0.1, 0.5, 0.05):
+        n, w, kept = 8192, 512, 0
+        for layer in range(4):
+            buf = torch.empty(n, w, dtype=torch.uint8, device=DEV)
+            L.check(lib.dsdf_dropout_mask(12345 + layer, layer, 7 * layer, n, w, p, buf.data_ptr(), None))
+            kept += int(buf.sum())
+        tot = 4 * n * w
+        rate = kept / tot
+        eff = lib.dsdf_dropout_effective_p(p)
+        scale = lib.dsdf_dropout_scale(p)
+        sigma = math.sqrt(eff * (1 - eff) / tot)
+        print(f"p = {p}: effective p {eff:.6f}, keep rate {rate:.6f} (expected {1 - eff:.6f}, sigma {sigma:.1e}), scale {scale:.6f}, "
+              f"E[keep * scale] = {rate * scale:.6f}; with the nominal 1/(1-p) it would be {rate / (1 - p):.6f}")
+        assert abs(rate - (1 - eff)) <= 5 * sigma
+        assert abs(scale * (1 - eff) - 1.0) <= 1e-6
+        assert abs(rate * scale - 1.0) <= 5 * sigma * scale
+
+
+@pytest.mark.parametrize("p", [0.2, 0.1])
+def test_dropout_train_mode_expectation_equals_eval(p):
+    """One hidden layer: the pre-tanh output is LINEAR in the dropout mask, so its train-mode expectation must equal the
+    eval-mode value (F.dropout's contract, deep_sdf_decoder.py:105-106).  A million rows with the same input draw a
+    million independent masks (the Philox stream is keyed by the row id).  With survivors scaled by the nominal 1/(1-p)
+    the mean is off by (1-eff)/(1-p) - 1 = +0.1 % (p = 0.2) / -0.17 % (p = 0.1): many sigma at this sample size."""
+    kw = dict(latent_size=2, dims=[64], geom_dimension=3, dropout=[0], dropout_prob=p, norm_layers=[], latent_in=[],
+              weight_norm=False, xyz_in_all=False, use_tanh=False, latent_dropout=False)
+    ospec = O.OracleSpec(**kw)
+    params = O.make_params(ospec, 11)
+    params["lin1.weight"] = params["lin1.weight"].abs() * 0.15 + 0.01       # keep the pre-tanh sum well conditioned
+    params["lin1.bias"] = params["lin1.bias"] * 0 + 0.02
+    mod = build_module(kw, params, DEV)
+    x1 = torch.tensor([[0.3, -0.2, 0.5, 0.1, -0.4]])
+    n = 1 << 20
+    inp = x1.expand(n, -1).contiguous().to(DEV)
+    with torch.no_grad():
+        y_eval = float(mod.eval()(inp[:8])[0])
+        torch.manual_seed(3)
+        y_tr = mod.train()(inp).squeeze(1).double().cpu()
+    z = torch.atanh(y_tr)
+    z_eval = math.atanh(y_eval)
+    mean, stderr = float(z.mean()), float(z.std()) / math.sqrt(n)
+    eff = L.lib().dsdf_dropout_effective_p(p)
+    nominal_bias = ((1 - eff) / (1 - p) - 1.0) * (z_eval - 0.02)
+    print(f"p = {p}: eval pre-tanh {z_eval:.6f}, train-mode mean {mean:.6f} +- {stderr:.1e}; a nominal-p scale would shift it by {nominal_bias:+.2e}")
+    assert abs(nominal_bias) > 6 * stderr            # the test has the power to see the old bias
+    assert abs(mean - z_eval) <= 5 * stderr + 2e-6

@@ -74,7 +74,7 @@ def emulate_fused_forward(ospec, params, table, row_scene, xyz, masks=None):
             h = a @ bf16r(W).t() + b
         h = torch.relu(h)
         if masks is not None and l in masks:
-            h = h * masks[l] / (1.0 - ospec.dropout_prob)
+            h = h * masks[l] * ospec.drop_scale()
         acts.append(h)
         a = bf16r(h)
     Wl = O.effective_weight(ospec, params, nh)
