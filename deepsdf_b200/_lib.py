@@ -12,6 +12,7 @@ from typing import Optional, Sequence
 import torch
 
 MAX_LAYERS = 16
+ABI_VERSION = 3          # include/dsdf.h DSDF_ABI_VERSION
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("DSDF_B200_LIB") or os.path.join(_HERE, "libdsdf_b200.so")   # the override is for A/B timing of two builds
 
@@ -67,6 +68,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_fused_supported": (C.c_int, [P(NetDesc)]),
         "dsdf_pack_bytes": (sz, [P(NetDesc)]),
         "dsdf_pack_weights": (C.c_int, [P(NetDesc), P(Params), vp, vp]),
+        "dsdf_scene_aux_bytes": (sz, [i32]),
         "dsdf_scene_prepare": (C.c_int, [P(NetDesc), vp, vp, vp, i32, f32, vp, vp]),
         "dsdf_fused_forward": (C.c_int, [P(NetDesc), vp, vp, vp, vp, i32, i64, vp, P(TrainIO), vp]),
         "dsdf_fused_forward_rows": (C.c_int, [P(NetDesc), vp, vp, i32, i64, vp, P(TrainIO), vp]),
@@ -79,6 +81,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_iso_count": (C.c_int, [vp, i32, i32, i32, f32, vp, vp]),
         "dsdf_iso_emit": (C.c_int, [vp, i32, i32, i32, f32, P(f32), P(f32), vp, vp, vp]),
         "dsdf_selftest_umma_pair": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp]),
+        "dsdf_selftest_umma_aux": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, vp]),
         "dsdf_selftest_umma": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint,
                                          C.c_uint, vp]),
     }
@@ -99,7 +102,7 @@ def lib() -> C.CDLL:
                 "or `make -C deepsdf_b200/csrc` (there is no fallback path)")
         _lib = C.CDLL(LIB_PATH)
         _declare(_lib)
-        if _lib.dsdf_abi_version() != 2:
+        if _lib.dsdf_abi_version() != ABI_VERSION:
             raise DsdfError("libdsdf_b200.so ABI version mismatch")
     return _lib
 

@@ -4,8 +4,9 @@
 // .. 0 the kernel produces
 //   dY_t = dX_{t+1} (.) gate_t        dX_{t+1} = dY_{t+1} . W_{t+1}   (tensor cores, W^T streamed through the TMA ring)
 // with dY of the last hidden layer seeded by the rank-1 product dL/dy * w_last.  The dY tile lives in shared memory as
-// bf16 (SW128: the A operand of the next chain link), the gates are the 1-bit relu*dropout words written by the forward,
-// and the dropout scale is applied with the gate.  Once a tile of dY_t is complete the 16 epilogue warps also emit
+// bf16 (SW128: the A operand of the next chain link), the gates are the 1-bit relu*dropout words written by the forward;
+// the inverted-dropout scale lives in the packed W^T blocks (training variant of the pack, fused_host.cu), so the
+// epilogue only gates.  Once a tile of dY_t is complete the 16 epilogue warps also emit
 //   * its column sums (bias gradients; the per-scene sums of dY_0 / dY_skip ARE the latent-code gradient up to a tiny
 //     [S x 512] x [512 x L] product, so the latent-gradient reduction is a fixed-order sum of per-tile partials),
 //   * the xyz-weighted column sums of dY_0 / dY_skip (gradients of the xyz weight columns),
@@ -35,7 +36,7 @@ constexpr int B_SMEM = B_OFF_XYZ + 3 * TILE_M * 4 + 1024;
 __device__ __forceinline__ void bwd_bar() { asm volatile("bar.sync 1, %0;" ::"n"(B_EPI_THREADS) : "memory"); }
 
 // 16 columns [c0, c0+16) of one row: v = accumulators (or dy * w_last), gated and scaled, packed to bf16 into the A tile
-__device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float dyv, uint32_t swl, uint32_t gate16, float scale,
+__device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float dyv, uint32_t swl, uint32_t gate16,
                                            uint32_t st0, uint32_t st1) {
   // swl / st0 / st1: SHARED-space byte addresses (explicit ld/st.shared); st0, st1 = the two 16-byte pieces of this row's
   // SW128 line that receive the 16 columns, formed once per thread
@@ -45,12 +46,12 @@ __device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float d
     tmem_ld16(taddr, r);
     tmem_ld_wait();
 #pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]) * scale;
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
   } else {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float4 w = lds_f32x4(swl + 16 * k);
-      const float d = dyv * scale;
+      const float d = dyv;
       v[4 * k + 0] = d * w.x; v[4 * k + 1] = d * w.y; v[4 * k + 2] = d * w.z; v[4 * k + 3] = d * w.w;
     }
   }
@@ -270,7 +271,6 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       for (int t = nh - 1; t >= 0; --t) {
         const bool has_acc = (t < nh - 1);
         const int n_halves = has_acc ? args.prog[t + 1].n_halves : 2;
-        const float scale = args.scale[t];
         const bool produce_a = (t > 0);
         // gate words of this row: word 4*Q + j of [layer][tile][16][128]
         const uint32_t* mrow = args.bitmask + ((size_t(t) * tiles_alloc + tile_c) * MASK_WORDS + j) * TILE_M + rt;
@@ -287,8 +287,8 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           // the previous dY tile's quarter must have been stashed and column-summed before it is overwritten
           if ((wany >> Q) & 1u) mbar_wait(&bar_q_released[Q], ((wpar >> Q) & 1u) ^ 1u);
           const uint32_t qoff = uint32_t(Q) * 2u * A_CHUNK_BYTES;
-          bwd_pass16(tmem_row + c0, has_acc, dyv, swl_a + c0 * 4, gate, scale, st_a0 + qoff, st_a1 + qoff);
-          bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, swl_a + (c0 + 16) * 4, gate >> 16, scale, st_a2 + qoff, st_a3 + qoff);
+          bwd_pass16(tmem_row + c0, has_acc, dyv, swl_a + c0 * 4, gate, st_a0 + qoff, st_a1 + qoff);
+          bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, swl_a + (c0 + 16) * 4, gate >> 16, st_a2 + qoff, st_a3 + qoff);
           fence_proxy_async_smem();
           tc_fence_before();
           __syncwarp();

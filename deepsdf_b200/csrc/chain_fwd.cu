@@ -4,19 +4,25 @@
 // bf16 in its own shared memory, its accumulators [128 x 512] fp32 in its own TMEM) and the pair shares every weight
 // tile: for a [256 out x 64 K] weight block each CTA TMA-loads only its 128 output rows, and one tcgen05.mma
 // (cta_group::2, M = 256 over the pair, N = 256, K = 16) issued by the leader CTA multiplies both activation tiles with
-// both halves.  That halves the L2 -> SM weight traffic and the shared-memory space of the weight ring per row, which
-// is what makes room for a 5-stage ring, bias / xyz-weight staging and 16 epilogue warps.
+// both halves.  That halves the L2 -> SM weight traffic and the shared-memory space of the weight ring per row.
 //
-// Per layer, per pair:   MMA order  (half 0: K chunks 0..7), (half 1: K chunks 0..7)
-//   * tmem_full[0] (multicast commit) -> both CTAs' epilogues post-process accumulator half 0 into REGISTERS while the
-//     tensor cores compute half 1;  free_lo (commit after half 1's K chunk 3) says activation chunks 0..3 are no longer
-//     read, so half 0 is written into the A tile before the layer's MMAs have even finished;
+// Everything that is NOT a hidden-activation product enters through one extra K = 16 "aux" step per accumulator half
+// (fused.cuh): the layer bias, the per-scene bias of lin0 / the latent_in layer (bias + latent columns . z, one vector per
+// scene), the xyz columns and - in row-latent mode - the per-row latent columns.  Their values are split hi + lo into
+// bf16 pairs so the products keep ~16 mantissa bits.  The aux A block [128 x 32] is written once per tile by the
+// epilogue threads, the aux B blocks ride in the weight ring.  So lin0 is a (tiny) tensor-core layer like the others, every
+// layer's epilogue is the same code, and the dropout scale 1/(1-p) is folded into the NEXT layer's packed weights
+// (fused_host.cu), which leaves the epilogue without a single multiply-add:
+//   TMEM load -> sign-bit funnel -> ReLU gate word AND bit-sliced Philox keep word -> select -> bf16 pack -> STS.128
+//
+// Per layer, per pair:   MMA order  (half 0: aux, K chunks 0..7), (half 1: aux, K chunks 0..7)
+//   * tmem_full[0] (multicast commit) -> both CTAs' epilogues post-process accumulator half 0 while the tensor cores
+//     compute half 1;  free_q0 / free_lo (commits after half 1's K chunks 1 / 3) say activation chunks 0..1 / 2..3 are no
+//     longer read, so half 0 is written into the A tile before the layer's MMAs have even finished;
 //   * tmem_full[1] -> half 1 is post-processed and written quarter by quarter (128 columns); the next layer's MMAs start
 //     on the K chunks that are already there (a_ready[0..3], one mbarrier per quarter, arrivals from both CTAs).
-// Epilogue per element: FFMA (bias and dropout scale folded, bias staged in shared memory), sign-bit funnel -> ReLU
-// gate word, AND with the bit-sliced Philox keep word (computed before the accumulators are ready), select, bf16 pack.
 // The final 512 -> 1 layer, tanh, clamp, L1 loss and dL/dy are fused into the last epilogue; in training every layer's
-// activation tile is TMA-stored (bf16) for wgrad together with its 1-bit gates.
+// activation tile is TMA-stored (bf16, UNSCALED: relu(h) * keep) for wgrad together with its 1-bit gates.
 // Replaces Decoder.forward (deep_sdf/networks/deep_sdf_decoder.py:76-111) and train_deep_sdf.py:511-519.
 #include <type_traits>
 
@@ -36,76 +42,28 @@ constexpr int P_EPI_REGS = 112, P_SVC_REGS = 24;       // register re-split: 16 
 constexpr int P_STAGES = 5;
 constexpr int P_STAGE_BYTES = 128 * 128;               // this CTA's half ([128 out rows][64 K] bf16) of a weight block
 constexpr int P_OFF_B = A_BYTES;
-constexpr int P_OFF_BIAS = P_OFF_B + P_STAGES * P_STAGE_BYTES;   // f32 [2][512]  (double-buffered per layer)
-constexpr int P_OFF_WXYZ = P_OFF_BIAS + 2 * FH * 4;              // f32 [3][512]
-constexpr int P_OFF_WLAST = P_OFF_WXYZ + 3 * FH * 4;             // f32 [512]
+constexpr int P_OFF_AUX = P_OFF_B + P_STAGES * P_STAGE_BYTES;    // aux A block: 4 k-cores x [128 rows][8 bf16]
+constexpr int P_OFF_WLAST = P_OFF_AUX + 4 * AUX_CORE_BYTES;      // f32 [512]
 constexpr int P_OFF_YPART = P_OFF_WLAST + FH * 4;                // f32 [4][128]
 constexpr int P_SMEM = P_OFF_YPART + 4 * TILE_M * 4 + 1024;
 
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(P_EPI_THREADS) : "memory"); }
 
 // Post-process 16 consecutive columns [c0, c0+16) of one row and write them (bf16) into the SW128 activation tile.
-//   has_acc  read the fp32 accumulators from TMEM (taddr) - false for the MMA-less first layer
-//   st0/st1  shared addresses of the two 16-byte pieces of the activation tile that receive the 16 columns
-//   sb       shared-memory bias (already multiplied by the dropout scale); swx xyz weight rows (same scaling) or null
+//   taddr    TMEM address of the 16 fp32 accumulators (bias, xyz and latent parts already inside: aux step)
 //   keep16   low 16 bits: Philox keep bits of these columns (all ones when the layer has no dropout)
-// Returns the 16 gate bits (relu AND keep); adds this row's share of the last-layer dot product to ydot.
-// kPlain: the common hidden layer (accumulators present, no per-row xyz / latent columns, not the last layer) as a
-// compile-time variant, so that its passes carry no flag handling (R2P takes all seven predicates; layer-invariant
-// conditions kept as run-time flags end up in a bit-field register that every pass re-tests).
-template <bool kTrain, bool kRowLat, bool kPlain>
-__device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc_rt, float ascale, uint32_t sb, bool has_xyz_rt, uint32_t swx,
-                                               float x, float y, float z, uint32_t keep16, bool is_last_rt, uint32_t swl,
-                                               uint32_t st0, uint32_t st1, float& ydot, const float* wl, int n_rl,
-                                               const float (&rl)[4]) {
-  // sb / swx / swl / sA are SHARED-space byte addresses (of this pass's first column where they are per column)
-  const bool has_acc = kPlain ? true : has_acc_rt, has_xyz = kPlain ? false : has_xyz_rt, is_last = kPlain ? false : is_last_rt;
+//   st0/st1  shared addresses of the two 16-byte pieces of the activation tile that receive the 16 columns
+//   kLast    last hidden layer: also accumulate this row's share of the 512 -> 1 product into ydot (swl: w_last in smem)
+// Returns the 16 gate bits (relu AND keep).
+template <bool kTrain, bool kLast>
+__device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, uint32_t keep16, uint32_t swl, uint32_t st0, uint32_t st1, float& ydot) {
   float v[16];
-  if (has_acc) {
+  {
     uint32_t r[16];
     tmem_ld16(taddr, r);
     tmem_ld_wait();
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float4 b = lds_f32x4(sb + 16 * k);
-      v[4 * k + 0] = fmaf(__uint_as_float(r[4 * k + 0]), ascale, b.x);
-      v[4 * k + 1] = fmaf(__uint_as_float(r[4 * k + 1]), ascale, b.y);
-      v[4 * k + 2] = fmaf(__uint_as_float(r[4 * k + 2]), ascale, b.z);
-      v[4 * k + 3] = fmaf(__uint_as_float(r[4 * k + 3]), ascale, b.w);
-    }
-  } else {
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float4 b = lds_f32x4(sb + 16 * k);
-      v[4 * k + 0] = b.x; v[4 * k + 1] = b.y; v[4 * k + 2] = b.z; v[4 * k + 3] = b.w;
-    }
-  }
-  if (has_xyz) {
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float4 wx = lds_f32x4(swx + 16 * k);
-      const float4 wy = lds_f32x4(swx + FH * 4 + 16 * k);
-      const float4 wz = lds_f32x4(swx + 2 * FH * 4 + 16 * k);
-      v[4 * k + 0] += x * wx.x + y * wy.x + z * wz.x;
-      v[4 * k + 1] += x * wx.y + y * wy.y + z * wz.y;
-      v[4 * k + 2] += x * wx.z + y * wy.z + z * wz.z;
-      v[4 * k + 3] += x * wx.w + y * wy.w + z * wz.w;
-    }
-  }
-  if (kRowLat && wl != nullptr) {
-    // row-latent mode: this row's own code times the latent weight columns (fp32, read through L1: the mode serves a few
-    // hundred thousand rows per call, shared memory has no room for the table, and only two layers come here)
-#pragma unroll
-    for (int d = 0; d < 4; ++d) {
-      if (d < n_rl) {
-        const float s = rl[d] * ascale;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const float4 w = __ldg(reinterpret_cast<const float4*>(wl + size_t(d) * FH) + k);
-          v[4 * k + 0] += s * w.x; v[4 * k + 1] += s * w.y; v[4 * k + 2] += s * w.z; v[4 * k + 3] += s * w.w;
-        }
-      }
-    }
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
   }
   uint32_t gate = 0;
   if (kTrain) {
@@ -119,24 +77,32 @@ __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, bool has_acc_rt, 
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.0f);
   }
-  if (is_last) {
+  if (kLast) {
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float4 w = lds_f32x4(swl + 16 * k);
       ydot += v[4 * k + 0] * w.x + v[4 * k + 1] * w.y + v[4 * k + 2] * w.z + v[4 * k + 3] * w.w;
     }
   }
-  // st0 / st1: the two 16-byte pieces of this row's SW128 line that hold these 16 columns (addresses formed once per thread)
   sts_u32x4(st0, pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
   sts_u32x4(st1, pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
   return gate;
 }
 
+// (hi, lo, hi) of x as bf16 bit patterns: the A-side triple that meets the B-side (w_hi, w_hi, w_lo)
+struct Tri { uint32_t h, l; };
+__device__ __forceinline__ Tri split3(float x) {
+  __nv_bfloat16 hi, lo;
+  split_bf16(x, hi, lo);
+  return Tri{uint32_t(__bfloat16_as_ushort(hi)), uint32_t(__bfloat16_as_ushort(lo))};
+}
+
 }  // namespace
 
-template <bool kTrain, bool kRowLat>
+template <bool kTrain>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(P_THREADS, 1)
 chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmActs,
+                     const __grid_constant__ CUtensorMap tmAux, const __grid_constant__ CUtensorMap tmScene,
                      const __grid_constant__ FwdArgs args) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -165,7 +131,9 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     fence_barrier_init();
   }
   if (warp == P_EPI_WARPS + 1) tmem_alloc_pair<512>(&tmem_slot);
-  if (warp == P_EPI_WARPS && lane == 0) { tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmActs); }
+  if (warp == P_EPI_WARPS && lane == 0) {
+    tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmActs); tma_prefetch_desc(&tmAux); tma_prefetch_desc(&tmScene);
+  }
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();
@@ -174,6 +142,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   const int nh = args.num_hidden;
   const int n_pairs = (args.n_tiles + 1) >> 1;
   const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
+  const bool row_mode = args.row_lat != nullptr;
 
   // Register re-split (each role issues its own setmaxnreg first): the kernel launches with 96 registers per thread (20
   // warps), the four single-lane service warps keep 24, the sixteen epilogue warps get 112.
@@ -187,11 +156,36 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       uint32_t stage = 0, phase = 0;
       const uint64_t pol_w = l2_policy_evict_last();    // 3.4 MB of weights, re-read by every tile
       for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+        // the two tiles of the pair may belong to different scenes: k-core 0 of a per-scene aux block is taken from
+        // rank 0's scene, k-core 1 from rank 1's (fused.cuh)
+        int scene0 = 0, scene1 = 0;
+        if (!row_mode) {
+          const int t0 = 2 * tp, t1 = (2 * tp + 1 < args.n_tiles) ? 2 * tp + 1 : args.n_tiles - 1;
+          scene0 = __ldg(args.tile_scene + t0);
+          scene1 = __ldg(args.tile_scene + t1);
+        }
         for (int l = 0; l < nh; ++l) {
-          if (!args.prog[l].has_mma) continue;
           const int n_halves = args.prog[l].n_halves, k_chunks = args.prog[l].k_chunks;
           const int row_base = args.prog[l].w_row0 + int(rank) * 128;
-          for (int h = 0; h < n_halves; ++h)
+          const int slot = row_mode ? -1 : args.prog[l].bias_slot;
+          const int aux_cores = 2 * args.aux_steps[l];
+          for (int h = 0; h < n_halves; ++h) {
+            // ---- aux stage: bias (+ xyz / latent) columns of these 256 output features
+            mbar_wait_a(empty0 + stage * 8, phase ^ 1);
+            if (elect_one()) {
+              if (leader) mbar_arrive_expect_tx_a(full0 + stage * 8, uint32_t(2 * aux_cores) * AUX_CORE_BYTES);
+              const uint32_t dst = sB_u + stage * P_STAGE_BYTES, bar = full_leader + stage * 8;
+              const int r = h * HALF_N + int(rank) * 128;
+              if (slot >= 0) {
+                tma_load_2d_pair_hint_a(dst, &tmScene, bar, 0, (scene0 * 2 + slot) * FH + r, pol_w);
+                tma_load_2d_pair_hint_a(dst + AUX_CORE_BYTES, &tmScene, bar, 8, (scene1 * 2 + slot) * FH + r, pol_w);
+              } else {
+                for (int c = 0; c < aux_cores; ++c)
+                  tma_load_2d_pair_hint_a(dst + c * AUX_CORE_BYTES, &tmAux, bar, 8 * c, l * FH + r, pol_w);
+              }
+            }
+            __syncwarp();
+            if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
             for (int kc = 0; kc < k_chunks; ++kc) {
               mbar_wait_a(empty0 + stage * 8, phase ^ 1);
               if (elect_one()) {
@@ -201,6 +195,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
               __syncwarp();
               if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
             }
+          }
         }
       }
     }
@@ -214,28 +209,31 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     if (leader) {
       const uint32_t idesc = umma_idesc_bf16(2 * TILE_M, HALF_N, 0, 0);
       const uint64_t desc_hi = umma_desc_hi_sw128(16, 1024);
+      const uint64_t aux_hi = umma_desc_hi_noswz(AUX_CORE_BYTES, 128);      // LBO = next k-core, SBO = next 8 rows
       const uint64_t a_base = desc_hi | uint64_t((smem_u32(sA) >> 4) & 0x3FFF);
       const uint64_t b_base = desc_hi | uint64_t((smem_u32(sB) >> 4) & 0x3FFF);
+      const uint64_t a_aux = aux_hi | uint64_t(((smem_a + P_OFF_AUX) >> 4) & 0x3FFF);
+      const uint64_t b_aux = aux_hi | uint64_t((smem_u32(sB) >> 4) & 0x3FFF);
       const uint32_t full0 = smem_u32(&bar_full[0]), empty0 = smem_u32(&bar_empty[0]);
       const uint32_t tfull0 = smem_u32(&bar_tmem_full[0]), fq0 = smem_u32(&bar_free_q0), flo = smem_u32(&bar_free_lo);
       const uint32_t ready0 = smem_u32(&bar_a_ready[0]);
       uint32_t stage = 0, phase = 0, a_cons = 0;
       for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
         for (int l = 0; l < nh; ++l) {
-          if (!args.prog[l].has_mma) continue;
           const int n_halves = args.prog[l].n_halves, k_chunks = args.prog[l].k_chunks;
+          const int aux_steps = args.aux_steps[l];
           const uint32_t apar = a_cons & 1; ++a_cons;
-          const int kc_lo_last = k_chunks < 4 ? k_chunks - 1 : 3;
+          const int kc_lo_last = k_chunks < 4 ? k_chunks - 1 : 3;      // -1: the aux step is the last reader
           const int kc_q0_last = k_chunks < 2 ? k_chunks - 1 : 1;
           uint32_t waited = 0;     // quarters of the previous layer's output whose a_ready has been consumed
           for (int h = 0; h < n_halves; ++h) {
             const bool last_half = (h == n_halves - 1);
-            for (int kc = 0; kc < k_chunks; ++kc) {
-              // K chunk kc reads quarter kc/2 of the A tile.  Besides, the first MMA of half h overwrites that half's
-              // accumulators, which the previous layer's epilogue reads quarter by quarter: half 0 needs quarters 0,1
-              // drained, half 1 needs quarters 2,3.
-              uint32_t needm = 1u << (kc >> 1);
-              if (kc == 0) needm |= 3u << (2 * h);
+            for (int kc = -1; kc < k_chunks; ++kc) {
+              // kc = -1 is the aux step: it reads the aux A block (written at the start of the tile, before the a_ready
+              // arrivals layer 0 waits for) and OVERWRITES this half's accumulators, which the previous layer's epilogue
+              // reads quarter by quarter: half 0 needs quarters 0,1 drained, half 1 needs quarters 2,3.
+              // K chunk kc >= 0 reads quarter kc/2 of the A tile.
+              uint32_t needm = (kc < 0) ? (3u << (2 * h)) : (1u << (kc >> 1));
               needm &= ~waited;
               while (needm) {
                 const int qd = __ffs(int(needm)) - 1;
@@ -247,12 +245,18 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
               tc_fence_after();
               const uint64_t ad = a_base + uint64_t(kc * (A_CHUNK_BYTES >> 4));
               const uint64_t bd = b_base + uint64_t(stage * (P_STAGE_BYTES >> 4));
+              const uint64_t bx = b_aux + uint64_t(stage * (P_STAGE_BYTES >> 4));
               const uint32_t d = tmem_base + h * HALF_N;
               if (elect_one()) {
-                umma_bf16_ss_pair(d, ad, bd, idesc, kc != 0 ? 1u : 0u);
-                umma_bf16_ss_pair(d, ad + 2, bd + 2, idesc, 1u);
-                umma_bf16_ss_pair(d, ad + 4, bd + 4, idesc, 1u);
-                umma_bf16_ss_pair(d, ad + 6, bd + 6, idesc, 1u);
+                if (kc < 0) {
+                  umma_bf16_ss_pair(d, a_aux, bx, idesc, 0u);
+                  if (aux_steps == 2) umma_bf16_ss_pair(d, a_aux + ((2 * AUX_CORE_BYTES) >> 4), bx + ((2 * AUX_CORE_BYTES) >> 4), idesc, 1u);
+                } else {
+                  umma_bf16_ss_pair(d, ad, bd, idesc, 1u);
+                  umma_bf16_ss_pair(d, ad + 2, bd + 2, idesc, 1u);
+                  umma_bf16_ss_pair(d, ad + 4, bd + 4, idesc, 1u);
+                  umma_bf16_ss_pair(d, ad + 6, bd + 6, idesc, 1u);
+                }
                 umma_commit_pair_a(empty0 + stage * 8, 0b11);
                 if (last_half && kc == kc_q0_last) umma_commit_pair_a(fq0, 0b11);
                 if (last_half && kc == kc_lo_last) umma_commit_pair_a(flo, 0b11);
@@ -336,10 +340,14 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     const uint32_t st_row = smem_a + rt * 128u + uint32_t(j >> 1) * A_CHUNK_BYTES;
     const uint32_t st_ps = (uint32_t(j & 1) << 6) ^ ((rt & 7u) << 4);
     const uint32_t st_a0 = st_row + st_ps, st_a1 = st_row + (st_ps ^ 16u), st_a2 = st_row + (st_ps ^ 32u), st_a3 = st_row + (st_ps ^ 48u);
+    const uint32_t aux_dst = smem_a + P_OFF_AUX + uint32_t(j) * AUX_CORE_BYTES + rt * 16u;   // k-core j of this row
+    const uint32_t swl = smem_a + P_OFF_WLAST;
     uint32_t mma_iter = 0;
     const bool stash = kTrain && args.store_acts != 0;
     uint32_t wpar = 0, wany = 0;        // per quarter: parity of / any hand-overs to the stash warp so far
     const int tiles_alloc = int(args.n_rows_pad / TILE_M);
+    const uint32_t one = 0x3F80u;       // bf16 1.0
+    const uint32_t one0 = leader ? one : 0u, one1 = leader ? 0u : one;
 
     for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
       const int tile = 2 * tp + int(rank);
@@ -347,70 +355,79 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       const int tile_c = tile_ok ? tile : args.n_tiles - 1;
       const bool valid = tile_ok && (int64_t(tile_c) * TILE_M + rt) < args.n_rows &&
                          (args.tile_rows == nullptr || int(rt) < __ldg(args.tile_rows + tile_c));
-      float px = 0.f, py = 0.f, pz = 0.f;
-      if (valid) {
-        const float* pt = args.xyz + (int64_t(tile_c) * TILE_M + rt) * args.xyz_stride;
-        px = __ldg(pt); py = __ldg(pt + 1); pz = __ldg(pt + 2);
-      }
-      const int scene = kRowLat ? 0 : __ldg(args.tile_scene + tile_c);
-      float ydot = 0.0f;
-      float rl[4] = {0.f, 0.f, 0.f, 0.f};
-      if (kRowLat && valid) {
-        const float* pl = args.row_lat + (int64_t(tile_c) * TILE_M + rt) * args.row_lat_stride;
+      // ---- aux A block of this tile: k-core j of row rt (every previous MMA of this CTA pair has completed: the last
+      //      epilogue of the previous tile waited for its tmem_full)
+      {
+        uint32_t w0 = 0, w1 = 0, w2 = 0, w3 = 0;
+        if (j < 2) {
+          float px = 0.f, py = 0.f, pz = 0.f;
+          if (valid) {
+            const float* pt = args.xyz + (int64_t(tile_c) * TILE_M + rt) * args.xyz_stride;
+            px = __ldg(pt); py = __ldg(pt + 1); pz = __ldg(pt + 2);
+          }
+          if (j == 0) {       // cols 0..7: one0, one0, x(h,l,h), y(h,l,h)
+            const Tri x = split3(px), y = split3(py);
+            w0 = one0 | (one0 << 16); w1 = x.h | (x.l << 16); w2 = x.h | (y.h << 16); w3 = y.l | (y.h << 16);
+          } else {            // cols 8..15: z(h,l,h), one1, one1, 0, 0, 0
+            const Tri z = split3(pz);
+            w0 = z.h | (z.l << 16); w1 = z.h | (one1 << 16); w2 = one1; w3 = 0u;
+          }
+        } else if (row_mode) {
+          // cols 16 + 3d ..: (hi, lo, hi) of latent component d < 4 -> 12 bf16 over k-cores 2 and 3
+          uint32_t e[16];
 #pragma unroll
-        for (int d = 0; d < 4; ++d) if (d < args.row_lat_dim) rl[d] = __ldg(pl + d);
+          for (int i = 0; i < 16; ++i) e[i] = 0u;
+          if (valid) {
+            const float* pl = args.row_lat + (int64_t(tile_c) * TILE_M + rt) * args.row_lat_stride;
+#pragma unroll
+            for (int d = 0; d < AUX_MAX_ROW_LAT; ++d)
+              if (d < args.row_lat_dim) {
+                const Tri t = split3(__ldg(pl + d));
+                e[3 * d] = t.h; e[3 * d + 1] = t.l; e[3 * d + 2] = t.h;
+              }
+          }
+          if (j == 2) { w0 = e[0] | (e[1] << 16); w1 = e[2] | (e[3] << 16); w2 = e[4] | (e[5] << 16); w3 = e[6] | (e[7] << 16); }
+          else { w0 = e[8] | (e[9] << 16); w1 = e[10] | (e[11] << 16); w2 = e[12] | (e[13] << 16); w3 = e[14] | (e[15] << 16); }
+        }
+        sts_u32x4(aux_dst, w0, w1, w2, w3);
+        fence_proxy_async_smem();
+        tc_fence_before();
+        __syncwarp();
+        // the "layer -1" hand-over: layer 0's MMAs wait for these like any layer waits for its predecessor's quarters
+        if (lane == 0) {
+#pragma unroll
+          for (int Q = 0; Q < 4; ++Q) mbar_arrive_remote(ready_leader + 8u * uint32_t(Q));
+        }
       }
+      float ydot = 0.0f;
 
       for (int l = 0; l < nh; ++l) {
         const ChainLayer& L = args.prog[l];
         const bool last = (l == nh - 1);
         const bool produce_a = !last;
         const bool drop = kTrain && L.dropout != 0 && args.dropout_on != 0;
-        const bool has_acc = L.has_mma != 0;
-        const float ascale = drop ? args.drop_scale : 1.0f;
-        const uint32_t sb = smem_a + P_OFF_BIAS + uint32_t(l & 1) * FH * 4;
-        // ---- before the accumulators are ready: stage this layer's bias (+ xyz weights), draw the first keep words
-        {
-          const float* src = (L.bias_slot >= 0 && !kRowLat) ? (args.cbias + (size_t(scene) * 2 + L.bias_slot) * FH) : args.bias[l];
-          sts_f32(sb + uint32_t(tid) * 4u, __ldg(src + tid) * ascale);
-          if (L.has_xyz) {
-            const float* wsrc = args.wxyz[l];
-            const uint32_t wx = smem_a + P_OFF_WXYZ + uint32_t(tid) * 4u;
-            sts_f32(wx, __ldg(wsrc + tid) * ascale);
-            sts_f32(wx + FH * 4, __ldg(wsrc + FH + tid) * ascale);
-            sts_f32(wx + 2 * FH * 4, __ldg(wsrc + 2 * FH + tid) * ascale);
-          }
-        }
+        // ---- before the accumulators are ready: draw the first keep words
         const uint64_t grow = args.row0 + uint64_t(int64_t(tile_c) * TILE_M + rt);
         uint32_t kwa = 0xFFFFFFFFu, kwb = 0xFFFFFFFFu;
         if (drop) {
           kwa = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(j), args.drop_thr);
           kwb = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(4 + j), args.drop_thr);
         }
-        epi_bar();
-        const bool has_xyz = L.has_xyz != 0;
-        const uint32_t swx = smem_a + P_OFF_WXYZ, swl = smem_a + P_OFF_WLAST;
-        uint32_t par = 0;
-        if (has_acc) { par = mma_iter & 1; ++mma_iter; }
+        const uint32_t par = mma_iter & 1;
+        ++mma_iter;
         uint32_t* gdst = nullptr;
         if (kTrain && args.bitmask != nullptr && tile_ok)
           gdst = args.bitmask + ((size_t(l) * tiles_alloc + tile) * MASK_WORDS + j) * TILE_M + rt;   // word 4*Q + j at + 4*Q*128
 
         // One 128-column quarter: two 16-column passes straight from TMEM into the A tile.
-        const float* wl_layer = (kRowLat && L.bias_slot >= 0) ? args.wlat + size_t(L.bias_slot) * args.row_lat_dim * FH : nullptr;
-        auto quarter_v = [&](int Q, uint32_t keep, auto PLAIN) {
-          constexpr bool kPlain = decltype(PLAIN)::value;
+        auto quarter_v = [&](int Q, uint32_t keep, auto LAST) {
+          constexpr bool kLast = decltype(LAST)::value;
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
           // the previous layer's stash of this quarter must have been read out of the tile
           if (stash && ((wany >> Q) & 1u)) mbar_wait(&bar_q_stashed[Q], ((wpar >> Q) & 1u) ^ 1u);
           const uint32_t qoff = uint32_t(Q) * 2u * A_CHUNK_BYTES;        // a quarter = two 64-column chunks
-          const uint32_t g0 = epi_pass16<kTrain, kRowLat, kPlain>(tmem_row + c0, has_acc, ascale, sb + c0 * 4, has_xyz, swx + c0 * 4, px,
-                                                                  py, pz, keep, last, swl + c0 * 4, st_a0 + qoff, st_a1 + qoff, ydot,
-                                                                  wl_layer ? wl_layer + c0 : nullptr, args.row_lat_dim, rl);
-          const uint32_t g1 = epi_pass16<kTrain, kRowLat, kPlain>(tmem_row + c0 + 16, has_acc, ascale, sb + (c0 + 16) * 4, has_xyz,
-                                                                  swx + (c0 + 16) * 4, px, py, pz, keep >> 16, last, swl + (c0 + 16) * 4,
-                                                                  st_a2 + qoff, st_a3 + qoff, ydot,
-                                                                  wl_layer ? wl_layer + c0 + 16 : nullptr, args.row_lat_dim, rl);
+          const uint32_t g0 = epi_pass16<kTrain, kLast>(tmem_row + c0, keep, swl + c0 * 4, st_a0 + qoff, st_a1 + qoff, ydot);
+          const uint32_t g1 = epi_pass16<kTrain, kLast>(tmem_row + c0 + 16, keep >> 16, swl + (c0 + 16) * 4, st_a2 + qoff, st_a3 + qoff, ydot);
           if (kTrain && gdst != nullptr) gdst[size_t(Q) * 4 * TILE_M] = g0 | (g1 << 16);
           fence_proxy_async_smem();
           tc_fence_before();
@@ -422,25 +439,24 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           }
         };
         // one run-time dispatch per quarter instead of flag tests in every 16-column pass
-        const bool plain = has_acc && !has_xyz && !last;
         auto quarter = [&](int Q, uint32_t keep) {
-          if (plain) quarter_v(Q, keep, std::true_type{});
+          if (last) quarter_v(Q, keep, std::true_type{});
           else quarter_v(Q, keep, std::false_type{});
         };
 
         // ---- half 0: ready while the tensor cores still compute half 1.  Activation chunks 0,1 may be overwritten once
         //      half 1's MMAs have passed K chunk 1 (free_q0), chunks 2,3 after K chunk 3 (free_lo); the previous layer's
         //      stash (TMA store) must have been read out of the tile.
-        if (has_acc) { mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); mbar_wait(&bar_free_q0, par); }
+        mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); mbar_wait(&bar_free_q0, par);
         quarter(0, kwa);
-        if (has_acc) mbar_wait(&bar_free_lo, par);
+        mbar_wait(&bar_free_lo, par);
         quarter(1, kwb);
         // ---- half 1: after all of this layer's MMAs; the next layer starts on the K chunks that are already there
         if (drop && L.n_halves == 2) {
           kwa = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(8 + j), args.drop_thr);
           kwb = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(12 + j), args.drop_thr);
         }
-        if (has_acc) { mbar_wait(&bar_tmem_full[1], par); tc_fence_after(); }
+        mbar_wait(&bar_tmem_full[1], par); tc_fence_after();
         if (L.n_halves == 2) {
           quarter(2, kwa);
           quarter(3, kwb);
@@ -511,26 +527,25 @@ static int resident_pairs(K kern, int n_sms) {
   return n;
 }
 
-int launch_chain_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, const FwdArgs& args, int n_sms, cudaStream_t stream) {
-  const bool rows = args.row_lat != nullptr;
-  auto kern = rows ? (args.training ? chain_forward_kernel<true, true> : chain_forward_kernel<false, true>)
-                   : (args.training ? chain_forward_kernel<true, false> : chain_forward_kernel<false, false>);
+int launch_chain_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, const CUtensorMap& tmAux, const CUtensorMap& tmScene,
+                         const FwdArgs& args, int n_sms, cudaStream_t stream) {
+  auto kern = args.training ? chain_forward_kernel<true> : chain_forward_kernel<false>;
   DSDF_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
-  static int max_pairs[4] = {0, 0, 0, 0};
-  int& mp = max_pairs[(args.training ? 1 : 0) + (rows ? 2 : 0)];
+  static int max_pairs[2] = {0, 0};
+  int& mp = max_pairs[args.training ? 1 : 0];
   if (mp == 0) mp = resident_pairs(kern, n_sms);
   const int n_pairs = (args.n_tiles + 1) / 2;
   int grid_pairs = mp;
   if (grid_pairs > n_pairs) grid_pairs = n_pairs;
   if (grid_pairs < 1) grid_pairs = 1;
-  kern<<<2 * grid_pairs, P_THREADS, P_SMEM, stream>>>(tmW, tmActs, args);
+  kern<<<2 * grid_pairs, P_THREADS, P_SMEM, stream>>>(tmW, tmActs, tmAux, tmScene, args);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
 int chain_forward_resident_pairs(int n_sms) {
-  cudaFuncSetAttribute(chain_forward_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM);
-  return resident_pairs(chain_forward_kernel<true, false>, n_sms);
+  cudaFuncSetAttribute(chain_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM);
+  return resident_pairs(chain_forward_kernel<true>, n_sms);
 }
 
 }  // namespace dsdf

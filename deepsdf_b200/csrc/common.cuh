@@ -361,6 +361,11 @@ __host__ __device__ constexpr uint64_t umma_desc_hi_sw128(uint32_t lbo_bytes, ui
   return (uint64_t((lbo_bytes >> 4) & 0x3FFF) << 16) | (uint64_t((sbo_bytes >> 4) & 0x3FFF) << 32) | (uint64_t(1) << 46) |
          (uint64_t(2) << 61);
 }
+// SWIZZLE_NONE (layout 0), K-major canonical layout: core matrix = 8 rows x 16 bytes, stored as 128 contiguous bytes;
+// LBO = byte distance between core matrices adjacent in K, SBO = byte distance between 8-row groups adjacent in M / N.
+__host__ __device__ constexpr uint64_t umma_desc_hi_noswz(uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return (uint64_t((lbo_bytes >> 4) & 0x3FFF) << 16) | (uint64_t((sbo_bytes >> 4) & 0x3FFF) << 32) | (uint64_t(1) << 46);
+}
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint64_t hi_template) {
   return hi_template | uint64_t((smem_addr >> 4) & 0x3FFF);
 }
@@ -381,6 +386,14 @@ __device__ __forceinline__ uint32_t sw128_offset(uint32_t row, uint32_t col_in_c
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);   // .x = lo (low 16 bits)
   return *reinterpret_cast<uint32_t*>(&v);
+}
+// x = hi + lo with hi = bf16(x), lo = bf16(x - hi): two bf16 operands that carry ~16 mantissa bits of x between them
+__host__ __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(x);
+  lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+}
+__device__ __forceinline__ uint32_t bf16_pair_bits(__nv_bfloat16 lo16, __nv_bfloat16 hi16) {
+  return uint32_t(__bfloat16_as_ushort(lo16)) | (uint32_t(__bfloat16_as_ushort(hi16)) << 16);
 }
 __device__ __forceinline__ float bf16_lo_to_f32(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi_to_f32(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }

@@ -19,14 +19,33 @@ constexpr int CHAIN_THREADS = (EPI_WARPS + 2) * 32;   // + TMA warp + MMA warp
 constexpr int CHAIN_SMEM = A_BYTES + NUM_STAGES * STAGE_BYTES + 1024;
 constexpr int MASK_WORDS = FH / 32;               // 16 x u32 keep/relu bits per row per hidden layer
 
+// ---- "aux" K columns of the forward chain: bias, xyz columns and (row-latent mode) short latent codes enter every layer
+// as one or two extra K = 16 tensor-core steps instead of per-element CUDA-core work in the epilogue.  The A side is a
+// [128 rows x 32] bf16 block per tile (written once per tile by the epilogue threads), the B side one [512 x 32] bf16 row
+// block per layer (pack) or one [512 x 16] block per (scene, slot) (scene mode: bias + latent part of lin0 / skip layer).
+// Values are split hi + lo (bf16 each) so that the products carry ~16 mantissa bits:
+//   col  0, 1   A = 1, 1 (rank-0 CTA of the pair) / 0, 0 (rank 1)     B = bias_hi, bias_lo
+//   col  2..10  A = (x_hi, x_lo, x_hi), (y..), (z..)                  B = (wx_hi, wx_hi, wx_lo), (wy..), (wz..)
+//   col 11, 12  A = 0, 0 (rank 0) / 1, 1 (rank 1)                     B = bias_hi, bias_lo   (the pair shares ONE B operand:
+//               the two CTAs' tiles may belong to different scenes, so k-core 0 comes from rank 0's scene and k-core 1 from
+//               rank 1's, and each CTA switches on its own copy of the bias with its 'one' columns)
+//   col 16+3d.. A = (z_d hi, lo, hi), d < 4 (row-latent mode)         B = (w hi, hi, lo) of latent column d
+// Both sides use the SWIZZLE_NONE K-major canonical layout: 8-row x 16-byte core matrices, rows of a k-core contiguous
+// (SBO = 128 B), k-cores 2 KB apart (LBO = 2048 B).
+constexpr int AUX_W = 32;
+constexpr int AUX_SCENE_W = 16;
+constexpr int AUX_CORE_BYTES = TILE_M * 16;       // one k-core of 128 rows: 2 KB
+constexpr int AUX_COL_ONE0 = 0, AUX_COL_XYZ = 2, AUX_COL_ONE1 = 11, AUX_COL_LAT = 16;
+constexpr int AUX_MAX_ROW_LAT = 4;
+
 // One hidden layer of a chain (forward: lin{l}; backward: dgrad of lin{l}).
 struct ChainLayer {
-  int32_t has_mma;      // 0: no tensor-core work (forward layer 0 in scene mode)
+  int32_t has_mma;      // backward: 0 = layer 0 (no dgrad product needed).  forward: always 1 (every layer has its aux step)
   int32_t w_row0;       // first row of this layer's block in the packed weight tensor
   int32_t n_halves;     // 1 or 2 accumulator halves (N = 256 each)
-  int32_t k_chunks;     // 64-wide K chunks read from the A tile
-  int32_t bias_slot;    // forward: -1 = layer bias; 0/1 = per-scene bias slot (latent folded in)
-  int32_t has_xyz;      // forward: + xyz . Wxyz (fp32, CUDA cores); backward: emit xyz-weighted column sums
+  int32_t k_chunks;     // 64-wide K chunks read from the A tile (forward layer 0: none, the aux step is all there is)
+  int32_t bias_slot;    // forward: -1 = layer-constant aux block; 0/1 = per-scene aux slot (latent folded into the bias)
+  int32_t has_xyz;      // forward: the aux block carries xyz columns; backward: emit xyz-weighted column sums
   int32_t dropout;      // dropout after this hidden layer (training)
   int32_t out_dim;      // true width (<= 512)
 };
@@ -37,12 +56,10 @@ struct FwdArgs {
   int64_t n_rows;
   int64_t n_rows_pad;                       // rows per layer region in acts / bitmask (multiple of 128)
   ChainLayer prog[DSDF_MAX_LAYERS];
-  const float* bias[DSDF_MAX_LAYERS];       // [512] fp32, zero padded
-  const float* wxyz[DSDF_MAX_LAYERS];       // [3][512] fp32 or null
-  const float* w_last;                      // [512] fp32 effective last-layer weight
+  int32_t aux_steps[DSDF_MAX_LAYERS];       // K = 16 aux steps of layer l: 1, or 2 where row-latent columns are live
+  const float* w_last;                      // [512] fp32 effective last-layer weight (dropout scale of the last hidden layer folded in when training)
   const float* b_last;                      // [1]
-  const int32_t* tile_scene;                // [n_tiles] -> row of cbias
-  const float* cbias;                       // [S][2][512] per-scene biases (latent part of lin0 / skip layer + bias)
+  const int32_t* tile_scene;                // [n_tiles] -> scene row of the per-scene aux table (scene mode)
   const float* xyz;                         // row r at xyz + r*xyz_stride (3 floats)
   int32_t xyz_stride;                       // floats between rows: 3 ([N,3]) or 4 ([N,4] xyz+sdf samples)
   int32_t gt_stride;                        // floats between gt values: 1 or 4
@@ -50,7 +67,6 @@ struct FwdArgs {
   int32_t use_tanh;
   int32_t training;
   uint32_t drop_thr;
-  float drop_scale;
   uint64_t seed;
   uint64_t row0;                            // global row id of local row 0 (dropout stream is keyed by global rows)
   const float* gt;                          // [N] or null
@@ -68,7 +84,6 @@ struct FwdArgs {
   const float* row_lat;                     // row r's code at row_lat + r*row_lat_stride, or null (scene mode)
   int32_t row_lat_stride;
   int32_t row_lat_dim;                      // L
-  const float* wlat;                        // fp32 [2][L][512]: latent columns of lin0 / the latent_in layer, transposed
 };
 
 struct BwdArgs {
@@ -80,7 +95,6 @@ struct BwdArgs {
   const float* w_last;                      // [512]
   const float* dy;                          // [N_pad]
   const uint32_t* bitmask;                  // [num_hidden][N_pad][16]
-  float scale[DSDF_MAX_LAYERS];             // backward factor of hidden layer l where its mask bit is set
   const float* xyz;                         // row r at xyz + r*xyz_stride
   int32_t xyz_stride;
   float* tile_part;                         // [n_tiles][part_stride] per-tile column sums

@@ -67,10 +67,27 @@ int fused_layout(const dsdf_net_desc* d, FusedLayout* lo) {
   size_t off = 0;
   lo->off_wp = off;      off = align_up(off + size_t(rows_f) * FH * 2, 1024);
   lo->off_wpt = off;     off = align_up(off + size_t(rows_b) * FH * 2, 1024);
+  const float sc = dropout_scale(d->dropout_prob);
+  bool any_drop = false;
+  lo->in_scale[0] = 1.0f;
+  for (int l = 1; l <= nh; ++l) {
+    const bool dr = ((d->dropout_mask >> (l - 1)) & 1) && d->dropout_prob > 0.f;
+    lo->in_scale[l] = dr ? sc : 1.0f;
+    any_drop |= dr;
+  }
+  lo->off_wp_tr = lo->off_wp;
+  lo->off_wpt_tr = lo->off_wpt;
+  if (any_drop) {
+    lo->off_wp_tr = off;   off = align_up(off + size_t(rows_f) * FH * 2, 1024);
+    lo->off_wpt_tr = off;  off = align_up(off + size_t(rows_b) * FH * 2, 1024);
+  }
+  lo->off_aux = off;     off = align_up(off + size_t(nh) * FH * AUX_W * 2, 1024);
   lo->off_bias = off;    off = align_up(off + size_t(nh) * FH * 4, 256);
   lo->off_wxyz = off;    off = align_up(off + size_t(2) * 3 * FH * 4, 256);        // slot 0: lin0, slot 1: skip layer
   lo->off_wlatT = off;   off = align_up(off + size_t(2) * L * FH * 4, 256);        // [slot][k][512]
   lo->off_wlast = off;   off = align_up(off + size_t(FH) * 4, 256);
+  lo->off_wlast_tr = lo->off_wlast;
+  if (any_drop) { lo->off_wlast_tr = off; off = align_up(off + size_t(FH) * 4, 256); }
   lo->jac_rows = (LD + 15) / 16 * 16;
   lo->off_wjac = align_up(off, 1024);   off = align_up(lo->off_wjac + size_t(lo->jac_rows) * 2 * FH * 2, 1024);
   for (int l = 0; l < nl; ++l) {
@@ -110,13 +127,29 @@ __global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
     if (a.params.g[l] != nullptr) { invn = 1.0f / sqrtf(tot); scale = a.params.g[l][o] * invn; }
     s_scale = scale;
     reinterpret_cast<float*>(a.pack + a.lo.off_invn[l])[o] = invn;
-    if (l < nh) reinterpret_cast<float*>(a.pack + a.lo.off_bias)[l * FH + o] = a.params.b[l][o];
+    if (l < nh) {
+      const float b = a.params.b[l][o];
+      reinterpret_cast<float*>(a.pack + a.lo.off_bias)[l * FH + o] = b;
+      // aux B row of this output feature: the bias, once for each CTA of a pair (fused.cuh)
+      __nv_bfloat16* ar = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_aux) + (size_t(l) * FH + o) * AUX_W;
+      __nv_bfloat16 hi, lo2;
+      split_bf16(b, hi, lo2);
+      ar[AUX_COL_ONE0] = hi; ar[AUX_COL_ONE0 + 1] = lo2;
+      ar[AUX_COL_ONE1] = hi; ar[AUX_COL_ONE1 + 1] = lo2;
+    }
   }
   __syncthreads();
   const float scale = s_scale;
   float* weff = reinterpret_cast<float*>(a.pack + a.lo.off_weff[l]) + size_t(o) * in;
   __nv_bfloat16* wp = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wp);
   __nv_bfloat16* wpt = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wpt);
+  // training variants (dropout scale of the previous hidden layer folded into the activation columns)
+  const bool two = a.lo.off_wp_tr != a.lo.off_wp;
+  __nv_bfloat16* wp_tr = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wp_tr);
+  __nv_bfloat16* wpt_tr = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wpt_tr);
+  float* wlast_tr = reinterpret_cast<float*>(a.pack + a.lo.off_wlast_tr);
+  const float ins = a.lo.in_scale[l];
+  __nv_bfloat16* aux_row = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_aux) + (size_t(l < nh ? l : 0) * FH + o) * AUX_W;
   float* wxyz = reinterpret_cast<float*>(a.pack + a.lo.off_wxyz);
   float* wlatT = reinterpret_cast<float*>(a.pack + a.lo.off_wlatT);
   float* wlast = reinterpret_cast<float*>(a.pack + a.lo.off_wlast);
@@ -125,21 +158,37 @@ __global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
   for (int k = threadIdx.x; k < in; k += blockDim.x) {
     const float w = vrow[k] * scale;
     weff[k] = w;
-    if (l == nh) { wlast[k] = w; continue; }
+    if (l == nh) { wlast[k] = w; if (two) wlast_tr[k] = w * ins; continue; }
     const int xw = a.lo.xw[l];
     if (k < xw) {
       if (l > 0) {
         wp[size_t(a.lo.fwd_row0[l] + o) * FH + k] = __float2bfloat16_rn(w);
         wpt[size_t(a.lo.bwd_row0[l] + k) * FH + o] = __float2bfloat16_rn(w);
+        if (two) {
+          wp_tr[size_t(a.lo.fwd_row0[l] + o) * FH + k] = __float2bfloat16_rn(w * ins);
+          wpt_tr[size_t(a.lo.bwd_row0[l] + k) * FH + o] = __float2bfloat16_rn(w * ins);
+        }
       }
     } else if (a.lo.lat_col0[l] >= 0 && k < a.lo.lat_col0[l] + L) {
       const int slot = (l == 0) ? 0 : 1;
-      wlatT[(size_t(slot) * L + (k - a.lo.lat_col0[l])) * FH + o] = w;
-      wjac[size_t(k - a.lo.lat_col0[l]) * (2 * FH) + slot * FH + o] = __float2bfloat16_rn(w);
+      const int dlat = k - a.lo.lat_col0[l];
+      wlatT[(size_t(slot) * L + dlat) * FH + o] = w;
+      wjac[size_t(dlat) * (2 * FH) + slot * FH + o] = __float2bfloat16_rn(w);
+      if (L <= AUX_MAX_ROW_LAT) {           // row-latent mode: (w_hi, w_hi, w_lo) meets the A side's (z_hi, z_lo, z_hi)
+        __nv_bfloat16 hi, lo2;
+        split_bf16(w, hi, lo2);
+        __nv_bfloat16* c = aux_row + AUX_COL_LAT + 3 * dlat;
+        c[0] = hi; c[1] = hi; c[2] = lo2;
+      }
     } else if (a.lo.xyz_col0[l] >= 0 && k >= a.lo.xyz_col0[l]) {
       const int slot = (l == 0) ? 0 : 1;
-      wxyz[(size_t(slot) * 3 + (k - a.lo.xyz_col0[l])) * FH + o] = w;
-      wjac[size_t(L + k - a.lo.xyz_col0[l]) * (2 * FH) + slot * FH + o] = __float2bfloat16_rn(w);
+      const int dx = k - a.lo.xyz_col0[l];
+      wxyz[(size_t(slot) * 3 + dx) * FH + o] = w;
+      wjac[size_t(L + dx) * (2 * FH) + slot * FH + o] = __float2bfloat16_rn(w);
+      __nv_bfloat16 hi, lo2;
+      split_bf16(w, hi, lo2);
+      __nv_bfloat16* c = aux_row + AUX_COL_XYZ + 3 * dx;
+      c[0] = hi; c[1] = hi; c[2] = lo2;
     }
   }
 }
@@ -165,29 +214,46 @@ __global__ void latent_renorm_kernel(float* table, const int64_t* scene_ids, int
   }
 }
 
-// cbias[s][slot][o] = bias_l[o] + sum_k Weff_l[o, lat_col0 + k] * z[scene_ids[s]][k]; grid (S, 2), block 512
+// Per-scene aux B rows (fused.cuh): scene_aux[s][slot][o][16] bf16 with
+//   b = bias_l[o] + sum_k Weff_l[o, lat_col0 + k] * z[scene_ids[s]][k]   (fp32, then split hi + lo)
+// at columns 0,1 and 11,12 and the xyz columns of the layer at 2..10.  grid (S, 2), block 512
 __global__ void scene_bias_kernel(const float* __restrict__ table, const int64_t* __restrict__ scene_ids, int L,
-                                  const float* __restrict__ wlatT, const float* __restrict__ bias, int lat_layer,
-                                  float* __restrict__ cbias) {
+                                  const float* __restrict__ wlatT, const float* __restrict__ bias, const float* __restrict__ wxyz,
+                                  int lat_layer, __nv_bfloat16* __restrict__ scene_aux) {
   const int s = blockIdx.x, slot = blockIdx.y, o = threadIdx.x;
   extern __shared__ float z[];
   const float* row = table + size_t(scene_ids[s]) * L;
   for (int k = threadIdx.x; k < L; k += blockDim.x) z[k] = row[k];
   __syncthreads();
-  float acc = 0.f;
+  uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
   if (slot == 0 || lat_layer > 0) {
     const int l = (slot == 0) ? 0 : lat_layer;
-    acc = bias[l * FH + o];
-    const float* w = wlatT + size_t(slot) * L * FH + o;
-    for (int k = 0; k < L; ++k) acc += w[size_t(k) * FH] * z[k];
+    float acc = bias[l * FH + o];
+    const float* wl = wlatT + size_t(slot) * L * FH + o;
+    for (int k = 0; k < L; ++k) acc += wl[size_t(k) * FH] * z[k];
+    __nv_bfloat16 e[AUX_SCENE_W];
+#pragma unroll
+    for (int i = 0; i < AUX_SCENE_W; ++i) e[i] = __float2bfloat16_rn(0.f);
+    __nv_bfloat16 hi, lo2;
+    split_bf16(acc, hi, lo2);
+    e[AUX_COL_ONE0] = hi; e[AUX_COL_ONE0 + 1] = lo2; e[AUX_COL_ONE1] = hi; e[AUX_COL_ONE1 + 1] = lo2;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      split_bf16(wxyz[(size_t(slot) * 3 + d) * FH + o], hi, lo2);
+      e[AUX_COL_XYZ + 3 * d] = hi; e[AUX_COL_XYZ + 3 * d + 1] = hi; e[AUX_COL_XYZ + 3 * d + 2] = lo2;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = bf16_pair_bits(e[2 * i], e[2 * i + 1]);
   }
-  cbias[(size_t(s) * 2 + slot) * FH + o] = acc;
+  uint4* dst = reinterpret_cast<uint4*>(scene_aux + ((size_t(s) * 2 + slot) * FH + o) * AUX_SCENE_W);
+  dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+  dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
 }
 
 static void fill_programs(const dsdf_net_desc* d, const FusedLayout& lo, ChainLayer* fwd, ChainLayer* bwd) {
   for (int l = 0; l < lo.num_hidden; ++l) {
     ChainLayer& F = fwd[l];
-    F.has_mma = (l > 0);
+    F.has_mma = 1;                 // every forward layer has at least its aux step (lin0 in scene mode: nothing else)
     F.w_row0 = lo.fwd_row0[l];
     F.n_halves = lo.fwd_halves[l];
     F.k_chunks = lo.fwd_kchunks[l];
@@ -207,7 +273,8 @@ static void fill_programs(const dsdf_net_desc* d, const FusedLayout& lo, ChainLa
   }
 }
 
-int launch_chain_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, const FwdArgs& args, int n_sms, cudaStream_t stream);
+int launch_chain_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, const CUtensorMap& tmAux, const CUtensorMap& tmScene,
+                         const FwdArgs& args, int n_sms, cudaStream_t stream);
 
 }  // namespace dsdf
 
@@ -239,8 +306,10 @@ extern "C" int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* p
   return 0;
 }
 
+extern "C" size_t dsdf_scene_aux_bytes(int32_t n_scenes) { return size_t(n_scenes > 0 ? n_scenes : 0) * 2 * FH * AUX_SCENE_W * 2; }
+
 extern "C" int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, float* lat_table, const int64_t* scene_ids,
-                                  int32_t n_scenes, float max_norm, float* cbias, void* stream) {
+                                  int32_t n_scenes, float max_norm, void* scene_aux, void* stream) {
   if (int e = require_sm100()) return e;
   FusedLayout lo;
   if (int e = fused_layout(desc, &lo)) return e;
@@ -251,14 +320,17 @@ extern "C" int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, f
     DSDF_CHECK_CUDA(cudaGetLastError());
   }
   const uint8_t* p = static_cast<const uint8_t*>(pack);
-  scene_bias_kernel<<<dim3(n_scenes, 2), FH, L * sizeof(float), st>>>(
-      lat_table, scene_ids, L, reinterpret_cast<const float*>(p + lo.off_wlatT),
-      reinterpret_cast<const float*>(p + lo.off_bias), lo.lat_layer, cbias);
+  if (scene_aux != nullptr) {
+    DSDF_REQUIRE((reinterpret_cast<uintptr_t>(scene_aux) & 15) == 0, "scene_aux must be 16-byte aligned");
+    scene_bias_kernel<<<dim3(n_scenes, 2), FH, L * sizeof(float), st>>>(
+        lat_table, scene_ids, L, reinterpret_cast<const float*>(p + lo.off_wlatT), reinterpret_cast<const float*>(p + lo.off_bias),
+        reinterpret_cast<const float*>(p + lo.off_wxyz), lo.lat_layer, static_cast<__nv_bfloat16*>(scene_aux));
+  }
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
-static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const float* cbias, const int32_t* tile_scene,
+static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const void* cbias, const int32_t* tile_scene,
                               const float* xyz, int32_t xyz_stride, int64_t n_rows, float* sdf_out, const dsdf_train_io* tr,
                               const float* row_lat, int32_t row_lat_stride, void* stream) {
   if (int e = require_sm100()) return e;
@@ -274,16 +346,14 @@ static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const
   a.n_rows = n_rows;
   a.n_tiles = int((n_rows + TILE_M - 1) / TILE_M);
   a.n_rows_pad = int64_t(a.n_tiles) * TILE_M;
-  for (int l = 0; l < lo.num_hidden; ++l) {
-    a.bias[l] = reinterpret_cast<const float*>(p + lo.off_bias) + size_t(l) * FH;
-    a.wxyz[l] = (l == 0) ? reinterpret_cast<const float*>(p + lo.off_wxyz)
-                         : (l == lo.lat_layer ? reinterpret_cast<const float*>(p + lo.off_wxyz) + 3 * FH : nullptr);
-  }
-  a.w_last = reinterpret_cast<const float*>(p + lo.off_wlast);
+  // training with dropout: the packs whose activation columns carry the previous layer's dropout scale
+  const bool tr_variant = tr->training && !tr->dropout_off;
+  for (int l = 0; l < lo.num_hidden; ++l)
+    a.aux_steps[l] = (row_lat != nullptr && (l == 0 || l == lo.lat_layer)) ? 2 : 1;
+  a.w_last = reinterpret_cast<const float*>(p + (tr_variant ? lo.off_wlast_tr : lo.off_wlast));
   a.b_last = tr && tr->b_last ? tr->b_last : nullptr;
   DSDF_REQUIRE(a.b_last != nullptr, "b_last (bias of the last layer) must be given");
   a.tile_scene = tile_scene;
-  a.cbias = cbias;
   a.xyz = xyz;
   DSDF_REQUIRE(xyz_stride >= 3, "xyz_stride must be >= 3");
   a.xyz_stride = xyz_stride;
@@ -291,8 +361,7 @@ static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const
   a.sdf_out = sdf_out;
   a.use_tanh = desc->use_tanh;
   a.training = tr->training;
-  a.drop_thr = dropout_threshold(desc->dropout_prob);
-  a.drop_scale = dropout_scale(desc->dropout_prob);    // 1 / (1 - effective p): E[keep * scale] == 1
+  a.drop_thr = dropout_threshold(desc->dropout_prob);   // survivors' scale 1 / (1 - effective p): folded into the tr packs
   a.seed = tr->seed;
   philox_round_keys(tr->seed, a.philox_rk);
   a.row0 = tr->row0;
@@ -312,7 +381,6 @@ static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const
     a.row_lat = row_lat;
     a.row_lat_stride = row_lat_stride;
     a.row_lat_dim = desc->latent_size;
-    a.wlat = reinterpret_cast<const float*>(p + lo.off_wlatT);
   } else {
     DSDF_REQUIRE(cbias != nullptr && tile_scene != nullptr, "scene mode needs cbias and tile_scene");
   }
@@ -321,15 +389,23 @@ static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const
     if (a.gt) DSDF_REQUIRE(a.dy_out && a.tile_loss, "training with gt needs dy_out and tile_loss");
     if (a.dy_unit) DSDF_REQUIRE(a.dy_out && !a.gt, "dy_unit needs dy_out and no gt");
   }
-  CUtensorMap tmW, tmActs;
-  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wp, FH, lo.fwd_rows, FH * 2, 64, 128)) return e;
+  CUtensorMap tmW, tmActs, tmAux, tmScene;
+  if (int e = make_tmap_bf16_2d(&tmW, p + (tr_variant ? lo.off_wp_tr : lo.off_wp), FH, lo.fwd_rows, FH * 2, 64, 128)) return e;
+  if (int e = make_tmap_bf16_2d_noswz(&tmAux, p + lo.off_aux, AUX_W, uint64_t(lo.num_hidden) * FH, AUX_W * 2, 8, 128)) return e;
+  if (cbias != nullptr) {
+    // per-scene aux rows [n_scenes][2][512][16]; the scene count is the caller's business (tile_scene indexes it)
+    DSDF_REQUIRE((reinterpret_cast<uintptr_t>(cbias) & 15) == 0, "scene_aux must be 16-byte aligned");
+    if (int e = make_tmap_bf16_2d_noswz(&tmScene, cbias, AUX_SCENE_W, uint64_t(1) << 30, AUX_SCENE_W * 2, 8, 128)) return e;
+  } else {
+    tmScene = tmAux;
+  }
   const void* acts_ptr = tr->acts ? tr->acts : static_cast<const void*>(p + lo.off_wp);   // dummy map when unused
   const uint64_t acts_rows = tr->acts ? uint64_t(lo.num_hidden) * a.n_rows_pad : uint64_t(lo.fwd_rows);
   if (int e = make_tmap_bf16_2d(&tmActs, acts_ptr, FH, acts_rows, FH * 2, 64, TILE_M)) return e;
-  return launch_chain_forward(tmW, tmActs, a, sm_count(), static_cast<cudaStream_t>(stream));
+  return launch_chain_forward(tmW, tmActs, tmAux, tmScene, a, sm_count(), static_cast<cudaStream_t>(stream));
 }
 
-extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const float* cbias,
+extern "C" int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const void* cbias,
                                   const int32_t* tile_scene, const float* xyz, int32_t xyz_stride, int64_t n_rows,
                                   float* sdf_out, const dsdf_train_io* tr, void* stream) {
   return fused_forward_impl(desc, pack, cbias, tile_scene, xyz, xyz_stride, n_rows, sdf_out, tr, nullptr, 0, stream);

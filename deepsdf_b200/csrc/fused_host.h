@@ -17,6 +17,12 @@ struct FusedLayout {
   int32_t fwd_rows, bwd_rows;
   size_t off_wp;                         // bf16 [fwd_rows][512]   forward B operand  (rows = out features, K = in)
   size_t off_wpt;                        // bf16 [bwd_rows][512]   dgrad B operand    (rows = in features,  K = out)
+  // training variants: the inverted-dropout scale 1/(1 - p_eff) of hidden layer l-1 multiplied into the hidden-activation
+  // columns of layer l's weights (and into the last layer), so that activations / dY are stored unscaled and neither chain
+  // epilogue multiplies.  Equal to the plain offsets when the network has no dropout.
+  size_t off_wp_tr, off_wpt_tr, off_wlast_tr;
+  size_t off_aux;                        // bf16 [num_hidden][512][AUX_W]  layer-constant aux B blocks (fused.cuh)
+  float in_scale[DSDF_MAX_LAYERS + 1];   // training: factor folded into the activation columns of layer l (l = num_hidden: last layer)
   size_t off_bias;                       // f32  [num_hidden][512]
   size_t off_wxyz;                       // f32  [2][3][512]       xyz columns of lin0 / skip layer
   size_t off_wlatT;                      // f32  [2][L][512]       latent columns of lin0 / skip layer, transposed

@@ -37,8 +37,8 @@ PFN_encodeTiled get_encode_tiled() {
   return fn;
 }
 
-int make_tmap_bf16_2d(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
-                      uint32_t box_inner, uint32_t box_outer) {
+static int make_tmap_bf16_2d_impl(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
+                                  uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle swz) {
   PFN_encodeTiled enc = get_encode_tiled();
   DSDF_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled driver entry point not available");
   DSDF_REQUIRE((reinterpret_cast<uintptr_t>(gptr) & 15) == 0, "TMA global address must be 16-byte aligned");
@@ -49,13 +49,22 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* gptr, uint64_t inner, uint64
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(gptr), gdim, gstride, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     snprintf(g_last_error, sizeof(g_last_error), "cuTensorMapEncodeTiled failed with CUresult %d", int(r));
     return 2;
   }
   return 0;
+}
+
+int make_tmap_bf16_2d(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
+                      uint32_t box_inner, uint32_t box_outer) {
+  return make_tmap_bf16_2d_impl(out, gptr, inner, outer, pitch_bytes, box_inner, box_outer, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int make_tmap_bf16_2d_noswz(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
+                            uint32_t box_inner, uint32_t box_outer) {
+  return make_tmap_bf16_2d_impl(out, gptr, inner, outer, pitch_bytes, box_inner, box_outer, CU_TENSOR_MAP_SWIZZLE_NONE);
 }
 
 }  // namespace dsdf

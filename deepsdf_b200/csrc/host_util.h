@@ -47,5 +47,9 @@ PFN_encodeTiled get_encode_tiled();
 // 2-D bf16 tensor [outer][inner] with row pitch `pitch_bytes`; box {box_inner, box_outer}; SWIZZLE_128B.
 int make_tmap_bf16_2d(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
                       uint32_t box_inner, uint32_t box_outer);
+// Same tensor, no swizzle: a box {8, rows} lands as `rows` contiguous 16-byte pieces = one k-core column of the
+// SWIZZLE_NONE K-major canonical layout (the aux operands of the forward chain).
+int make_tmap_bf16_2d_noswz(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
+                            uint32_t box_inner, uint32_t box_outer);
 
 }  // namespace dsdf

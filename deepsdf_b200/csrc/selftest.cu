@@ -266,3 +266,123 @@ extern "C" int dsdf_selftest_umma_pair(int mode, const void* A, const void* B, f
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Aux-step bring-up: the pair GEMM above plus aux_k (16 or 32) extra K columns whose operands use the SWIZZLE_NONE K-major
+// canonical layout the forward chain's bias / xyz step relies on: A_aux [256][32] written by threads (k-core c of row r at
+// c * 2048 + r * 16), B_aux [256][32] fetched by no-swizzle TMA boxes {8, 128} (one per k-core).  C = A B^T + A_aux B_aux^T.
+// LBO / SBO of the aux descriptors are run-time arguments so that the host can confirm the convention.
+namespace dsdf {
+
+struct Selftest3Args {
+  int K, aux_k;
+  uint32_t lbo, sbo;
+  const __nv_bfloat16* a_aux;   // [256][32]
+  float* C;                     // [256][256]
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(ST_THREADS, 1)
+umma_aux_selftest_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmBaux, Selftest3Args args) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int K = args.K, n_cores = args.aux_k / 8;
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + 65536;
+  uint8_t* sAaux = smem + 131072;               // 4 k-cores x 2 KB
+  uint8_t* sBaux = smem + 131072 + 8192;
+  __shared__ uint64_t bar_full, bar_done, bar_a_ready;
+  __shared__ uint32_t tmem_base_slot;
+  const int warp = threadIdx.x >> 5;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  if (threadIdx.x == 0) {
+    mbar_init(&bar_full, 1);
+    mbar_init(&bar_done, 1);
+    mbar_init(&bar_a_ready, 2 * 4);
+    fence_barrier_init();
+  }
+  if (warp == 5) tmem_alloc_pair<256>(&tmem_base_slot);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t full_leader = mapa_u32(smem_u32(&bar_full), 0);
+  const uint32_t ready_leader = mapa_u32(smem_u32(&bar_a_ready), 0);
+  if (warp < 4) {
+    const int r = threadIdx.x;                       // row of this CTA's A_aux
+    for (int c = 0; c < n_cores; ++c) {
+      const uint4 v = *reinterpret_cast<const uint4*>(args.a_aux + size_t(rank * 128 + r) * 32 + c * 8);
+      *reinterpret_cast<uint4*>(sAaux + c * 2048 + r * 16) = v;
+    }
+    fence_proxy_async_all();
+    tc_fence_before();
+    __syncwarp();
+    if (lane_id() == 0) mbar_arrive_cluster(ready_leader);
+  }
+  if (warp == 4 && elect_one()) {
+    const uint32_t per_cta = 2u * 128u * uint32_t(K) * 2u + uint32_t(n_cores) * 2048u;
+    if (leader) mbar_arrive_expect_tx(&bar_full, 2u * per_cta);
+    for (int kc = 0; kc < K / 64; ++kc) {
+      tma_load_2d_pair(sA + kc * 16384, &tmA, full_leader, kc * 64, int(rank) * 128);
+      tma_load_2d_pair(sB + kc * 16384, &tmB, full_leader, kc * 64, int(rank) * 128);
+    }
+    for (int c = 0; c < n_cores; ++c) tma_load_2d_pair(sBaux + c * 2048, &tmBaux, full_leader, c * 8, int(rank) * 128);
+  }
+  if (warp == 5 && leader) {
+    mbar_wait(&bar_full, 0);
+    mbar_wait_cluster(&bar_a_ready, 0);
+    tc_fence_after();
+    if (elect_one()) {
+      const uint32_t idesc = umma_idesc_bf16(256, 256, 0, 0);
+      const uint64_t hi = umma_desc_hi_sw128(16, 1024);
+      const uint64_t hi_aux = umma_desc_hi_noswz(args.lbo, args.sbo);
+      for (int s2 = 0; s2 < args.aux_k / 16; ++s2)
+        umma_bf16_ss_pair(tmem_base, umma_desc(smem_u32(sAaux) + s2 * 4096, hi_aux), umma_desc(smem_u32(sBaux) + s2 * 4096, hi_aux), idesc,
+                          s2 > 0 ? 1u : 0u);
+      for (int ks = 0; ks < K / 16; ++ks) {
+        const uint32_t off = (ks >> 2) * 16384u + (ks & 3) * 32u;
+        umma_bf16_ss_pair(tmem_base, umma_desc(smem_u32(sA) + off, hi), umma_desc(smem_u32(sB) + off, hi), idesc, 1u);
+      }
+      umma_commit_pair(&bar_done, 0b11);
+    }
+    __syncwarp();
+  }
+  if (warp < 4) {
+    mbar_wait(&bar_done, 0);
+    tc_fence_after();
+    const int row = warp * 32 + lane_id();
+    for (int c0 = 0; c0 < 256; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem_base + (uint32_t(warp * 32) << 16) + c0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) args.C[size_t(rank * 128 + row) * 256 + c0 + j] = __uint_as_float(v[j]);
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 5) tmem_dealloc_pair<256>(tmem_base);
+}
+
+}  // namespace dsdf
+
+extern "C" int dsdf_selftest_umma_aux(const void* A, const void* B, const void* A_aux, const void* B_aux, float* C, int K, int aux_k,
+                                      unsigned lbo, unsigned sbo, void* stream) {
+  using namespace dsdf;
+  if (int e = require_sm100()) return e;
+  DSDF_REQUIRE(K % 64 == 0 && K >= 64 && K <= 256, "selftest: K must be 64..256, multiple of 64");
+  DSDF_REQUIRE(aux_k == 16 || aux_k == 32, "selftest: aux_k must be 16 or 32");
+  CUtensorMap tmA, tmB, tmBaux;
+  if (int e = make_tmap_bf16_2d(&tmA, A, K, 256, uint64_t(K) * 2, 64, 128)) return e;
+  if (int e = make_tmap_bf16_2d(&tmB, B, K, 256, uint64_t(K) * 2, 64, 128)) return e;
+  if (int e = make_tmap_bf16_2d_noswz(&tmBaux, B_aux, 32, 256, 64, 8, 128)) return e;
+  Selftest3Args args{K, aux_k, lbo, sbo, reinterpret_cast<const __nv_bfloat16*>(A_aux), C};
+  const size_t smem = 131072 + 16384 + 1024;
+  DSDF_CHECK_CUDA(cudaFuncSetAttribute(umma_aux_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  umma_aux_selftest_kernel<<<2, ST_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmB, tmBaux, args);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

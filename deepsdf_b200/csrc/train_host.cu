@@ -89,7 +89,7 @@ extern "C" int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, i
   sizes[6] = plan.total_floats * 4;
   sizes[7] = size_t(kLastBlocks) * (FH + 1) * 4;
   sizes[8] = (size_t(n_scenes) * n_slots(lo) * FH + size_t(n_scenes)) * 4;
-  sizes[9] = size_t(n_scenes) * 2 * FH * 4;
+  sizes[9] = size_t(n_scenes) * 2 * FH * AUX_SCENE_W * 2;
   return 0;
 }
 
@@ -118,12 +118,11 @@ extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, con
   a.n_rows = n_rows;
   a.n_tiles = int(n_rows / TILE_M);
   a.n_rows_pad = n_rows;
-  a.w_last = reinterpret_cast<const float*>(p + lo.off_wlast);
+  // training: the pack variant with the dropout scales folded into W^T and w_last (the forward ran on its twin)
+  a.w_last = reinterpret_cast<const float*>(p + (training ? lo.off_wlast_tr : lo.off_wlast));
   a.dy = bufs->dy;
   a.bitmask = bufs->bitmask;
-  const float sc = dropout_scale(desc->dropout_prob);
   for (int l = 0; l < lo.num_hidden; ++l) {
-    a.scale[l] = (training && ((desc->dropout_mask >> l) & 1)) ? sc : 1.0f;
     const bool sums = (sum_mask >> l) & 1u;
     a.colsum_slot[l] = sums ? l : -1;
     a.xyzsum_slot[l] = !sums ? -1 : ((l == 0) ? lo.num_hidden : (l == lo.lat_layer ? lo.num_hidden + 3 : -1));
@@ -137,7 +136,7 @@ extern "C" int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, con
   DSDF_REQUIRE(a.store_dys == 0 || bufs->dys != nullptr, "store_mask needs bufs->dys");
   DSDF_REQUIRE(sum_mask == 0 || bufs->tile_part != nullptr, "sum_mask needs bufs->tile_part");
   CUtensorMap tmW, tmDys;
-  if (int e = make_tmap_bf16_2d(&tmW, p + lo.off_wpt, FH, lo.bwd_rows, FH * 2, 64, 128)) return e;
+  if (int e = make_tmap_bf16_2d(&tmW, p + (training ? lo.off_wpt_tr : lo.off_wpt), FH, lo.bwd_rows, FH * 2, 64, 128)) return e;
   const void* dys_ptr = bufs->dys ? bufs->dys : static_cast<const void*>(p + lo.off_wpt);   // dummy map when nothing is stored
   const uint64_t dys_rows = bufs->dys ? uint64_t(lo.num_hidden) * n_rows : uint64_t(lo.bwd_rows);
   if (int e = make_tmap_bf16_2d(&tmDys, dys_ptr, FH, dys_rows, FH * 2, 64, TILE_M)) return e;
@@ -167,8 +166,8 @@ extern "C" int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs
 extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
                                  const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows,
                                  const float* lat_table, const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total,
-                                 float reg_lambda_eff, float inv_n, const dsdf_param_grads* pgrads, float* lat_grad,
-                                 float* loss_out, void* stream) {
+                                 float reg_lambda_eff, float inv_n, int32_t training, const dsdf_param_grads* pgrads,
+                                 float* lat_grad, float* loss_out, void* stream) {
   if (int e = require_sm100()) return e;
   FinishArgs a;
   memset(&a, 0, sizeof(a));
@@ -197,6 +196,7 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
   a.tile_loss = bufs->tile_loss;
   a.loss_out = loss_out;
   a.xyz_slot0 = a.lo.num_hidden;
+  for (int l = 0; l <= a.lo.num_hidden; ++l) a.in_scale[l] = training ? a.lo.in_scale[l] : 1.0f;
   for (int l = 0; l < desc->num_linear; ++l) {
     DSDF_REQUIRE(pgrads->v[l] && pgrads->b[l], "missing gradient pointers");
     if ((desc->weight_norm_mask >> l) & 1) DSDF_REQUIRE(pgrads->g[l] && params->g[l], "missing g pointers");

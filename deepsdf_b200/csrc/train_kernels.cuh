@@ -31,6 +31,8 @@ struct FinishArgs {
   const float* tile_loss;       // [n_tiles]
   float* loss_out;              // [2]: total loss, data term
   int32_t xyz_slot0;            // first xyz-sum slot of lin0 (3 slots), skip layer follows (+3)
+  float in_scale[DSDF_MAX_LAYERS + 1];   // the activation stash is UNSCALED (relu * keep): the dropout scale of hidden layer
+                                         // l-1 multiplies dW of layer l's activation columns here (1 when dropout is off)
 };
 
 // scene_sums[s][slot][c] = sum over the tiles of scene s (ascending tile order) of tile_part[tile][slot][c].
@@ -96,9 +98,11 @@ __global__ void __launch_bounds__(128) assemble_grads_kernel(const __grid_consta
     float g = 0.f;
     if (l == nh) {
       for (int b = 0; b < a.n_last_blocks; ++b) g += a.last_part[size_t(b) * (FH + 1) + k];
+      g *= a.in_scale[l];
     } else if (k < a.lo.xw[l]) {
       for (int sg = a.plan.layer_seg0[l]; sg < a.plan.layer_seg0[l + 1]; ++sg)
         g += a.wg_part[a.plan.seg[sg].part_offset + size_t(o) * a.plan.seg[sg].n + k];
+      g *= a.in_scale[l];
     } else if (a.lo.lat_col0[l] >= 0 && k < a.lo.lat_col0[l] + L) {
       const int kk = k - a.lo.lat_col0[l];
       for (int s = 0; s < S; ++s)

@@ -45,7 +45,7 @@ def _declare_train(lib) -> None:
     lib.dsdf_fused_wgrad.restype = C.c_int
     lib.dsdf_fused_wgrad.argtypes = [P(L.NetDesc), P(TrainBufs), i64, vp]
     lib.dsdf_fused_finish.restype = C.c_int
-    lib.dsdf_fused_finish.argtypes = [P(L.NetDesc), vp, P(L.Params), P(TrainBufs), vp, i64, vp, vp, i32, i64, f32, f32,
+    lib.dsdf_fused_finish.argtypes = [P(L.NetDesc), vp, P(L.Params), P(TrainBufs), vp, i64, vp, vp, i32, i64, f32, f32, i32,
                                       P(L.ParamGrads), vp, vp, vp]
     lib.dsdf_adam.restype = C.c_int
     lib.dsdf_adam.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp, vp]
@@ -96,12 +96,15 @@ class FusedEngine:
     # ------------------------------------------------------------------ scenes
     def scene_bias(self, lat_table: torch.Tensor, scene_ids: torch.Tensor, max_norm: Optional[float] = None,
                    out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """Per-scene bias vectors [S, 2, 512]; applies nn.Embedding(max_norm) renorm to the listed rows in place."""
+        """Per-scene aux rows [S, 2, 512, 16] bf16 (bias + latent part of lin0 / the latent_in layer and the xyz columns, in the
+        K-column order of the forward's aux tensor-core step); applies nn.Embedding(max_norm) renorm to the listed rows in
+        place."""
         L.require_cuda(lat_table, scene_ids)
         assert lat_table.dtype == torch.float32 and lat_table.is_contiguous() and lat_table.shape[1] == self.spec.latent_size
         assert scene_ids.dtype == torch.int64 and scene_ids.is_contiguous()
         S = scene_ids.numel()
-        cb = out if out is not None else torch.empty(S, 2, 512, device=self.device)
+        cb = out if out is not None else torch.empty(S, 2, 512, 16, dtype=torch.bfloat16, device=self.device)
+        assert cb.dtype == torch.bfloat16 and cb.numel() == S * 2 * 512 * 16 and cb.is_contiguous()
         with torch.cuda.device(self.device):
             L.check(self.lib.dsdf_scene_prepare(C.byref(self.desc), self.pack.data_ptr(), lat_table.data_ptr(),
                                                 scene_ids.data_ptr(), S, float(max_norm or 0.0), cb.data_ptr(), self._st()))
@@ -244,7 +247,7 @@ class FusedEngine:
         S = scene_ids.numel()
         b = self.grad_buffers(N, need_dys=False)
         if "cbias" not in b or b["cbias"].shape[0] != S:
-            b["cbias"] = torch.empty(S, 2, 512, device=self.device)
+            b["cbias"] = torch.empty(S, 2, 512, 16, dtype=torch.bfloat16, device=self.device)
         cb = self.scene_bias(lat_table, scene_ids, None, out=b["cbias"])
         io = L.TrainIO()
         io.b_last = self._b_last().data_ptr()
@@ -321,10 +324,11 @@ class FusedEngine:
         S = scene_ids.numel()
         b = self.train_buffers(N, S)
         tb = self._tb
-        cb = self.scene_bias(lat_table, scene_ids, code_bound, out=b["cbias"].view(torch.float32)[:S * 1024].view(S, 2, 512))
+        cb = self.scene_bias(lat_table, scene_ids, code_bound, out=b["cbias"].view(torch.bfloat16)[:S * 2 * 512 * 16].view(S, 2, 512, 16))
         io = L.TrainIO()
         io.b_last = self._b_last().data_ptr()
-        io.training = int(training)
+        io.training = 1                              # loss / dy / gates / stash are produced either way
+        io.dropout_off = int(not training)           # training=False: the same step with dropout disabled
         io.seed = seed
         io.row0 = row0
         io.gt = gt.data_ptr()
@@ -358,7 +362,7 @@ class FusedEngine:
             e3 = mark()
             L.check(lib.dsdf_fused_finish(C.byref(desc), self.pack.data_ptr(), C.byref(self._P), C.byref(tb), tile_scene.data_ptr(), N,
                                           lat_table.data_ptr(), scene_ids.data_ptr(), S, lat_table.shape[0], float(reg_lambda_eff),
-                                          1.0 / float(n_total), C.byref(PG), lat_grad.data_ptr(), b["loss"].data_ptr(), st))
+                                          1.0 / float(n_total), int(training), C.byref(PG), lat_grad.data_ptr(), b["loss"].data_ptr(), st))
             e4 = mark()
         if ev is not None:
             ev.extend([("fused_forward", e0, e1), ("fused_dgrad", e1, e2), ("wgrad", e2, e3), ("finish", e3, e4)])

@@ -33,7 +33,7 @@ extern "C" {
 #endif
 
 #define DSDF_MAX_LAYERS 16
-#define DSDF_ABI_VERSION 2
+#define DSDF_ABI_VERSION 3
 
 /* Network description == the reference's NetworkSpecs after Decoder.__init__ resolved the layer sizes. */
 typedef struct dsdf_net_desc {
@@ -76,7 +76,9 @@ int dsdf_check_device(void);
 
 /* ------------------------------------------------------------------------------------------------
  * Dropout: Philox4x32-7, counter (row, layer, 2*(col/32)+k), key seed; 8 random bits per decision, bit-sliced over 32
- * columns; keep iff the 8-bit draw >= round(p*256) (csrc/common.cuh).
+ * columns; keep iff the 8-bit draw >= round(p*256) (csrc/common.cuh).  Survivors are scaled by dsdf_dropout_scale(p) =
+ * 1 / (1 - effective p); on the fused path that factor is folded into the NEXT layer's packed weights (training variant of
+ * the pack), so the stashed activations are relu(h) * keep, unscaled.
  * Writes the {0,1} keep mask of one hidden layer as uint8 [n_rows, width] (tests / oracle hand-over). */
 int dsdf_dropout_mask(uint64_t seed, uint32_t layer, uint64_t row0, int64_t n_rows, int32_t width, float p,
                       uint8_t* mask_out, void* stream);
@@ -106,8 +108,8 @@ int dsdf_generic_backward(const dsdf_net_desc* desc, const dsdf_params* params, 
  * latent_in layer collapse into a per-scene bias vector (dsdf_scene_prepare) and are never materialised per row.
  *   pack       caller buffer of dsdf_pack_bytes(), 1024-byte aligned; rebuilt by dsdf_pack_weights whenever the
  *              parameters change (fold g*v/||v||, bf16 pack of W and W^T, fp32 side tables).
- *   cbias      [n_scenes][2][512] fp32, written by dsdf_scene_prepare
- *   tile_scene [ceil(n_rows/128)] int32: row of cbias each tile uses
+ *   scene_aux  [n_scenes][2][512][16] bf16, written by dsdf_scene_prepare
+ *   tile_scene [ceil(n_rows/128)] int32: scene (row of scene_aux) each tile uses; the two tiles of a CTA pair may differ
  */
 typedef struct dsdf_train_io {
   const float* b_last;     /* device pointer to the last layer's bias [1] (always required) */
@@ -133,18 +135,22 @@ typedef struct dsdf_train_io {
 int dsdf_fused_supported(const dsdf_net_desc* desc);
 size_t dsdf_pack_bytes(const dsdf_net_desc* desc);
 int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, void* stream);
-/* nn.Embedding(max_norm) renorm of the listed rows (in place, max_norm <= 0: off) + per-scene bias vectors. */
+/* nn.Embedding(max_norm) renorm of the listed rows (in place, max_norm <= 0: off) + the per-scene aux rows
+ * scene_aux [n_scenes][2][512][16] bf16 (dsdf_scene_aux_bytes, 16-byte aligned; NULL: renorm only): per output feature the
+ * scene's bias of lin0 / the latent_in layer (layer bias + latent columns . z, fp32, split hi + lo) and the layer's xyz
+ * columns, in the K-column order of the forward chain's aux tensor-core step (csrc/fused.cuh). */
+size_t dsdf_scene_aux_bytes(int32_t n_scenes);
 int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, float* lat_table, const int64_t* scene_ids,
-                       int32_t n_scenes, float max_norm, float* cbias, void* stream);
+                       int32_t n_scenes, float max_norm, void* scene_aux, void* stream);
 /* xyz: row r at xyz + r * xyz_stride (3 floats).  xyz_stride = 3 for [N,3] queries, 4 to read the reference's [N,4]
  * (xyz, sdf) sample rows in place (deep_sdf/data.py:102-110, train_deep_sdf.py:483-490). */
-int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const float* cbias, const int32_t* tile_scene,
+int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const void* scene_aux, const int32_t* tile_scene,
                        const float* xyz, int32_t xyz_stride, int64_t n_rows, float* sdf_out, const dsdf_train_io* io,
                        void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Fused training step (scene mode).  All buffers are caller-owned device memory; dsdf_train_buf_sizes() fills
- * sizes[10] (bytes) in the order of the struct members below (+ sizes[9] = cbias).  n_rows must be a multiple of 128
+ * sizes[10] (bytes) in the order of the struct members below (+ sizes[9] = scene_aux).  n_rows must be a multiple of 128
  * and every 128-row tile must belong to one scene (SamplesPerScene % 128 == 0: 16384 and 16000 both are).
  *   forward (training=1, gt given)  -> sdf, dy, tile_loss, bitmask, acts
  *   dsdf_fused_dgrad                -> dys (bf16 dY per hidden layer), tile_part (per-tile column sums)
@@ -180,7 +186,8 @@ int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs* bufs, int
 int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
                       const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows, const float* lat_table,
                       const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total, float reg_lambda_eff,
-                      float inv_n, const dsdf_param_grads* pgrads, float* lat_grad, float* loss_out, void* stream);
+                      float inv_n, int32_t training, const dsdf_param_grads* pgrads, float* lat_grad, float* loss_out,
+                      void* stream);
 /* Row-latent forward: every row brings its own latent code (queries[r] = [latent(L), xyz(3)], row stride ldq floats) - the
  * microstructure consumers of deep_sdf/mesh.py:457-497, whose codes come from a spline over the domain (L = 1 or 2;
  * supported: L <= 4).  Same kernel and same dsdf_train_io as dsdf_fused_forward; the latent columns of lin0 and of the
@@ -272,6 +279,10 @@ int dsdf_debug_wgrad_clusters(void);
 /* CTA-pair (cta_group::2) bring-up: C[256,256] = A[256,K] * B[256,K]^T on one 2-CTA cluster; mode bit2 = A written by
  * threads and handed over with a remote mbarrier arrive (see csrc/selftest.cu). */
 int dsdf_selftest_umma_pair(int mode, const void* A, const void* B, float* C, int K, void* stream);
+/* aux-step bring-up: the pair GEMM plus aux_k (16 | 32) extra K columns in the SWIZZLE_NONE K-major canonical layout
+ * (A_aux, B_aux: [256][32] bf16); lbo / sbo = descriptor offsets under test (the kernels use 2048 / 128). */
+int dsdf_selftest_umma_aux(const void* A, const void* B, const void* A_aux, const void* B_aux, float* C, int K, int aux_k,
+                           unsigned lbo, unsigned sbo, void* stream);
 
 #ifdef __cplusplus
 }

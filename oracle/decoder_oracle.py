@@ -59,6 +59,10 @@ class OracleSpec:
     # by its reciprocal; a test that hands the kernels' masks to the oracle sets this to the same number
     # (kernel_dropout_scale) so that both sides evaluate the same function.
     dropout_scale: Optional[float] = None
+    # Only read by decoder_forward_bf16_operands (the emulation of the CUDA chain's operand rounding): True = the dropout
+    # scale of hidden layer l is multiplied into the activation columns of layer l+1's weights BEFORE their bf16 rounding
+    # and the activations are rounded unscaled - the arithmetic of the round-2 kernels (csrc/fused_host.cu, training pack).
+    fold_scale_into_weights: bool = False
     # derived
     full_dims: List[int] = field(default_factory=list)
     in_dims: List[int] = field(default_factory=list)
@@ -463,6 +467,8 @@ def decoder_forward_bf16_operands(spec: OracleSpec, params, lat_rows: torch.Tens
     nh = spec.num_linear - 1
     a = None
     h = None
+    fold = bool(spec.fold_scale_into_weights)
+    pend = 1.0               # fold: scale of the previous layer's dropout, owed to this layer's activation columns
     for l in range(nh):
         W = effective_weight(spec, params, l)
         b = params[f"lin{l}.bias"]
@@ -470,20 +476,23 @@ def decoder_forward_bf16_operands(spec: OracleSpec, params, lat_rows: torch.Tens
             h = lat_rows @ W[:, :L].t() + b + xyz @ W[:, L:L + D].t()
         elif l in spec.latent_in:
             xw = spec.in_dims[l] - (L + D)
-            h = a[:, :xw] @ _RoundBF16.apply(W[:, :xw]).t() + (lat_rows @ W[:, xw:xw + L].t() + b) + xyz @ W[:, xw + L:].t()
+            h = a[:, :xw] @ _RoundBF16.apply(W[:, :xw] * pend).t() + (lat_rows @ W[:, xw:xw + L].t() + b) + xyz @ W[:, xw + L:].t()
         else:
-            h = a @ _RoundBF16.apply(W).t() + b
+            h = a @ _RoundBF16.apply(W * pend).t() + b
         drop = training and spec.dropout is not None and l in spec.dropout and spec.dropout_prob > 0
+        sc = spec.drop_scale() if drop else 1.0
         if gates is not None:
             h = h * gates[l]
-            if drop:
-                h = h * spec.drop_scale()
         else:
             h = torch.relu(h)
             if drop:
-                h = h * masks[l] * spec.drop_scale()
+                h = h * masks[l]
+        if fold:
+            pend = sc
+        else:
+            h = h * sc
         a = _RoundBF16.apply(h)
-    y = h @ effective_weight(spec, params, nh).t() + params[f"lin{nh}.bias"]
+    y = h @ (effective_weight(spec, params, nh) * (pend if fold else 1.0)).t() + params[f"lin{nh}.bias"]
     if spec.use_tanh:
         y = torch.tanh(y)
     return torch.tanh(y)

@@ -30,6 +30,7 @@ def _setup(name, out_scale=0.025, p_drop=None):
         kw["dropout_prob"] = p_drop
     ospec = O.OracleSpec(**kw)
     ospec.dropout_scale = O.kernel_dropout_scale(ospec.dropout_prob)      # the kernels' masks are handed to the oracle
+    ospec.fold_scale_into_weights = True      # operand-precision emulation: the scale lives in the next layer's bf16 weights
     params = sdf_scale_params(ospec, META[name]["seed"], out_scale=out_scale)
     mod = build_module(kw, params, DEV)
     return kw, ospec, params, mod, FusedEngine(mod)

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     lib = L.lib()
     for n in sorted(names):
         assert hasattr(lib, n), f"{n} declared in include/dsdf.h but not exported by libdsdf_b200.so"
-    assert lib.dsdf_abi_version() == 2
+    assert lib.dsdf_abi_version() == L.ABI_VERSION
 
 
 def test_no_gpu_means_loud_failure():

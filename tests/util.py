@@ -62,6 +62,7 @@ def emulate_fused_forward(ospec, params, table, row_scene, xyz, masks=None):
     z = table[row_scene]
     a = None
     acts = []
+    pend = 1.0      # dropout scale of the previous layer: folded into this layer's activation columns before their bf16 rounding
     for l in range(nh):
         W = O.effective_weight(ospec, params, l)
         b = params[f"lin{l}.bias"]
@@ -69,13 +70,15 @@ def emulate_fused_forward(ospec, params, table, row_scene, xyz, masks=None):
             h = z @ W[:, :L].t() + b + xyz @ W[:, L:L + D].t()
         elif l in ospec.latent_in:
             xw = ospec.in_dims[l] - (L + D)
-            h = a[:, :xw] @ bf16r(W[:, :xw]).t() + (z @ W[:, xw:xw + L].t() + b) + xyz @ W[:, xw + L:].t()
+            h = a[:, :xw] @ bf16r(W[:, :xw] * pend).t() + (z @ W[:, xw:xw + L].t() + b) + xyz @ W[:, xw + L:].t()
         else:
-            h = a @ bf16r(W).t() + b
+            h = a @ bf16r(W * pend).t() + b
         h = torch.relu(h)
+        pend = 1.0
         if masks is not None and l in masks:
-            h = h * masks[l] * ospec.drop_scale()
-        acts.append(h)
+            h = h * masks[l]
+            pend = ospec.drop_scale()
+        acts.append(h * pend)
         a = bf16r(h)
     Wl = O.effective_weight(ospec, params, nh)
     y = acts[-1] @ Wl.t() + params[f"lin{nh}.bias"]
