@@ -24,7 +24,8 @@ def test_pair_gemm_sw128(K):
     lib = L.lib()
     A, B, _, _ = _operands(K, 1)
     C = torch.zeros(256, 256, device=DEV)
-    L.check(lib.dsdf_selftest_umma_pair(0, A.to(DEV).data_ptr(), B.to(DEV).data_ptr(), C.data_ptr(), K, None))
+    Ad, Bd = A.to(DEV), B.to(DEV)
+    L.check(lib.dsdf_selftest_umma_pair(0, Ad.data_ptr(), Bd.data_ptr(), C.data_ptr(), K, None))
     torch.cuda.synchronize()
     ref = A.float() @ B.float().t()
     assert (C.cpu() - ref).abs().max().item() <= 1e-3 * ref.abs().max().item()
