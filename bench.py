@@ -31,6 +31,16 @@ sys.path.insert(0, ROOT)
 
 FLOP_FWD_PER_ROW = 2 * 1835520            # 3.671 MFLOP/row forward (algorithmic)
 FLOP_TRAIN_PER_ROW = 3 * FLOP_FWD_PER_ROW  # fwd + dgrad + wgrad
+# EXECUTED tensor-core MACs per row at L = 256 (SURVEY 8(d) reconciliation rule): the latent columns of lin0 / lin4 are
+# hoisted into per-scene biases, padded shapes are what the MMAs really run.
+#   forward: K-chunk MMAs 512x(512*2 + 256 + 256... ) -> per layer out_pad x in_pad: lin1,2,5,6,7: 512x512; lin3: 256x512;
+#            lin4: 512x256; + one K=16 aux step per layer (bias / per-scene bias / xyz): 512x16 (lin3: 256x16)
+#   dgrad:   dX_l = dY_{l+1} W_{l+1}: layers 7,6,5,2,1: 512x512; lin4 (253 inputs): 256x512; lin3: 512x256
+#   wgrad:   dW_l = dY_l^T X_{l-1}, l = 1..7: 512x512 each except lin4: 512x256 (lin3's 253 outputs ride in a 512-wide block)
+EXEC_MAC_FWD = 5 * 512 * 512 + 256 * 512 + 512 * 256 + 7 * 512 * 16 + 256 * 16
+EXEC_MAC_DGRAD = 5 * 512 * 512 + 256 * 512 + 512 * 256
+EXEC_MAC_WGRAD = 6 * 512 * 512 + 512 * 256
+EXEC_FLOP = {"fused_forward": 2 * EXEC_MAC_FWD, "fused_dgrad": 2 * EXEC_MAC_DGRAD, "wgrad": 2 * EXEC_MAC_WGRAD}
 SCENES_PER_STEP = 64
 SAMPLES_PER_SCENE = 16384
 SCENES_TOTAL = 1024                        # lat_vecs rows per GPU
@@ -54,9 +64,10 @@ SPECS = {
 }
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of each tensor kernel at this workload, from the committed ncu
-# capture (profiles/r01_ncu_v9_summary.txt); algorithmic stash traffic: forward 8.6 GB, dgrad 7.5 GB, wgrad 14.7 GB
-NCU_DRAM_BYTES = {"fused_forward": 8.560e9, "fused_dgrad": 7.678e9, "wgrad": 14.512e9}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of each tensor kernel at this workload: a STATIC copy of the
+# committed ncu capture (profiles/r02_ncu_v2_summary.txt), not re-measured by this script; algorithmic stash traffic:
+# forward 8.6 GB, dgrad 7.5 GB, wgrad 14.7 GB
+NCU_DRAM_BYTES = {"fused_forward": 8.561e9, "fused_dgrad": 7.675e9, "wgrad": 14.514e9}
 
 
 def load_peaks():
@@ -235,13 +246,19 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
 
+    from deepsdf_b200 import _lib as L
+    lib = L.lib()
+    strong = args.scaling == "strong"
+    if SCENES_PER_STEP % world:
+        raise SystemExit("strong scaling splits the 64-scene batch: --gpus must divide 64")
+    S_step = SCENES_PER_STEP // world if strong else SCENES_PER_STEP      # scenes this rank steps per iteration
     trainer = SceneTrainer(SPECS, SCENES_TOTAL, dev, rank=rank, world_size=world, seed=0)
-    N = SCENES_PER_STEP * SAMPLES_PER_SCENE
+    N = S_step * SAMPLES_PER_SCENE
     gen = torch.Generator(device=dev).manual_seed(2 + rank)
     gcpu = torch.Generator().manual_seed(5 + rank)
     dev_batches, host_batches, dev_ids, host_ids = [], [], [], []
     for b in range(N_HOST_BATCHES):
-        ids = torch.randperm(SCENES_TOTAL, generator=gcpu)[:SCENES_PER_STEP].sort().values
+        ids = torch.randperm(SCENES_TOTAL, generator=gcpu)[:S_step].sort().values
         db = make_batch(gen, dev, ids, SCENES_TOTAL)
         dev_batches.append(db)
         host_batches.append(db.cpu().pin_memory())
@@ -275,12 +292,14 @@ def run_gpu(args):
     trainer.engine.kernel_events = []
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    launches0 = int(lib.dsdf_launch_count())
     e0.record()
     for i in range(args.steps):
         loss = trainer.step(dev_batches[i % N_HOST_BATCHES], dev_ids[i % N_HOST_BATCHES], epoch=1, global_rows=global_rows,
                             row0=row0)
     e1.record()
     barrier()
+    gpu_launches = int(lib.dsdf_launch_count()) - launches0        # counted by the library at its launch statements
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     kev = trainer.engine.kernel_events
     trainer.engine.kernel_events = None
@@ -324,10 +343,54 @@ def run_gpu(args):
         "flops_per_launch": FLOP_FWD_PER_ROW * N,
         "kernels_ms": kern,
         "kernels_tflops": {k: FLOP_FWD_PER_ROW * N / (v / 1e3) / 1e12 for k, v in tensor_kernels.items()},
+        # SURVEY 8(d) reconciliation: the tensor-core work the kernels actually issue (latent columns hoisted into per-scene
+        # biases, padded shapes) - what ncu's tensor-pipe % reflects; never to be read as the algorithmic figure above
+        "executed_tflops": EXEC_FLOP[dom] * N / (dom_ms / 1e3) / 1e12,
+        "executed_frac": EXEC_FLOP[dom] * N / (dom_ms / 1e3) / 1e12 / peak,
+        "kernels_executed_tflops": {k: EXEC_FLOP[k] * N / (v / 1e3) / 1e12 for k, v in tensor_kernels.items()},
+        "step_executed_frac_of_peak": sum(EXEC_FLOP.values()) * N / (ms_step / 1e3) / 1e12 / peak,
+        "traffic_source": "static (ncu capture of the same launch, committed under profiles/)",
         "step_tflops_algorithmic": FLOP_TRAIN_PER_ROW * N / (ms_step / 1e3) / 1e12,
         "step_frac_of_peak": FLOP_TRAIN_PER_ROW * N / (ms_step / 1e3) / 1e12 / peak,
         "step_frac_of_datasheet_2250": FLOP_TRAIN_PER_ROW * N / (ms_step / 1e3) / 1e12 / 2250.0,
     }
+
+    # ---- strong scaling ("each rank's batch = S/G scenes"): the FIXED 64 x 16384 batch split over the ranks,
+    #      global-N loss normaliser, one all-reduce of the decoder gradient per step.  Reported as an extra object of the
+    #      default (weak) line so that the driver's 1/2/4/8-GPU SCALE record carries it.  On one GPU the per-rank shards of
+    #      2 / 4 / 8 GPUs are timed alone (no collective): the compute-side bound T1 / (n * T_shard) of the strong efficiency.
+    def timed(scenes, steps, g_rows, r0):
+        n_rows = scenes * SAMPLES_PER_SCENE
+        sl = [(b[:n_rows], i[:scenes].contiguous()) for b, i in zip(dev_batches, dev_ids)]
+        for k in range(3):
+            trainer.step(sl[k % N_HOST_BATCHES][0], sl[k % N_HOST_BATCHES][1], epoch=1, global_rows=g_rows, row0=r0)
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for k in range(steps):
+            trainer.step(sl[k % N_HOST_BATCHES][0], sl[k % N_HOST_BATCHES][1], epoch=1, global_rows=g_rows, row0=r0)
+        b.record()
+        barrier()
+        return max_over_ranks(a.elapsed_time(b)) / steps
+
+    strong_obj = None
+    if not strong:
+        g_rows = SCENES_PER_STEP * SAMPLES_PER_SCENE
+        if world > 1 and SCENES_PER_STEP % world == 0:
+            s_loc = SCENES_PER_STEP // world
+            ms_s = timed(s_loc, args.steps, g_rows, rank * s_loc * SAMPLES_PER_SCENE)
+            strong_obj = {"value": g_rows / (ms_s / 1e3), "unit": "samples/s", "ms_per_step": ms_s, "scenes_per_gpu": s_loc,
+                          "global_rows_per_step": g_rows, "n_gpus": world,
+                          "what": "fixed 64 x 16384 batch split over the GPUs, decoder-gradient all-reduce every step"}
+        elif world == 1:
+            shards = {}
+            for n_g in (2, 4, 8):
+                shards[str(n_g)] = timed(SCENES_PER_STEP // n_g, args.steps, g_rows, 0)
+            strong_obj = {"value": value, "unit": "samples/s", "ms_per_step": ms_step, "scenes_per_gpu": SCENES_PER_STEP, "n_gpus": 1,
+                          "global_rows_per_step": g_rows, "shard_ms_per_step": shards,
+                          "shard_efficiency_bound": {k: ms_step / (int(k) * v) for k, v in shards.items()},
+                          "what": "one GPU: the whole batch (= the headline) and, alone on this GPU, the per-rank shards of 2/4/8 GPUs "
+                                  "(compute only, no collective): T1 / (n * T_shard) bounds the strong-scaling efficiency from above"}
 
     # ---- secondary metrics of BASELINE.json (never part of the timed train region): grid queries/s (config #4) and the
     #      batched latent-only optimisation (config #3), each sharded without a collective
@@ -356,16 +419,19 @@ def run_gpu(args):
     line = {
         "metric": "train SDF samples/s (fwd+bwd+optimizer)", "value": value, "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": "config#2: Decoder 8x512 L=256 latent_in=[4] weight_norm dropout0.2, 64 scenes x 16384 samples per GPU per step",
+        "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "config#2: Decoder 8x512 L=256 latent_in=[4] weight_norm dropout0.2, " +
+                               (f"64 scenes x 16384 samples per step split over {world} GPU(s)" if strong else
+                                "64 scenes x 16384 samples per GPU per step"),
                    "rows_per_gpu_step": N, "global_rows_per_step": global_rows, "parallelism": f"dp{world}",
                    "cache": "per-step working set (bf16 activation + dY stashes, 17 GB) is far larger than the 126 MB L2; 4 rotating input batches"},
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e},
-        "gpu_launches": 14 * args.steps,      # per step: renorm, scene bias, forward, dgrad, wgrad, wgrad_last, 5 finish, 2 Adam, pack
+        "gpu_launches": gpu_launches,         # this repo's kernels inside timed region 1 (dsdf_launch_count; NCCL's are not ours)
         "roofline": roofline,
         "cpu_baseline": cpu,
         "clocks": clk,
+        "strong": strong_obj,
         "grid": extras.get("grid"), "latent_opt": extras.get("latent_opt"), "sampler": extras.get("sampler"), "isosurface": extras.get("isosurface"), "microstructure": extras.get("microstructure"), "extras_error": extras.get("error"),
         "loss_last_step": loss_dev,
         "loss_last_step_e2e": [float(x) for x in last],
@@ -533,6 +599,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the grid / latent-optimisation secondary metrics")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: 64 scenes per GPU per step (default, the driver's SCALE runs); strong: the fixed 64-scene batch split "
+                         "over the GPUs.  The default line always carries a `strong` object as well")
     args = ap.parse_args()
     # stdout carries exactly one JSON line: libraries that print to fd 1 (NCCL's version banner) go to stderr instead
     sys.stdout.flush()

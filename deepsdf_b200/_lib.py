@@ -58,6 +58,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_abi_version": (C.c_int, []),
         "dsdf_last_error": (C.c_char_p, []),
         "dsdf_check_device": (C.c_int, []),
+        "dsdf_launch_count": (i64, []),
         "dsdf_dropout_effective_p": (f32, [f32]),
         "dsdf_dropout_scale": (f32, [f32]),
         "dsdf_dropout_mask": (C.c_int, [u64, u32, u64, i64, i32, f32, vp, vp]),
@@ -65,6 +66,10 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_generic_forward": (C.c_int, [P(NetDesc), P(Params), vp, i64, i32, u64, u64, vp, vp, sz, vp]),
         "dsdf_generic_backward": (C.c_int, [P(NetDesc), P(Params), vp, i64, i32, u64, u64, vp, vp, P(ParamGrads), i32,
                                             vp, sz, vp]),
+        "dsdf_small_supported": (C.c_int, [P(NetDesc)]),
+        "dsdf_small_pack_bytes": (sz, [P(NetDesc)]),
+        "dsdf_small_pack_weights": (C.c_int, [P(NetDesc), P(Params), vp, vp]),
+        "dsdf_small_forward": (C.c_int, [P(NetDesc), vp, vp, i64, vp, i64, vp, vp, i64, vp]),
         "dsdf_fused_supported": (C.c_int, [P(NetDesc)]),
         "dsdf_pack_bytes": (sz, [P(NetDesc)]),
         "dsdf_pack_weights": (C.c_int, [P(NetDesc), P(Params), vp, vp]),

@@ -37,9 +37,9 @@ __device__ __forceinline__ void bwd_bar() { asm volatile("bar.sync 1, %0;" ::"n"
 
 // 16 columns [c0, c0+16) of one row: v = accumulators (or dy * w_last), gated and scaled, packed to bf16 into the A tile
 __device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float dyv, uint32_t swl, uint32_t gate16,
-                                           uint32_t st0, uint32_t st1) {
-  // swl / st0 / st1: SHARED-space byte addresses (explicit ld/st.shared); st0, st1 = the two 16-byte pieces of this row's
-  // SW128 line that receive the 16 columns, formed once per thread
+                                           uint32_t (&pk)[8]) {
+  // swl: SHARED-space byte address (explicit ld.shared).  pk: the 16 gated values as packed bf16 pairs - the caller stores
+  // them (two 16-byte pieces of this row's SW128 line) once the tile quarter may be overwritten
   float v[16];
   if (has_acc) {
     uint32_t r[16];
@@ -57,10 +57,8 @@ __device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float d
   }
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = (gate16 & (1u << i)) ? v[i] : 0.0f;
-  const uint32_t p0 = pack_bf16x2(v[0], v[1]), p1 = pack_bf16x2(v[2], v[3]), p2 = pack_bf16x2(v[4], v[5]), p3 = pack_bf16x2(v[6], v[7]);
-  const uint32_t p4 = pack_bf16x2(v[8], v[9]), p5 = pack_bf16x2(v[10], v[11]), p6 = pack_bf16x2(v[12], v[13]), p7 = pack_bf16x2(v[14], v[15]);
-  sts_u32x4(st0, p0, p1, p2, p3);
-  sts_u32x4(st1, p4, p5, p6, p7);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) pk[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
 }
 
 }  // namespace
@@ -268,27 +266,40 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       }
       bwd_bar();      // s_xyz visible to the column-sum passes of this tile
 
+      // gate words of this row for hidden layer t: word 4*Q + j of [layer][tile][16][128].  Fetched one layer ahead (before
+      // the column-sum pass of the layer above), so that their L2 latency is never on the path to the first quarter.
+      uint32_t gn0 = 0, gn1 = 0, gn2 = 0, gn3 = 0;
+      auto fetch_gates = [&](int t) {
+        gn0 = gn1 = gn2 = gn3 = 0;
+        if (tile_ok && t >= 0) {
+          const uint32_t* mrow = args.bitmask + ((size_t(t) * tiles_alloc + tile_c) * MASK_WORDS + j) * TILE_M + rt;
+          gn0 = __ldg(mrow); gn1 = __ldg(mrow + 4 * TILE_M); gn2 = __ldg(mrow + 8 * TILE_M); gn3 = __ldg(mrow + 12 * TILE_M);
+        }
+      };
+      fetch_gates(nh - 1);
       for (int t = nh - 1; t >= 0; --t) {
         const bool has_acc = (t < nh - 1);
         const int n_halves = has_acc ? args.prog[t + 1].n_halves : 2;
         const bool produce_a = (t > 0);
-        // gate words of this row: word 4*Q + j of [layer][tile][16][128]
-        const uint32_t* mrow = args.bitmask + ((size_t(t) * tiles_alloc + tile_c) * MASK_WORDS + j) * TILE_M + rt;
-        uint32_t gw0 = 0, gw1 = 0, gw2 = 0, gw3 = 0;
-        if (tile_ok) {
-          gw0 = __ldg(mrow); gw1 = __ldg(mrow + 4 * TILE_M);
-          if (n_halves == 2) { gw2 = __ldg(mrow + 8 * TILE_M); gw3 = __ldg(mrow + 12 * TILE_M); }
-        }
+        const uint32_t gw0 = gn0, gw1 = gn1, gw2 = gn2, gw3 = gn3;
         uint32_t par = 0;
         if (has_acc) { par = mma_iter & 1; ++mma_iter; }
 
-        auto quarter = [&](int Q, uint32_t gate) {
+        // `free_bar` (or null): the mbarrier that says the MMAs no longer read the dY chunks of this quarter
+        auto quarter = [&](int Q, uint32_t gate, uint64_t* free_bar) {
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
-          // the previous dY tile's quarter must have been stashed and column-summed before it is overwritten
-          if ((wany >> Q) & 1u) mbar_wait(&bar_q_released[Q], ((wpar >> Q) & 1u) ^ 1u);
           const uint32_t qoff = uint32_t(Q) * 2u * A_CHUNK_BYTES;
-          bwd_pass16(tmem_row + c0, has_acc, dyv, swl_a + c0 * 4, gate, st_a0 + qoff, st_a1 + qoff);
-          bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, swl_a + (c0 + 16) * 4, gate >> 16, st_a2 + qoff, st_a3 + qoff);
+          uint32_t p0[8], p1[8];
+          bwd_pass16(tmem_row + c0, has_acc, dyv, swl_a + c0 * 4, gate, p0);
+          bwd_pass16(tmem_row + c0 + 16, has_acc, dyv, swl_a + (c0 + 16) * 4, gate >> 16, p1);
+          // only the stores wait: for the tensor cores to have read the old chunks, and for the previous dY tile's quarter to
+          // have been stashed and column-summed
+          if (free_bar != nullptr) mbar_wait(free_bar, par);
+          if ((wany >> Q) & 1u) mbar_wait(&bar_q_released[Q], ((wpar >> Q) & 1u) ^ 1u);
+          sts_u32x4(st_a0 + qoff, p0[0], p0[1], p0[2], p0[3]);
+          sts_u32x4(st_a1 + qoff, p0[4], p0[5], p0[6], p0[7]);
+          sts_u32x4(st_a2 + qoff, p1[0], p1[1], p1[2], p1[3]);
+          sts_u32x4(st_a3 + qoff, p1[4], p1[5], p1[6], p1[7]);
           fence_proxy_async_smem();
           tc_fence_before();
           __syncwarp();
@@ -297,20 +308,20 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           wpar ^= 1u << Q; wany |= 1u << Q;
         };
 
-        if (has_acc) { mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); mbar_wait(&bar_free_q0, par); }
-        quarter(0, gw0);
-        if (has_acc) mbar_wait(&bar_free_lo, par);
-        quarter(1, gw1);
+        if (has_acc) { mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); }
+        quarter(0, gw0, has_acc ? &bar_free_q0 : nullptr);
+        quarter(1, gw1, has_acc ? &bar_free_lo : nullptr);
         if (has_acc) { mbar_wait(&bar_tmem_full[1], par); tc_fence_after(); }
         if (n_halves == 2) {
-          quarter(2, gw2);
-          quarter(3, gw3);
+          quarter(2, gw2, nullptr);
+          quarter(3, gw3, nullptr);
         } else {
           tc_fence_before();
           __syncwarp();
           if (produce_a && lane == 0) { mbar_arrive_remote(ready_leader + 16u); mbar_arrive_remote(ready_leader + 24u); }
         }
 
+        fetch_gates(t - 1);      // in flight under the column sums
         // ---- column sums of this warp's 32 columns, once all 16 warps have written that quarter
         {
           // warp w owns columns [32w, 32w+32) = four 16-byte pieces of one 64-column chunk.  lane = (piece, row class r0):
@@ -423,6 +434,7 @@ int launch_chain_dgrad(const CUtensorMap& tmW, const CUtensorMap& tmDys, const B
   const int n_pairs = (args.n_tiles + 1) / 2;
   int grid_pairs = max_pairs < n_pairs ? max_pairs : n_pairs;
   if (grid_pairs < 1) grid_pairs = 1;
+  DSDF_LAUNCHED;
   chain_dgrad_kernel<<<2 * grid_pairs, B_THREADS, B_SMEM, stream>>>(tmW, tmDys, args);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;

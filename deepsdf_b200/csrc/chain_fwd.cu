@@ -52,11 +52,12 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"
 // Post-process 16 consecutive columns [c0, c0+16) of one row and write them (bf16) into the SW128 activation tile.
 //   taddr    TMEM address of the 16 fp32 accumulators (bias, xyz and latent parts already inside: aux step)
 //   keep16   low 16 bits: Philox keep bits of these columns (all ones when the layer has no dropout)
-//   st0/st1  shared addresses of the two 16-byte pieces of the activation tile that receive the 16 columns
+//   pk       the 16 results, packed bf16 pairs; the caller stores them (two 16-byte pieces of the SW128 activation tile)
+//            once the tile chunk may be overwritten - everything up to there overlaps that wait
 //   kLast    last hidden layer: also accumulate this row's share of the 512 -> 1 product into ydot (swl: w_last in smem)
 // Returns the 16 gate bits (relu AND keep).
 template <bool kTrain, bool kLast>
-__device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, uint32_t keep16, uint32_t swl, uint32_t st0, uint32_t st1, float& ydot) {
+__device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, uint32_t keep16, uint32_t swl, uint32_t (&pk)[8], float& ydot) {
   float v[16];
   {
     uint32_t r[16];
@@ -84,8 +85,8 @@ __device__ __forceinline__ uint32_t epi_pass16(uint32_t taddr, uint32_t keep16, 
       ydot += v[4 * k + 0] * w.x + v[4 * k + 1] * w.y + v[4 * k + 2] * w.z + v[4 * k + 3] * w.w;
     }
   }
-  sts_u32x4(st0, pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-  sts_u32x4(st1, pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+#pragma unroll
+  for (int i = 0; i < 8; ++i) pk[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
   return gate;
 }
 
@@ -408,10 +409,16 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         const bool drop = kTrain && L.dropout != 0 && args.dropout_on != 0;
         // ---- before the accumulators are ready: draw the first keep words
         const uint64_t grow = args.row0 + uint64_t(int64_t(tile_c) * TILE_M + rt);
-        uint32_t kwa = 0xFFFFFFFFu, kwb = 0xFFFFFFFFu;
+        // all four keep words of the layer now: the warps idle here anyway (the tensor cores are still on half 0), and later
+        // every cycle between tmem_full[1] and the last a_ready arrive is on the critical path of the next layer
+        uint32_t kwa = 0xFFFFFFFFu, kwb = 0xFFFFFFFFu, kwc = 0xFFFFFFFFu, kwd = 0xFFFFFFFFu;
         if (drop) {
           kwa = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(j), args.drop_thr);
           kwb = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(4 + j), args.drop_thr);
+          if (L.n_halves == 2) {
+            kwc = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(8 + j), args.drop_thr);
+            kwd = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(12 + j), args.drop_thr);
+          }
         }
         const uint32_t par = mma_iter & 1;
         ++mma_iter;
@@ -420,15 +427,23 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           gdst = args.bitmask + ((size_t(l) * tiles_alloc + tile) * MASK_WORDS + j) * TILE_M + rt;   // word 4*Q + j at + 4*Q*128
 
         // One 128-column quarter: two 16-column passes straight from TMEM into the A tile.
-        auto quarter_v = [&](int Q, uint32_t keep, auto LAST) {
+        // `free_bar` (or null): the mbarrier that says the MMAs no longer read the activation chunks of this quarter
+        auto quarter_v = [&](int Q, uint32_t keep, uint64_t* free_bar, auto LAST) {
           constexpr bool kLast = decltype(LAST)::value;
           const uint32_t c0 = uint32_t(Q) * 128u + uint32_t(j) * 32u;
-          // the previous layer's stash of this quarter must have been read out of the tile
-          if (stash && ((wany >> Q) & 1u)) mbar_wait(&bar_q_stashed[Q], ((wpar >> Q) & 1u) ^ 1u);
           const uint32_t qoff = uint32_t(Q) * 2u * A_CHUNK_BYTES;        // a quarter = two 64-column chunks
-          const uint32_t g0 = epi_pass16<kTrain, kLast>(tmem_row + c0, keep, swl + c0 * 4, st_a0 + qoff, st_a1 + qoff, ydot);
-          const uint32_t g1 = epi_pass16<kTrain, kLast>(tmem_row + c0 + 16, keep >> 16, swl + (c0 + 16) * 4, st_a2 + qoff, st_a3 + qoff, ydot);
+          uint32_t p0[8], p1[8];
+          const uint32_t g0 = epi_pass16<kTrain, kLast>(tmem_row + c0, keep, swl + c0 * 4, p0, ydot);
+          const uint32_t g1 = epi_pass16<kTrain, kLast>(tmem_row + c0 + 16, keep >> 16, swl + (c0 + 16) * 4, p1, ydot);
           if (kTrain && gdst != nullptr) gdst[size_t(Q) * 4 * TILE_M] = g0 | (g1 << 16);
+          // only the stores have to wait: for the tensor cores to be done with the old chunks, and for the previous layer's
+          // stash of this quarter to have been read out of the tile
+          if (free_bar != nullptr) mbar_wait(free_bar, par);
+          if (stash && ((wany >> Q) & 1u)) mbar_wait(&bar_q_stashed[Q], ((wpar >> Q) & 1u) ^ 1u);
+          sts_u32x4(st_a0 + qoff, p0[0], p0[1], p0[2], p0[3]);
+          sts_u32x4(st_a1 + qoff, p0[4], p0[5], p0[6], p0[7]);
+          sts_u32x4(st_a2 + qoff, p1[0], p1[1], p1[2], p1[3]);
+          sts_u32x4(st_a3 + qoff, p1[4], p1[5], p1[6], p1[7]);
           fence_proxy_async_smem();
           tc_fence_before();
           __syncwarp();
@@ -439,27 +454,22 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           }
         };
         // one run-time dispatch per quarter instead of flag tests in every 16-column pass
-        auto quarter = [&](int Q, uint32_t keep) {
-          if (last) quarter_v(Q, keep, std::true_type{});
-          else quarter_v(Q, keep, std::false_type{});
+        auto quarter = [&](int Q, uint32_t keep, uint64_t* free_bar) {
+          if (last) quarter_v(Q, keep, free_bar, std::true_type{});
+          else quarter_v(Q, keep, free_bar, std::false_type{});
         };
 
         // ---- half 0: ready while the tensor cores still compute half 1.  Activation chunks 0,1 may be overwritten once
         //      half 1's MMAs have passed K chunk 1 (free_q0), chunks 2,3 after K chunk 3 (free_lo); the previous layer's
         //      stash (TMA store) must have been read out of the tile.
-        mbar_wait(&bar_tmem_full[0], par); tc_fence_after(); mbar_wait(&bar_free_q0, par);
-        quarter(0, kwa);
-        mbar_wait(&bar_free_lo, par);
-        quarter(1, kwb);
+        mbar_wait(&bar_tmem_full[0], par); tc_fence_after();
+        quarter(0, kwa, &bar_free_q0);
+        quarter(1, kwb, &bar_free_lo);
         // ---- half 1: after all of this layer's MMAs; the next layer starts on the K chunks that are already there
-        if (drop && L.n_halves == 2) {
-          kwa = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(8 + j), args.drop_thr);
-          kwb = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(12 + j), args.drop_thr);
-        }
         mbar_wait(&bar_tmem_full[1], par); tc_fence_after();
         if (L.n_halves == 2) {
-          quarter(2, kwa);
-          quarter(3, kwb);
+          quarter(2, kwc, nullptr);
+          quarter(3, kwd, nullptr);
         } else {
           if (kTrain && gdst != nullptr) { gdst[size_t(2) * 4 * TILE_M] = 0u; gdst[size_t(3) * 4 * TILE_M] = 0u; }
           tc_fence_before();
@@ -538,6 +548,7 @@ int launch_chain_forward(const CUtensorMap& tmW, const CUtensorMap& tmActs, cons
   int grid_pairs = mp;
   if (grid_pairs > n_pairs) grid_pairs = n_pairs;
   if (grid_pairs < 1) grid_pairs = 1;
+  DSDF_LAUNCHED;
   kern<<<2 * grid_pairs, P_THREADS, P_SMEM, stream>>>(tmW, tmActs, tmAux, tmScene, args);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -301,6 +301,7 @@ extern "C" int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* p
   DSDF_CHECK_CUDA(cudaMemsetAsync(pack, 0, a.lo.off_weff[0], st));
   int max_out = 0;
   for (int l = 0; l < desc->num_linear; ++l) max_out = desc->out_dim[l] > max_out ? desc->out_dim[l] : max_out;
+  DSDF_LAUNCHED;
   pack_weights_kernel<<<dim3(max_out, desc->num_linear), 128, 0, st>>>(a);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -316,12 +317,14 @@ extern "C" int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, f
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int L = desc->latent_size;
   if (max_norm > 0.f) {
+    DSDF_LAUNCHED;
     latent_renorm_kernel<<<(n_scenes + 3) / 4, 128, 0, st>>>(lat_table, scene_ids, n_scenes, L, max_norm);
     DSDF_CHECK_CUDA(cudaGetLastError());
   }
   const uint8_t* p = static_cast<const uint8_t*>(pack);
   if (scene_aux != nullptr) {
     DSDF_REQUIRE((reinterpret_cast<uintptr_t>(scene_aux) & 15) == 0, "scene_aux must be 16-byte aligned");
+    DSDF_LAUNCHED;
     scene_bias_kernel<<<dim3(n_scenes, 2), FH, L * sizeof(float), st>>>(
         lat_table, scene_ids, L, reinterpret_cast<const float*>(p + lo.off_wlatT), reinterpret_cast<const float*>(p + lo.off_bias),
         reinterpret_cast<const float*>(p + lo.off_wxyz), lo.lat_layer, static_cast<__nv_bfloat16*>(scene_aux));

@@ -3,6 +3,7 @@
 namespace dsdf {
 
 thread_local char g_last_error[512] = {0};
+long long g_kernel_launches = 0;
 
 int require_sm100() {
   int dev = 0;

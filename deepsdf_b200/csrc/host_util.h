@@ -35,6 +35,12 @@ inline int set_error(const char* fmt, const char* a = "", const char* b = "") {
     }                                                                                           \
   } while (0)
 
+// Number of kernels this library has launched since it was loaded (host-side counter next to every launch statement of the
+// fused / small-network / sampler / consumer paths; the generic fp32 path is not counted).  bench.py reports the
+// difference over its timed region as `gpu_launches`.
+extern long long g_kernel_launches;
+#define DSDF_LAUNCHED (++::dsdf::g_kernel_launches)
+
 // sm_100 only: anything else is an error, there is no fallback path.
 int require_sm100();
 int sm_count();

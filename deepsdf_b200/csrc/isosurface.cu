@@ -206,6 +206,7 @@ extern "C" int dsdf_iso_count(const float* volume, int32_t nx, int32_t ny, int32
   IsoArgs a;
   if (int e = fill_args(&a, volume, nx, ny, nz, level)) return e;
   a.origin[0] = a.origin[1] = a.origin[2] = 0.f; a.voxel[0] = a.voxel[1] = a.voxel[2] = 1.f;
+  DSDF_LAUNCHED;
   iso_count_kernel<<<unsigned(dsdf_iso_num_blocks(nx, ny, nz)), ISO_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(a, block_counts);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -218,6 +219,7 @@ extern "C" int dsdf_iso_emit(const float* volume, int32_t nx, int32_t ny, int32_
   if (int e = fill_args(&a, volume, nx, ny, nz, level)) return e;
   DSDF_REQUIRE(origin3 && voxel3 && block_offsets && verts, "iso-surface: null argument");
   for (int k = 0; k < 3; ++k) { a.origin[k] = origin3[k]; a.voxel[k] = voxel3[k]; }
+  DSDF_LAUNCHED;
   iso_emit_kernel<<<unsigned(dsdf_iso_num_blocks(nx, ny, nz)), ISO_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(a, block_offsets, verts);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -278,6 +278,7 @@ extern "C" int dsdf_fused_input_grad(const dsdf_net_desc* desc, const void* pack
   DSDF_CHECK_CUDA(cudaFuncSetAttribute(input_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, J_SMEM));
   int grid = sm_count();
   if (grid > a.n_tiles) grid = a.n_tiles;
+  DSDF_LAUNCHED;
   input_grad_kernel<<<grid, J_THREADS, J_SMEM, static_cast<cudaStream_t>(stream)>>>(tmDys, tmJ, a);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -288,6 +289,7 @@ extern "C" int dsdf_grid_points(int32_t N, int64_t i0, int64_t n, float* xyz_out
   DSDF_REQUIRE(N >= 2 && i0 >= 0 && n >= 0 && i0 + n <= int64_t(N) * N * N, "grid range out of bounds");
   if (n == 0) return 0;
   const float voxel = float(2.0 / double(N - 1));      // Python double, rounded once when it meets the fp32 tensor
+  DSDF_LAUNCHED;
   grid_points_kernel<<<unsigned((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(N, i0, n, voxel, xyz_out);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -318,6 +320,7 @@ extern "C" int dsdf_fused_latent_finish(const dsdf_net_desc* desc, const void* p
   a.inv_n = inv_n;
   a.lat_grad = lat_grad;
   a.shape_loss = shape_loss;
+  DSDF_LAUNCHED;
   latent_finish_kernel<<<n_scenes, FH, 0, static_cast<cudaStream_t>(stream)>>>(a);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;

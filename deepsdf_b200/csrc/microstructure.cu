@@ -93,6 +93,7 @@ extern "C" int dsdf_tile_queries(const float* samples_orig, int32_t ld_s, const 
     t.half[d] = float(p);
     t.gain[d] = float(2.0 / p);
   }
+  DSDF_LAUNCHED;
   tile_queries_kernel<<<unsigned((n_pad + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(samples_orig, ld_s, lat, ld_l,
                                                                                                    latent_size, n, n_pad, t, queries);
   DSDF_CHECK_CUDA(cudaGetLastError());
@@ -112,6 +113,7 @@ extern "C" int dsdf_cap_sdf(float* sdf, float* G, int64_t ldg, int32_t latent_si
     c.dim[i] = dims[i]; c.offset[i] = float(multipliers[i] * (1.0 - measures[i])); c.neg_mult[i] = float(-multipliers[i]);
     c.cap[i] = caps[i];
   }
+  DSDF_LAUNCHED;
   cap_sdf_kernel<<<unsigned((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(sdf, G, ldg, latent_size, samples_orig, ld_s, n, c);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -86,6 +86,7 @@ extern "C" int dsdf_sample_batch(const float* store, const int64_t* meta, const 
   DSDF_REQUIRE(store && meta && scene_ids && batch_out && n_scenes > 0 && samples_per_scene > 0, "dsdf_sample_batch: bad arguments");
   DSDF_REQUIRE((reinterpret_cast<uintptr_t>(store) & 15) == 0 && (reinterpret_cast<uintptr_t>(batch_out) & 15) == 0,
                "sample store and batch must be 16-byte aligned ([rows,4] fp32)");
+  DSDF_LAUNCHED;
   sample_batch_kernel<<<dim3((samples_per_scene + 255) / 256, n_scenes), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float4*>(store), meta, scene_ids, samples_per_scene, seed, reinterpret_cast<float4*>(batch_out));
   DSDF_CHECK_CUDA(cudaGetLastError());

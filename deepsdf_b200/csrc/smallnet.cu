@@ -246,12 +246,11 @@ __global__ void __launch_bounds__(SN_THREADS) small_forward_kernel(const __grid_
       float t1 = tanhf(y), dt = 1.f;
       if (d.use_tanh) { dt = 1.f - t1 * t1; t1 = tanhf(t1); }      // deep_sdf_decoder.py:94-95 then the final self.th (:108-109)
       dt *= 1.f - t1 * t1;
-      if (!d.use_tanh) { /* single tanh: dt = 1 - t1^2 */ }
       if (row0 + tid < a.n_rows) a.sdf_out[row0 + tid] = t1;
       sY[tid] = dt;
     }
-    if (!with_grad) continue;      // (uniform: the next tile's first __syncthreads orders the buffers)
-    __syncthreads();
+    __syncthreads();               // the last-layer reads of `cur` are done before anybody stages the next tile / seeds dY
+    if (!with_grad) continue;
     // ================================================================ backward chain: dY_l = (dY_{l+1} W_{l+1}) (.) gate_l
     // seed: dX[f][r] = dy[r] * w_last[f], gated by the last hidden layer
     {
@@ -325,7 +324,7 @@ __global__ void __launch_bounds__(SN_THREADS) small_forward_kernel(const __grid_
       const int r = i / LD, c = i % LD;                  // c fastest: consecutive addresses within a row of G
       if (row0 + r < a.n_rows) a.G[(row0 + r) * a.ldg + c] = sG[c * SN_ROWS + r];
     }
-    // leave the padded feature rows of both buffers finite-and-zero for the next tile's forward (they were written as 0)
+    __syncthreads();               // sG / sIn are re-staged by the next tile
   }
 }
 
@@ -343,6 +342,7 @@ int launch_small(const SmallArgs& a, cudaStream_t st) {
   if (per_sm < 1) per_sm = 1;
   int grid = sm_count() * per_sm;
   if (grid > a.n_tiles) grid = a.n_tiles;
+  DSDF_LAUNCHED;
   small_forward_kernel<WP><<<grid, SN_THREADS, smem, st>>>(a);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -373,6 +373,7 @@ extern "C" int dsdf_small_pack_weights(const dsdf_net_desc* desc, const dsdf_par
   DSDF_CHECK_CUDA(cudaMemsetAsync(pack, 0, a.lo.total * sizeof(float), st));
   int max_out = 1;
   for (int l = 0; l < desc->num_linear; ++l) max_out = desc->out_dim[l] > max_out ? desc->out_dim[l] : max_out;
+  DSDF_LAUNCHED;
   small_pack_kernel<<<dim3(max_out, desc->num_linear), 128, 0, st>>>(a);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -201,17 +201,22 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
     DSDF_REQUIRE(pgrads->v[l] && pgrads->b[l], "missing gradient pointers");
     if ((desc->weight_norm_mask >> l) & 1) DSDF_REQUIRE(pgrads->g[l] && params->g[l], "missing g pointers");
   }
+  DSDF_LAUNCHED;
   last_reduce_kernel<<<(FH + 1 + 31) / 32, 256, 0, st>>>(bufs->last_part, kLastBlocks);
+  DSDF_LAUNCHED;
   scene_sums_kernel<<<dim3(n_scenes, a.n_slots), FH, 0, st>>>(a.tile_part, tile_scene, a.n_tiles, a.n_slots, a.scene_sums);
   if (lat_grad) {
     DSDF_CHECK_CUDA(cudaMemsetAsync(lat_grad, 0, size_t(n_scenes_total) * desc->latent_size * sizeof(float), st));
+    DSDF_LAUNCHED;
     latent_grad_kernel<<<dim3(n_scenes, (desc->latent_size + 7) / 8), 256, 0, st>>>(a);
   }
   int max_out = 0;
   for (int l = 0; l < desc->num_linear; ++l) max_out = desc->out_dim[l] > max_out ? desc->out_dim[l] : max_out;
+  DSDF_LAUNCHED;
   assemble_grads_kernel<<<dim3(max_out, desc->num_linear), 128, 0, st>>>(a);
   if (loss_out) {
     DSDF_REQUIRE(lat_grad || reg_lambda_eff == 0.f, "loss with regulariser needs the latent-grad pass");
+    DSDF_LAUNCHED;
     loss_kernel<<<1, 256, 0, st>>>(a);
   }
   DSDF_CHECK_CUDA(cudaGetLastError());
@@ -227,6 +232,7 @@ extern "C" int dsdf_adam(float* p, const float* g, float* m, float* v, int64_t n
   DSDF_REQUIRE(step >= 1, "Adam step counter starts at 1");
   const float bc1 = float(1.0 - pow(double(beta1), double(step)));
   const float bc2 = float(1.0 - pow(double(beta2), double(step)));
+  DSDF_LAUNCHED;
   adam_kernel<<<unsigned((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, v, n, lr, beta1, beta2, eps, bc1,
                                                                                        sqrtf(bc2), grad_scale, grad_scale_dev);
   DSDF_CHECK_CUDA(cudaGetLastError());
@@ -237,7 +243,9 @@ extern "C" int dsdf_clip_coef(const float* g, int64_t n, float max_norm, float* 
   if (int e = require_sm100()) return e;
   DSDF_REQUIRE(n > 0 && g && scratch && out, "dsdf_clip_coef: bad arguments");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DSDF_LAUNCHED;
   sumsq_partial_kernel<<<1024, 256, 0, st>>>(g, n, scratch);
+  DSDF_LAUNCHED;
   clip_coef_kernel<<<1, 1024, 0, st>>>(scratch, max_norm, out);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -189,6 +189,7 @@ __global__ void __launch_bounds__(256) wgrad_last_kernel(const __nv_bfloat16* __
 
 int launch_wgrad(const CUtensorMap& tmDys, const CUtensorMap& tmActs, const WgradArgs& args, cudaStream_t stream) {
   DSDF_CHECK_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
+  DSDF_LAUNCHED;
   wgrad_kernel<<<4 * args.plan.n_clusters, WG_THREADS, WG_SMEM, stream>>>(tmDys, tmActs, args);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -211,6 +212,7 @@ int wgrad_max_active_clusters() {
 }
 
 int launch_wgrad_last(const void* x_last, const float* dy, int64_t n_rows_pad, float* part, int n_blocks, cudaStream_t stream) {
+  DSDF_LAUNCHED;
   wgrad_last_kernel<<<n_blocks, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x_last), dy, n_rows_pad, part);
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -84,11 +84,18 @@ class FusedEngine:
     def _st(self) -> int:
         return L.stream_ptr(self.device)
 
-    def repack(self) -> None:
-        """Fold g*v/||v|| and rebuild the bf16 operand packs from the decoder's *current* parameters."""
+    def repack(self, force: bool = True) -> None:
+        """Fold g*v/||v|| and rebuild the bf16 operand packs from the decoder's *current* parameters.  ``force=False``
+        skips the launch when no parameter tensor changed since the last pack (``small.param_key``: torch's version
+        counters + the trainer's ``_param_epoch``)."""
+        from .small import param_key
+        key = param_key(self.decoder)
+        if not force and key == getattr(self, "_pack_key", None):
+            return
         self._P = self.decoder.c_params()
         with torch.cuda.device(self.device):
             L.check(self.lib.dsdf_pack_weights(C.byref(self.desc), C.byref(self._P), self.pack.data_ptr(), self._st()))
+        self._pack_key = key
 
     def _b_last(self) -> torch.Tensor:
         return getattr(self.decoder, "lin" + str(self.spec.num_linear - 1)).bias

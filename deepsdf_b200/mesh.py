@@ -29,8 +29,12 @@ def create_mesh_sdf(decoder, latent_vec: torch.Tensor, N: int = 256, max_batch: 
     L-wide gradient never has to be stored.  Results stay on the device unless ``out_device`` says otherwise."""
     eng = fused_engine_for(decoder)
     if eng is None:
-        raise L.DsdfError("create_mesh_sdf needs a decoder supported by the fused path (8x512 class); use Decoder.forward "
-                          "chunks for the small networks")
+        from .small import small_engine_for
+        sm = small_engine_for(decoder)
+        if sm is None:
+            raise L.DsdfError("create_mesh_sdf needs a decoder of the fused 8x512 class or of the small-network class (hidden width "
+                              "<= 128); evaluate other NetworkSpecs through Decoder.forward chunks")
+        return _create_mesh_sdf_small(sm, latent_vec, N, max_batch, with_grad, slab, out_device, latent_tangents)
     dev = eng.device
     Lz = eng.spec.latent_size
     i0, i1 = slab if slab is not None else (0, N)
@@ -67,6 +71,46 @@ def create_mesh_sdf(decoder, latent_vec: torch.Tensor, N: int = 256, max_batch: 
         else:
             n_pad = (n + TILE - 1) // TILE * TILE
             eng.decode_scenes(cb, ts[:n_pad // TILE], xyz[:n], out=sdf_c)
+        sdf[head:head + n].copy_(sdf_c[:n])
+        head += n
+    shape = (i1 - i0, N, N)
+    if not with_grad:
+        return sdf.view(shape)
+    return sdf.view(shape), dxyz.view(*shape, 3), dlat.view(*shape, -1)
+
+
+def _create_mesh_sdf_small(sm, latent_vec, N, max_batch, with_grad, slab, out_device, latent_tangents):
+    """create_mesh_sdf for the small decoders: the same chunk loop on the fused fp32 small-network kernel (one launch per
+    chunk evaluates SDF and, with derivatives, G = dSDF/d[latent, xyz])."""
+    import ctypes as C
+    dev, Lz, D = sm.device, sm.spec.latent_size, sm.spec.geom_dimension
+    if D != 3:
+        raise L.DsdfError("create_mesh_sdf evaluates a 3-D grid (geom_dimension 3)")
+    i0, i1 = slab if slab is not None else (0, N)
+    first, total = i0 * N * N, (i1 - i0) * N * N
+    out_device = out_device or dev
+    sdf = torch.empty(total, device=out_device)
+    dxyz = dlat = None
+    if with_grad:
+        T = Lz if latent_tangents is None else latent_tangents.shape[1]
+        dxyz = torch.empty(total, 3, device=out_device)
+        dlat = torch.empty(total, T, device=out_device)
+        if latent_tangents is not None:
+            latent_tangents = latent_tangents.to(dev, torch.float32)
+    chunk = max(TILE, min(int(max_batch), total))
+    xyz = torch.empty(chunk, 3, device=dev)
+    sdf_c = torch.empty(chunk, device=dev)
+    G = torch.empty(chunk, Lz + 3, device=dev) if with_grad else None
+    lib = L.lib()
+    head = 0
+    while head < total:
+        n = min(chunk, total - head)
+        with torch.cuda.device(dev):
+            L.check(lib.dsdf_grid_points(N, first + head, n, xyz.data_ptr(), L.stream_ptr(dev)))
+        sm.sdf_and_input_grad(xyz[:n], latent=latent_vec, with_grad=with_grad, sdf=sdf_c, G=G)
+        if with_grad:
+            dxyz[head:head + n].copy_(G[:n, Lz:Lz + 3])
+            dlat[head:head + n].copy_(G[:n, :Lz] if latent_tangents is None else G[:n, :Lz] @ latent_tangents)
         sdf[head:head + n].copy_(sdf_c[:n])
         head += n
     shape = (i1 - i0, N, N)
@@ -142,10 +186,13 @@ def convert_sdf_samples_to_ply(pytorch_3d_sdf_tensor: torch.Tensor, voxel_grid_o
 
 
 def create_mesh(decoder, latent_vec: torch.Tensor, filename: str, N: int = 256, max_batch: int = 1 << 21, offset=None, scale=None) -> int:
-    """deep_sdf/mesh.py:26-85 end to end on the device: grid evaluation (fused forward) + iso-surface + ``<filename>.ply``."""
+    """deep_sdf/mesh.py:26-85 end to end on the device: grid evaluation (fused forward) + iso-surface + ply file.  Like this
+    fork's reference the mesh is written to ``filename`` AS GIVEN (mesh.py:31,76-83: ``ply_filename = filename``; callers such
+    as ``create_mesh_from_latent`` pass a name that already ends in .ply) and the decoder is left in eval mode (mesh.py:29)."""
+    decoder.eval()
     sdf = create_mesh_sdf(decoder, latent_vec, N=N, max_batch=max_batch)
     voxel_size = 2.0 / (N - 1)                                                   # mesh.py:33-35
-    return convert_sdf_samples_to_ply(sdf, [-1.0, -1.0, -1.0], voxel_size, filename + ".ply", offset, scale)
+    return convert_sdf_samples_to_ply(sdf, [-1.0, -1.0, -1.0], voxel_size, filename, offset, scale)
 
 
 # ---------------------------------------------------------------------------------------------- microstructure evaluation
@@ -165,10 +212,15 @@ def evaluate_network_sdf(decoder, lat_vec_red: torch.Tensor, samples_orig: torch
     cap decides the value).  FlexiCubes / splinepy (the mesh from ``sdf`` and the spline basis) are not part of this path.
     Three kernels of libdsdf_b200.so around the fused forward / dgrad / input-gradient launches; nothing leaves the device."""
     import ctypes as C
-    eng = fused_engine_for(decoder)
-    if eng is None or eng.spec.latent_size > 4:
-        raise L.DsdfError("evaluate_network_sdf needs an 8x512-class decoder with CodeLength <= 4")
-    dev, Lz = eng.device, eng.spec.latent_size
+    from .small import small_engine_for
+    sm = small_engine_for(decoder)                       # 4x32 / 4x64 / 6x128: the networks the optimisation runs use
+    eng = None if sm is not None else fused_engine_for(decoder)
+    if sm is None and (eng is None or eng.spec.latent_size > 4):
+        raise L.DsdfError("evaluate_network_sdf needs a small-network-class decoder (hidden width <= 128) or an 8x512-class decoder "
+                          "with CodeLength <= 4")
+    if (sm or eng).spec.geom_dimension != 3:
+        raise L.DsdfError("evaluate_network_sdf works on 3-D samples (geom_dimension 3)")
+    dev, Lz = (sm or eng).device, (sm or eng).spec.latent_size
     so = samples_orig.detach().to(dev, torch.float32).contiguous()
     lat = lat_vec_red.detach().to(dev, torch.float32).contiguous()
     n = so.shape[0]
@@ -180,7 +232,10 @@ def evaluate_network_sdf(decoder, lat_vec_red: torch.Tensor, samples_orig: torch
     t3 = (C.c_float * 3)(*[float(t) for t in tiling])
     with torch.cuda.device(dev):
         L.check(lib.dsdf_tile_queries(so.data_ptr(), so.stride(0), lat.data_ptr(), lat.stride(0), Lz, n, n_pad, t3, queries.data_ptr(), st))
-    sdf, G = eng.sdf_and_input_grad_rows(queries, with_grad=with_grad)
+    if sm is not None:
+        sdf, G = sm.sdf_and_input_grad(queries[:n], with_grad=with_grad)
+    else:
+        sdf, G = eng.sdf_and_input_grad_rows(queries, with_grad=with_grad)
     caps = list((cap_border_dict or {}).items())
     if len(caps) > 6 or any(k not in location_lookup for k, _ in caps):
         raise L.DsdfError("cap_border_dict takes the six keys of location_lookup (x0, x1, y0, y1, z0, z1)")

@@ -160,9 +160,9 @@ def reconstruct_split(experiment_directory: str, checkpoint: str = "latest", dat
             torch.save(lat[j].reshape(1, 1, -1).clone(), code_fn)
             errs[os.path.join(d, c, i)] = float(final[j])
             if resolution > 0:
-                mesh_fn = os.path.join(root, reconstruction_meshes_subdir, d, c, i)
+                mesh_fn = os.path.join(root, reconstruction_meshes_subdir, d, c, i + ".ply")
                 os.makedirs(os.path.dirname(mesh_fn), exist_ok=True)
-                create_mesh(decoder, lat[j], mesh_fn, N=resolution)                      # writes <instance>.ply
+                create_mesh(decoder, lat[j], mesh_fn, N=resolution)                      # writes the name as given (this fork's mesh.py:31)
     return {"epoch": saved_epoch, "loss": errs}
 
 

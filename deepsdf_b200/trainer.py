@@ -203,6 +203,8 @@ class SceneTrainer:
             eng.clip_coef(self.flat_g, self.grad_clip, self._clip_scratch, self._clip_out)
             scale_dev = self._clip_out[1:2]
         eng.adam(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.step_count, lr_dec, scale_dev=scale_dev)
+        # the kernel wrote the parameters behind torch's version counters: cached packs of other engines key on this
+        object.__setattr__(self.decoder, "_param_epoch", getattr(self.decoder, "_param_epoch", 0) + 1)
         eng.repack()
         return loss
 

@@ -4,8 +4,9 @@
 broadcast over ``queries`` [n, 3]; with ``latent_vector=None`` the queries already carry their latent columns
 ([n, L+3]).  For the 8x512-class decoders and a broadcast latent the call runs on the fused tcgen05 forward (the latent
 collapses into one per-scene bias vector, nothing of size [n, L+3] is materialised); per-row codes of length <= 4 (the
-microstructure consumers) run on the same kernel in row-latent mode; everything else goes through the module's generic
-CUDA path.  No CPU path.
+microstructure consumers) run on the same kernel in row-latent mode; the small decoders (hidden width <= 128: 4x32, 4x64,
+6x128) run on the fused fp32 small-network kernel in both forms; everything else (and every differentiable call) goes
+through the module's generic CUDA path.  No CPU path.
 """
 from __future__ import annotations
 
@@ -30,12 +31,21 @@ def fused_engine_for(decoder):
         eng = FusedEngine(dec)
         object.__setattr__(dec, "_fused_engine", eng)
     else:
-        eng.repack()
+        eng.repack(force=False)          # keyed on the parameters' version counters: no launch when nothing changed
     return eng
 
 
 def decode_sdf(decoder, latent_vector, queries):
     num_samples = queries.shape[0]
+    from .small import small_engine_for
+    no_grad = not torch.is_grad_enabled() or not (queries.requires_grad or (latent_vector is not None and latent_vector.requires_grad))
+    if no_grad and not decoder.training and num_samples > 0 and queries.is_cuda:
+        # the small decoders of the optimisation / analysis consumers: one fused fp32 kernel (csrc/smallnet.cu)
+        sm = small_engine_for(decoder)
+        if sm is not None:
+            q = queries.detach().to(sm.device, torch.float32)
+            q = q if q.stride(1) == 1 else q.contiguous()
+            return sm.sdf_and_input_grad(q, latent=latent_vector, with_grad=False)[0].unsqueeze(1)
     if latent_vector is None:
         # rows carry their own codes (mesh.py:490-497): short codes run on the fused forward in row-latent mode
         dec = decoder.module if isinstance(decoder, torch.nn.DataParallel) else decoder

@@ -73,6 +73,8 @@ int dsdf_abi_version(void);
 const char* dsdf_last_error(void);
 /* 0 if the current CUDA device is sm_100; error otherwise (used by the Python side to fail loudly). */
 int dsdf_check_device(void);
+/* kernels launched by this library since it was loaded (fused, small-network, sampler and consumer paths) */
+int64_t dsdf_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------
  * Dropout: Philox4x32-7, counter (row, layer, 2*(col/32)+k), key seed; 8 random bits per decision, bit-sliced over 32
@@ -100,6 +102,23 @@ int dsdf_generic_backward(const dsdf_net_desc* desc, const dsdf_params* params, 
                           int32_t training, uint64_t seed, uint64_t row0, const float* grad_out, float* grad_input,
                           const dsdf_param_grads* pgrads, int32_t accumulate, void* workspace, size_t workspace_bytes,
                           void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Small-network path (csrc/smallnet.cu): hidden widths <= 128, weight-norm or plain layers, any latent_in set, CodeLength +
+ * geom_dimension <= 16, no LayerNorm / xyz_in_all / latent_dropout - the 4x32 / 4x64 / 6x128 decoders of the reference's
+ * optimisation runs (optimization_runs/config.json:8).  ONE kernel, eval mode: the 128-row tile stays in shared memory
+ * across all layers (fp32 FFMA), and with G != NULL the same kernel walks the chain back and writes
+ * G[r] = dSDF/d[latent, xyz] of row r - what the L x n_cpt jvp loop of deep_sdf/mesh.py:405-422 re-derives per tangent.
+ *   pack     caller buffer of dsdf_small_pack_bytes(), 16-byte aligned, rebuilt by dsdf_small_pack_weights when the
+ *            parameters change (fold g*v/||v||, padded W and W^T per layer)
+ *   queries  row r at queries + r*ldq: [latent(L), xyz(D)]; with `latent` != NULL the rows hold xyz only and the one code
+ *            latent[L] is broadcast (decode_sdf with a latent_vector, deep_sdf/utils.py:57-61; create_mesh)
+ *   G        [n_rows][ldg] fp32 or NULL, ldg >= L + D */
+int dsdf_small_supported(const dsdf_net_desc* desc);
+size_t dsdf_small_pack_bytes(const dsdf_net_desc* desc);
+int dsdf_small_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, void* stream);
+int dsdf_small_forward(const dsdf_net_desc* desc, const void* pack, const float* queries, int64_t ldq, const float* latent,
+                       int64_t n_rows, float* sdf_out, float* G, int64_t ldg, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Fused tcgen05 path (hidden width 512, weight-norm or plain layers, one latent_in layer, geom_dim 3).
