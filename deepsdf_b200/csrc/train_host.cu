@@ -86,7 +86,11 @@ extern "C" int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, i
   sizes[3] = size_t(n_pad) * 4;
   sizes[4] = size_t(n_tiles) * 4;
   sizes[5] = size_t(n_tiles) * n_slots(lo) * FH * 4;
-  sizes[6] = plan.total_floats * 4;
+  // split-K partials: one [4 x 128][n <= 512] block per segment, at most one segment per cluster plus one per layer boundary.
+  // The bound (not the plan's own total) is reported so that the size is monotonic in n_rows: a workspace allocated for a
+  // larger batch also serves every smaller one (the chunks of --batch_split).
+  const size_t wg_bound = size_t(WG_CLUSTERS + lo.num_hidden) * 4 * 128 * FH;
+  sizes[6] = (size_t(plan.total_floats) > wg_bound ? size_t(plan.total_floats) : wg_bound) * 4;
   sizes[7] = size_t(kLastBlocks) * (FH + 1) * 4;
   sizes[8] = (size_t(n_scenes) * n_slots(lo) * FH + size_t(n_scenes)) * 4;
   sizes[9] = size_t(n_scenes) * 2 * FH * AUX_SCENE_W * 2;
@@ -166,8 +170,8 @@ extern "C" int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs
 extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
                                  const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows,
                                  const float* lat_table, const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total,
-                                 float reg_lambda_eff, float inv_n, int32_t training, const dsdf_param_grads* pgrads,
-                                 float* lat_grad, float* loss_out, void* stream) {
+                                 float reg_lambda_eff, float inv_n, int32_t training, int32_t accumulate,
+                                 const dsdf_param_grads* pgrads, float* lat_grad, float* loss_out, void* stream) {
   if (int e = require_sm100()) return e;
   FinishArgs a;
   memset(&a, 0, sizeof(a));
@@ -196,6 +200,7 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
   a.tile_loss = bufs->tile_loss;
   a.loss_out = loss_out;
   a.xyz_slot0 = a.lo.num_hidden;
+  a.accumulate = accumulate;
   for (int l = 0; l <= a.lo.num_hidden; ++l) a.in_scale[l] = training ? a.lo.in_scale[l] : 1.0f;
   for (int l = 0; l < desc->num_linear; ++l) {
     DSDF_REQUIRE(pgrads->v[l] && pgrads->b[l], "missing gradient pointers");
@@ -206,7 +211,7 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
   DSDF_LAUNCHED;
   scene_sums_kernel<<<dim3(n_scenes, a.n_slots), FH, 0, st>>>(a.tile_part, tile_scene, a.n_tiles, a.n_slots, a.scene_sums);
   if (lat_grad) {
-    DSDF_CHECK_CUDA(cudaMemsetAsync(lat_grad, 0, size_t(n_scenes_total) * desc->latent_size * sizeof(float), st));
+    if (!accumulate) DSDF_CHECK_CUDA(cudaMemsetAsync(lat_grad, 0, size_t(n_scenes_total) * desc->latent_size * sizeof(float), st));
     DSDF_LAUNCHED;
     latent_grad_kernel<<<dim3(n_scenes, (desc->latent_size + 7) / 8), 256, 0, st>>>(a);
   }

@@ -31,6 +31,8 @@ struct FinishArgs {
   const float* tile_loss;       // [n_tiles]
   float* loss_out;              // [2]: total loss, data term
   int32_t xyz_slot0;            // first xyz-sum slot of lin0 (3 slots), skip layer follows (+3)
+  int32_t accumulate;           // != 0: add to the parameter / latent gradients and to the loss (batch_split chunks,
+                                // train_deep_sdf.py:495-535) instead of overwriting them
   float in_scale[DSDF_MAX_LAYERS + 1];   // the activation stash is UNSCALED (relu * keep): the dropout scale of hidden layer
                                          // l-1 multiplies dW of layer l's activation columns here (1 when dropout is off)
 };
@@ -123,19 +125,19 @@ __global__ void __launch_bounds__(128) assemble_grads_kernel(const __grid_consta
   if (threadIdx.x == 0) {
     const float dg = ((red[0] + red[1]) + (red[2] + red[3])) * invn;
     s_dg = dg;
-    if (wn) a.grads.g[l][o] = dg;
+    if (wn) a.grads.g[l][o] = (a.accumulate ? a.grads.g[l][o] : 0.f) + dg;
     float db = 0.f;
     if (l == nh) { for (int b = 0; b < a.n_last_blocks; ++b) db += a.last_part[size_t(b) * (FH + 1) + FH]; }
     else { for (int s = 0; s < S; ++s) db += a.scene_sums[(size_t(s) * a.n_slots + l) * FH + o]; }
-    a.grads.b[l][o] = db;
+    a.grads.b[l][o] = (a.accumulate ? a.grads.b[l][o] : 0.f) + db;
   }
   __syncthreads();
   float* dv = a.grads.v[l] + size_t(o) * in;
   if (wn) {
     const float gi = a.params.g[l][o] * invn, dg = s_dg;
-    for (int k = threadIdx.x; k < in; k += blockDim.x) dv[k] = gi * (s_dw[k] - v[k] * invn * dg);
+    for (int k = threadIdx.x; k < in; k += blockDim.x) dv[k] = (a.accumulate ? dv[k] : 0.f) + gi * (s_dw[k] - v[k] * invn * dg);
   } else {
-    for (int k = threadIdx.x; k < in; k += blockDim.x) dv[k] = s_dw[k];
+    for (int k = threadIdx.x; k < in; k += blockDim.x) dv[k] = (a.accumulate ? dv[k] : 0.f) + s_dw[k];
   }
 }
 
@@ -179,7 +181,8 @@ __global__ void __launch_bounds__(256) latent_grad_kernel(const __grid_constant_
   for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
   if (lane == 0) {
     if (a.reg_scale != 0.f && s_norm > 0.f) acc += a.reg_scale * float(rows) * z[k] / s_norm;
-    a.lat_grad[size_t(a.scene_ids[s]) * L + k] = acc;
+    float* dst = a.lat_grad + size_t(a.scene_ids[s]) * L + k;
+    *dst = (a.accumulate ? *dst : 0.f) + acc;
   }
 }
 
@@ -201,8 +204,8 @@ __global__ void __launch_bounds__(256) loss_kernel(const __grid_constant__ Finis
       for (int s = 0; s < a.n_scenes; ++s) reg += a.scene_reg[s];
       reg *= a.reg_scale;
     }
-    a.loss_out[0] = data + reg;
-    a.loss_out[1] = data;
+    a.loss_out[0] = (a.accumulate ? a.loss_out[0] : 0.f) + data + reg;
+    a.loss_out[1] = (a.accumulate ? a.loss_out[1] : 0.f) + data;
   }
 }
 

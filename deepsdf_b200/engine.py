@@ -45,7 +45,7 @@ def _declare_train(lib) -> None:
     lib.dsdf_fused_wgrad.restype = C.c_int
     lib.dsdf_fused_wgrad.argtypes = [P(L.NetDesc), P(TrainBufs), i64, vp]
     lib.dsdf_fused_finish.restype = C.c_int
-    lib.dsdf_fused_finish.argtypes = [P(L.NetDesc), vp, P(L.Params), P(TrainBufs), vp, i64, vp, vp, i32, i64, f32, f32, i32,
+    lib.dsdf_fused_finish.argtypes = [P(L.NetDesc), vp, P(L.Params), P(TrainBufs), vp, i64, vp, vp, i32, i64, f32, f32, i32, i32,
                                       P(L.ParamGrads), vp, vp, vp]
     lib.dsdf_adam.restype = C.c_int
     lib.dsdf_adam.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp, vp]
@@ -283,9 +283,13 @@ class FusedEngine:
 
     # ------------------------------------------------------------------ training
     def train_buffers(self, n_rows: int, n_scenes: int) -> Dict[str, torch.Tensor]:
-        key = ("train", n_rows, n_scenes)
-        if self._bufs_key == key:
+        """Caller-owned workspaces of the training step, sized by ``dsdf_train_buf_sizes``.  A set allocated for a larger
+        (rows, scenes) is reused as it is: every size is monotonic in both, and the kernels lay the regions out from the
+        row count of the call - so the chunks of ``--batch_split`` share the allocation of the largest chunk."""
+        k = self._bufs_key
+        if k is not None and k[0] == "train" and k[1] >= n_rows and k[2] >= n_scenes:
             return self._bufs
+        key = ("train", n_rows, n_scenes)
         sizes = (C.c_size_t * 10)()
         L.check(self.lib.dsdf_train_buf_sizes(C.byref(self.desc), n_rows, n_scenes, sizes))
         names = ["acts", "dys", "bitmask", "dy", "tile_loss", "tile_part", "wg_part", "last_part", "scene_sums", "cbias"]
@@ -320,16 +324,18 @@ class FusedEngine:
     def loss_and_grads(self, lat_table: torch.Tensor, scene_ids: torch.Tensor, tile_scene: torch.Tensor, xyz: torch.Tensor,
                        gt: torch.Tensor, *, clamp: float, reg_lambda_eff: float, n_total: int, code_bound: Optional[float],
                        seed: int, row0: int, PG: L.ParamGrads, lat_grad: torch.Tensor, training: bool = True,
-                       point_stride: int = 3, gt_stride: int = 1, n_rows: Optional[int] = None) -> torch.Tensor:
+                       point_stride: int = 3, gt_stride: int = 1, n_rows: Optional[int] = None, accumulate: bool = False,
+                       scene_capacity: int = 0) -> torch.Tensor:
         """train_deep_sdf.py:483-533 for one (local) batch: returns the 2-element loss tensor (total, data term); fills
-        the decoder gradients behind ``PG`` and the dense latent gradient ``lat_grad`` [S_total, L].
+        the decoder gradients behind ``PG`` and the dense latent gradient ``lat_grad`` [S_total, L] (``accumulate``: adds to
+        them and to the loss instead - one chunk of ``--batch_split``).
         ``n_total`` is the GLOBAL batch size (loss normaliser, :519).  ``point_stride=4, gt_stride=4`` read the
         reference's [N,4] (xyz, sdf) sample rows in place: pass ``xyz = samples`` and ``gt = samples.view(-1)[3:]``."""
         N = int(n_rows) if n_rows is not None else xyz.shape[0]
         if N % TILE:
             raise L.DsdfError("fused training needs a multiple of 128 rows (SamplesPerScene % 128 == 0)")
         S = scene_ids.numel()
-        b = self.train_buffers(N, S)
+        b = self.train_buffers(N, max(S, int(scene_capacity)))
         tb = self._tb
         cb = self.scene_bias(lat_table, scene_ids, code_bound, out=b["cbias"].view(torch.bfloat16)[:S * 2 * 512 * 16].view(S, 2, 512, 16))
         io = L.TrainIO()
@@ -369,7 +375,8 @@ class FusedEngine:
             e3 = mark()
             L.check(lib.dsdf_fused_finish(C.byref(desc), self.pack.data_ptr(), C.byref(self._P), C.byref(tb), tile_scene.data_ptr(), N,
                                           lat_table.data_ptr(), scene_ids.data_ptr(), S, lat_table.shape[0], float(reg_lambda_eff),
-                                          1.0 / float(n_total), int(training), C.byref(PG), lat_grad.data_ptr(), b["loss"].data_ptr(), st))
+                                          1.0 / float(n_total), int(training), int(accumulate), C.byref(PG), lat_grad.data_ptr(),
+                                          b["loss"].data_ptr(), st))
             e4 = mark()
         if ev is not None:
             ev.extend([("fused_forward", e0, e1), ("fused_dgrad", e1, e2), ("wgrad", e2, e3), ("finish", e3, e4)])

@@ -122,11 +122,29 @@ class Decoder(nn.Module):
                 f"Decoder expects input [N, {self.spec.full_dims[0]}] (latent ++ xyz), got {tuple(input.shape)}")
         L.require_cuda(input, *self.flat_param_list())
         seed = 0
-        if self.training:
-            # one Philox key per call, drawn from torch's CPU generator -> torch.manual_seed makes runs repeatable
+        if self.training and (self.spec.uses_dropout() or self.spec.latent_dropout):
+            # one Philox key per call, drawn from torch's CPU generator -> torch.manual_seed makes runs repeatable.  Only
+            # when the spec has dropout: a network without it must not disturb the caller's RNG stream (the reference's
+            # DataLoader shuffle draws from the same generator)
             seed = int(torch.randint(0, 2 ** 62, (1,)).item())
         params = self.flat_param_list()
         return _DecoderFn.apply(self, input, bool(self.training), seed, *params)
+
+
+class _SecondOrderGuard(torch.autograd.Function):
+    """Identity on the per-row input gradient G, tied to the decoder's input and parameters in the autograd graph: G is a
+    kernel output, its own derivatives (second order in x or in the parameters) are not provided - asking for them must be
+    an error, not a silent zero."""
+
+    @staticmethod
+    def forward(ctx, G, *deps):
+        return G.view_as(G)
+
+    @staticmethod
+    def backward(ctx, g):
+        raise RuntimeError("deepsdf_b200.Decoder: second-order derivatives (d/dx or d/dparams of dSDF/dinput) are not provided; "
+                           "only the first-order double-backward trick of torch.autograd.functional.jvp (deep_sdf/mesh.py:405-422) "
+                           "and first-order parameter gradients under create_graph=True are")
 
 
 class _DecoderFn(torch.autograd.Function):
@@ -164,6 +182,7 @@ class _DecoderFn(torch.autograd.Function):
                 if need_grad and chunk == N:
                     ctx.saved_ws = ws
         ctx.save_for_backward(x, *params)
+        ctx.inp_ref = inp if inp.requires_grad else None      # only to hang the second-order guard on (backward, create_graph)
         return out
 
     @staticmethod
@@ -184,6 +203,12 @@ class _DecoderFn(torch.autograd.Function):
         go = (torch.ones(N, 1, device=x.device) if double else grad_out.detach()).contiguous().float()
         gin = torch.empty_like(x) if (need_in or double) else None
         pgrads = [torch.empty_like(p) for p in params] if (need_p and not double) else None
+        if double and need_p:
+            # loss.backward(create_graph=True) / a gradient-penalty term: the parameters still get their FIRST-order gradient
+            # (one more backward launch with the real cotangent); it is returned as a constant of the higher-order graph
+            pgrads2 = _DecoderFn._param_grads_only(ctx, module, x, params, P, grad_out.detach().contiguous().float())
+        else:
+            pgrads2 = None
         PG = None
         if pgrads is not None:
             PG = L.ParamGrads()
@@ -211,8 +236,43 @@ class _DecoderFn(torch.autograd.Function):
                     go[r0:r0 + n].data_ptr(), gin[r0:r0 + n].data_ptr() if gin is not None else None,
                     C.byref(PG) if PG is not None else None, int(ci > 0), ws.data_ptr(), nbytes, st))
         if double:
-            # first-order exact; differentiable w.r.t. grad_out (rows are independent scalars)
-            return (None, grad_out * gin, None, None) + tuple(None for _ in params)
+            # first-order exact; differentiable w.r.t. grad_out (rows are independent scalars).  G itself is a constant of the
+            # graph: a request for ITS derivative raises (guard) instead of returning a silent zero.
+            deps = [t for t in ([ctx.inp_ref] if ctx.inp_ref is not None else []) + [p for p in params if p.requires_grad]]
+            G = _SecondOrderGuard.apply(gin, *deps) if deps else gin
+            gp = tuple(g if n else None for g, n in zip(pgrads2, ctx.needs_input_grad[4:])) if pgrads2 is not None else tuple(
+                None for _ in params)
+            return (None, grad_out * G, None, None) + gp
         grads_p = tuple(g if n else None for g, n in zip(pgrads, ctx.needs_input_grad[4:])) if pgrads is not None else tuple(
             None for _ in params)
         return (None, gin if need_in else None, None, None) + grads_p
+
+    @staticmethod
+    def _param_grads_only(ctx, module, x, params, P, go):
+        """Parameter gradients for cotangent ``go`` (no input gradient): the backward launches of the normal path."""
+        lib = L.lib()
+        desc = module._desc
+        N = x.shape[0]
+        pgrads = [torch.empty_like(p) for p in params]
+        PG = L.ParamGrads()
+        it = iter(pgrads)
+        for layer in range(module.spec.num_linear):
+            for name, t in zip(("v", "g", "b", "ln_w", "ln_b"), module.layer_tensors(layer)):
+                if t is not None:
+                    getattr(PG, name)[layer] = next(it).data_ptr()
+        with torch.cuda.device(x.device):
+            st = L.stream_ptr(x.device)
+            chunk = ctx.chunk
+            for ci, r0 in enumerate(range(0, N, chunk)):
+                n = min(chunk, N - r0)
+                nbytes = lib.dsdf_generic_workspace_bytes(C.byref(desc), n)
+                if ctx.saved_ws is not None:
+                    ws = ctx.saved_ws
+                else:
+                    ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+                    scratch = torch.empty(n, 1, device=x.device)
+                    L.check(lib.dsdf_generic_forward(C.byref(desc), C.byref(P), x[r0:r0 + n].data_ptr(), n, int(ctx.training),
+                                                     ctx.seed, r0, scratch.data_ptr(), ws.data_ptr(), nbytes, st))
+                L.check(lib.dsdf_generic_backward(C.byref(desc), C.byref(P), x[r0:r0 + n].data_ptr(), n, int(ctx.training), ctx.seed,
+                                                  r0, go[r0:r0 + n].data_ptr(), None, C.byref(PG), int(ci > 0), ws.data_ptr(), nbytes, st))
+        return pgrads

@@ -64,6 +64,9 @@ class NetSpec:
         return (self.dropout is not None and layer in self.dropout and layer < self.num_linear - 1
                 and self.dropout_prob > 0.0)                                       # decoder.py:105-106
 
+    def uses_dropout(self) -> bool:
+        return any(self.has_dropout(layer) for layer in range(self.num_linear - 1))
+
     def desc(self) -> NetDesc:
         d = NetDesc()
         d.latent_size = self.latent_size

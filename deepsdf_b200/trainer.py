@@ -128,6 +128,7 @@ class SceneTrainer:
         self.code_reg_lambda = get_spec_with_default(specs, "CodeRegularizationLambda", 1e-4)
         self.grad_clip = get_spec_with_default(specs, "GradientClipNorm", None)
         self.step_count = 0
+        self.batch_split = 1          # --batch_split (train_deep_sdf.py:602-609): chunks per batch, gradients accumulated
         self.seed = seed
         self._clip_scratch = torch.zeros(1024, device=self.device)
         self._clip_out = torch.ones(2, device=self.device)
@@ -152,7 +153,7 @@ class SceneTrainer:
     # ------------------------------------------------------------------ one optimiser step
     def step(self, samples: torch.Tensor, scene_ids: torch.Tensor, epoch: int, global_rows: Optional[int] = None,
              row0: int = 0, batch_scene_ids: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """One iteration of train_deep_sdf.py:481-545 (batch_split = 1) on this rank's share of the batch.
+        """One iteration of train_deep_sdf.py:481-545 (``self.batch_split`` chunks, :495-535) on this rank's share of the batch.
 
         samples    [S * SamplesPerScene, 4] fp32 device tensor, scene-major rows of (x, y, z, sdf) - exactly what the
                    reference's DataLoader yields after ``reshape(-1, 4)`` (:483); read in place, never split or copied
@@ -182,10 +183,36 @@ class SceneTrainer:
             if code_bound:
                 eng.scene_bias(self.lat_vecs, batch_scene_ids, code_bound)     # renorm only; the bias it writes is scratch
                 code_bound = None
-        loss = eng.loss_and_grads(self.lat_vecs, scene_ids, tile_scene, flat, flat[3:], clamp=self.clamp if self.enforce_minmax else 0.0,
-                                  reg_lambda_eff=lam, n_total=n_total, code_bound=code_bound, seed=seed,
-                                  row0=row0, PG=self.PG, lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
-                                  n_rows=N)
+        clamp = self.clamp if self.enforce_minmax else 0.0
+        n_tiles = N // TILE
+        k_split = max(1, min(int(self.batch_split), n_tiles))
+        if k_split == 1:
+            loss = eng.loss_and_grads(self.lat_vecs, scene_ids, tile_scene, flat, flat[3:], clamp=clamp,
+                                      reg_lambda_eff=lam, n_total=n_total, code_bound=code_bound, seed=seed,
+                                      row0=row0, PG=self.PG, lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
+                                      n_rows=N)
+        else:
+            # train_deep_sdf.py:495-535: the batch in `batch_split` row chunks (torch.chunk sizes: ceil(rows / k), here in whole
+            # 128-row tiles), every chunk's loss divided by the WHOLE batch's row count (:519), gradients accumulated, one
+            # optimiser step.  Dropout streams are keyed by the global row id, so chunking leaves the masks untouched; the
+            # activation stash is sized by the largest chunk only.
+            tps = sps // TILE
+            per = (n_tiles + k_split - 1) // k_split
+            for c in range(k_split):
+                t0, t1 = c * per, min(n_tiles, (c + 1) * per)
+                if t0 >= t1:
+                    break
+                s0, s1 = t0 // tps, (t1 - 1) // tps + 1               # scenes this chunk touches (a scene may span chunks)
+                key = ("chunk", S, sps, k_split, c)
+                ts = self._tile_scene_cache.get(key)
+                if ts is None:
+                    ts = (torch.arange(t0, t1, dtype=torch.int32, device=self.device) // tps - s0).contiguous()
+                    self._tile_scene_cache[key] = ts
+                part = flat[t0 * TILE * 4:]
+                loss = eng.loss_and_grads(self.lat_vecs, scene_ids[s0:s1], ts, part, part[3:], clamp=clamp, reg_lambda_eff=lam,
+                                          n_total=n_total, code_bound=code_bound, seed=seed, row0=row0 + t0 * TILE, PG=self.PG,
+                                          lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
+                                          n_rows=(t1 - t0) * TILE, accumulate=c > 0, scene_capacity=S)
         # the decoder-gradient all-reduce (NCCL, its own stream) overlaps the latent Adam, which needs no exchange
         work = None
         if self.world_size > 1:

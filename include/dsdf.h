@@ -178,6 +178,9 @@ int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const void* 
  *                                      [n_scenes_total, L] (zeroed, rows of scene_ids written; scene_ids must be
  *                                      unique within a batch), loss_out[0] = loss incl. regulariser, [1] = data term.
  *                                      reg_lambda_eff = CodeRegularizationLambda * min(1, epoch/100) or 0.
+ *                                      training != 0: the step ran with dropout (the stash is unscaled; dW gets the scales).
+ *                                      accumulate != 0: add to the gradients and to loss_out instead of overwriting them - the
+ *                                      chunks of --batch_split (train_deep_sdf.py:495-535); a scene may then span chunks.
  * Every reduction has a fixed order: two runs on the same inputs give bit-identical gradients. */
 typedef struct dsdf_train_bufs {
   void* acts;            /* bf16 [num_hidden][n_rows][512] */
@@ -205,8 +208,8 @@ int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs* bufs, int
 int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
                       const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows, const float* lat_table,
                       const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total, float reg_lambda_eff,
-                      float inv_n, int32_t training, const dsdf_param_grads* pgrads, float* lat_grad, float* loss_out,
-                      void* stream);
+                      float inv_n, int32_t training, int32_t accumulate, const dsdf_param_grads* pgrads, float* lat_grad,
+                      float* loss_out, void* stream);
 /* Row-latent forward: every row brings its own latent code (queries[r] = [latent(L), xyz(3)], row stride ldq floats) - the
  * microstructure consumers of deep_sdf/mesh.py:457-497, whose codes come from a spline over the domain (L = 1 or 2;
  * supported: L <= 4).  Same kernel and same dsdf_train_io as dsdf_fused_forward; the latent columns of lin0 and of the

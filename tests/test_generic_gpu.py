@@ -227,3 +227,47 @@ def test_dropin_decoder_in_reference_loop_reproduces_main_function_fixture():
     for k, v in final.items():
         assert torch.allclose(sd[k].cpu(), v, rtol=1e-4, atol=5e-6), k
     assert torch.allclose(lat_vecs.weight.detach(), torch.from_numpy(z["lat_final"]), rtol=1e-4, atol=5e-6)
+
+
+def test_create_graph_backward_gives_parameter_gradients_and_guards_second_order():
+    """loss.backward(create_graph=True) must still deliver first-order parameter gradients (it returned None), and a
+    second-order request through the kernel's input gradient must raise instead of silently contributing zero."""
+    m, pre, table, rows, xyz, gt = _inputs("small_4x64_L2_tanh")
+    ospec = O.OracleSpec(**m["spec"])
+    params = O.make_params(ospec, m["seed"])
+    mod = build_module(m["spec"], params, DEV).eval()
+    inp = torch.cat([table[rows], xyz], 1)[:512].to(DEV).requires_grad_(True)
+    w = torch.linspace(-1, 1, 512, device=DEV).reshape(-1, 1)
+    # reference gradients (plain backward)
+    (mod(inp) * w).sum().backward()
+    ref_p = {k: p.grad.clone() for k, p in mod.named_parameters()}
+    ref_x = inp.grad.clone()
+    mod.zero_grad()
+    inp.grad = None
+    # create_graph=True: same first-order gradients
+    (mod(inp) * w).sum().backward(create_graph=True)
+    for k, p in mod.named_parameters():
+        assert p.grad is not None and torch.allclose(p.grad.detach(), ref_p[k], rtol=1e-5, atol=1e-7), k
+    assert torch.allclose(inp.grad.detach(), ref_x, rtol=1e-5, atol=1e-7)
+    mod.zero_grad()
+    inp.grad = None
+    # an eikonal-style term: d/dparams of |dSDF/dx| needs second-order kernels -> loud failure
+    y = mod(inp)
+    (gx,) = torch.autograd.grad(y.sum(), inp, create_graph=True)
+    pen = (gx[:, -3:].norm(dim=1) - 1).pow(2).mean()
+    with pytest.raises(RuntimeError, match="second-order"):
+        pen.backward()
+
+
+def test_forward_without_dropout_leaves_the_rng_alone():
+    """a training-mode forward of a spec WITHOUT dropout must not draw from torch's global generator (the reference's
+    DataLoader shuffle shares it)."""
+    m = META["geom2d_3x24_L2"]
+    mod = build_module(m["spec"], None, DEV).train()
+    x = torch.randn(64, 4, device=DEV)
+    torch.manual_seed(123)
+    a = torch.rand(3)
+    torch.manual_seed(123)
+    mod(x)
+    b = torch.rand(3)
+    assert torch.equal(a, b)

@@ -1,0 +1,105 @@
+"""Training-loop features around the fused step (VERDICT r01 missing #7, ADVICE r01 train.py):
+  * --batch_split (train_deep_sdf.py:495-535): chunked gradient accumulation == the unchunked step up to summation order;
+  * OptimizerParameters/*.pth is a real torch.optim.Adam state_dict of the reference's two parameter groups, so that the
+    reference's load_optimizer (train_deep_sdf.py:116-131) accepts it;
+  * --continue (train_deep_sdf.py:420-453): an interrupted + resumed run reproduces the uninterrupted one bit for bit."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from tests.util import build_module
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NET = dict(dims=[512] * 8, dropout=list(range(8)), dropout_prob=0.2, norm_layers=list(range(8)), latent_in=[4],
+           weight_norm=True, xyz_in_all=False, use_tanh=False, latent_dropout=False, geom_dimension=3)
+
+
+def _specs(L=16, sps=1024, spb=4):
+    return {"NetworkSpecs": NET, "CodeLength": L,
+            "LearningRateSchedule": [{"Type": "Step", "Initial": 5e-4, "Interval": 500, "Factor": 0.5},
+                                     {"Type": "Step", "Initial": 1e-3, "Interval": 500, "Factor": 0.5}],
+            "SamplesPerScene": sps, "ScenesPerBatch": spb, "ClampingDistance": 0.1, "CodeRegularization": True,
+            "CodeRegularizationLambda": 1e-4, "CodeBound": 1.0}
+
+
+@pytest.mark.parametrize("split", [2, 3, 7])
+def test_batch_split_accumulates_the_same_gradients(split):
+    from deepsdf_b200.trainer import SceneTrainer
+    from oracle import decoder_oracle as O
+    S, sps = 4, 1024                                     # 32 tiles: 3 chunks = 11 + 11 + 10 tiles, scenes span chunk borders
+    rng = np.random.RandomState(2)
+    xyz = rng.uniform(-1, 1, (S, sps, 3)).astype(np.float32)
+    sdf = np.stack([0.25 * O.corner_spheres_sdf(xyz[s], 0.4 + 0.1 * s, limit=0.9) for s in range(S)]).astype(np.float32)
+    batch = torch.from_numpy(np.concatenate([xyz, sdf.reshape(S, sps, 1)], -1)).reshape(-1, 4).contiguous().to(DEV)
+    ids = torch.tensor([0, 2, 3, 5], device=DEV)
+    out = []
+    for k in (1, split):
+        tr = SceneTrainer(_specs(), 6, DEV, seed=4)
+        tr.batch_split = k
+        loss = tr.step(batch, ids, epoch=50)
+        torch.cuda.synchronize()
+        out.append((loss.cpu().clone(), tr.flat_g.cpu().clone(), tr.lat_grad.cpu().clone(), tr.flat_p.cpu().clone()))
+    (l1, g1, z1, p1), (l2, g2, z2, p2) = out
+    rel_g = float((g1 - g2).norm() / g1.norm())
+    rel_z = float((z1 - z2).norm() / z1.norm())
+    print(f"batch_split {split}: loss {float(l1[0]):.7f} vs {float(l2[0]):.7f}; decoder grad rel diff {rel_g:.2e}, latent grad rel diff {rel_z:.2e}")
+    assert abs(float(l1[0]) - float(l2[0])) <= 1e-6 * abs(float(l1[0])) and abs(float(l1[1]) - float(l2[1])) <= 1e-6 * abs(float(l1[1]))
+    assert rel_g <= 1e-5 and rel_z <= 1e-5               # same tiles, same masks, same per-tile arithmetic: only the order of the sums differs
+    assert float((p1 - p2).abs().max()) <= 2.1 * 5e-4    # one Adam step moves a parameter by at most lr (sign flips of ~0 gradients)
+
+
+def _write_experiment(tmp_path, epochs):
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "make_tiny_experiment.py"), str(tmp_path), "8"])
+    exp = os.path.join(str(tmp_path), "exp")
+    with open(os.path.join(exp, "specs.json")) as f:
+        specs = json.load(f)
+    specs.update(NumEpochs=epochs, SnapshotFrequency=2, LogFrequency=1, ScenesPerBatch=4, SamplesPerScene=1024)
+    with open(os.path.join(exp, "specs.json"), "w") as f:
+        json.dump(specs, f)
+    return exp, specs
+
+
+def test_optimizer_checkpoint_is_a_reference_adam_state_dict_and_continue_is_exact(tmp_path, monkeypatch):
+    from deepsdf_b200 import train as T
+    for k in ("WORLD_SIZE", "RANK", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    # ---- an uninterrupted 4-epoch run
+    exp_a, specs = _write_experiment(tmp_path / "a", 4)
+    res_a = T.main_function(exp_a)
+    # ---- the same run stopped after epoch 2 (a snapshot epoch) and continued from that snapshot
+    exp_b, _ = _write_experiment(tmp_path / "b", 4)
+    T.main_function(exp_b, max_epochs=2)
+    res_b = T.main_function(exp_b, continue_from="2")
+    assert res_b["epochs"] == 4 and len(res_b["loss"]) == len(res_a["loss"])
+    assert res_b["loss"] == res_a["loss"]                                         # bit for bit: deterministic kernels, per-epoch shuffles
+    ma = torch.load(os.path.join(exp_a, "ModelParameters", "latest.pth"), weights_only=False)["model_state_dict"]
+    mb = torch.load(os.path.join(exp_b, "ModelParameters", "latest.pth"), weights_only=False)["model_state_dict"]
+    assert all(torch.equal(ma[k], mb[k]) for k in ma)
+    la = torch.load(os.path.join(exp_a, "LatentCodes", "latest.pth"), weights_only=False)["latent_codes"]["weight"]
+    lb = torch.load(os.path.join(exp_b, "LatentCodes", "latest.pth"), weights_only=False)["latent_codes"]["weight"]
+    assert torch.equal(la, lb)
+    # ---- the optimiser file is what the reference's save_optimizer writes: load it the way load_optimizer does (:116-131) into
+    #      the optimiser train_deep_sdf.py:400-411 builds
+    ck = torch.load(os.path.join(exp_a, "OptimizerParameters", "latest.pth"), weights_only=False)
+    assert ck["epoch"] == 4
+    decoder = torch.nn.DataParallel(build_module(dict(latent_size=specs["CodeLength"], **specs["NetworkSpecs"])))
+    lat_vecs = torch.nn.Embedding(8, specs["CodeLength"], max_norm=specs["CodeBound"])
+    opt = torch.optim.Adam([{"params": decoder.parameters(), "lr": 1e-4}, {"params": lat_vecs.parameters(), "lr": 1e-3}])
+    opt.load_state_dict(ck["optimizer_state_dict"])
+    sd = opt.state_dict()
+    assert len(sd["param_groups"]) == 2 and len(sd["param_groups"][1]["params"]) == 1
+    n_steps = 4 * (8 // 4)
+    for p in list(decoder.parameters()) + list(lat_vecs.parameters()):
+        st = opt.state[p]
+        assert st["exp_avg"].shape == p.shape and st["exp_avg_sq"].shape == p.shape and int(st["step"]) == n_steps
+        assert float(st["exp_avg_sq"].min()) >= 0.0
+    assert float(opt.state[next(iter(lat_vecs.parameters()))]["exp_avg"].abs().sum()) > 0.0
+    # learning rates of the saved epoch (train_deep_sdf.py:315-318)
+    assert abs(sd["param_groups"][0]["lr"] - specs["LearningRateSchedule"][0]["Initial"]) < 1e-12
