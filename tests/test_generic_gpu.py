@@ -236,8 +236,8 @@ def test_create_graph_backward_gives_parameter_gradients_and_guards_second_order
     ospec = O.OracleSpec(**m["spec"])
     params = O.make_params(ospec, m["seed"])
     mod = build_module(m["spec"], params, DEV).eval()
-    inp = torch.cat([table[rows], xyz], 1)[:512].to(DEV).requires_grad_(True)
-    w = torch.linspace(-1, 1, 512, device=DEV).reshape(-1, 1)
+    inp = torch.cat([table[rows], xyz], 1).to(DEV).requires_grad_(True)
+    w = torch.linspace(-1, 1, inp.shape[0], device=DEV).reshape(-1, 1)
     # reference gradients (plain backward)
     (mod(inp) * w).sum().backward()
     ref_p = {k: p.grad.clone() for k, p in mod.named_parameters()}
