@@ -170,7 +170,7 @@ extern "C" int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs
 extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
                                  const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows,
                                  const float* lat_table, const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total,
-                                 float reg_lambda_eff, float inv_n, int32_t training, int32_t accumulate,
+                                 float reg_lambda_eff, float inv_n, int32_t training, int32_t accumulate, int32_t phases,
                                  const dsdf_param_grads* pgrads, float* lat_grad, float* loss_out, void* stream) {
   if (int e = require_sm100()) return e;
   FinishArgs a;
@@ -206,20 +206,28 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
     DSDF_REQUIRE(pgrads->v[l] && pgrads->b[l], "missing gradient pointers");
     if ((desc->weight_norm_mask >> l) & 1) DSDF_REQUIRE(pgrads->g[l] && params->g[l], "missing g pointers");
   }
-  DSDF_LAUNCHED;
-  last_reduce_kernel<<<(FH + 1 + 31) / 32, 256, 0, st>>>(bufs->last_part, kLastBlocks);
-  DSDF_LAUNCHED;
-  scene_sums_kernel<<<dim3(n_scenes, a.n_slots), FH, 0, st>>>(a.tile_part, tile_scene, a.n_tiles, a.n_slots, a.scene_sums);
-  if (lat_grad) {
+  const bool do_scene = (phases & DSDF_FINISH_SCENE) != 0, do_params = (phases & DSDF_FINISH_PARAMS) != 0;
+  DSDF_REQUIRE(do_scene || do_params, "dsdf_fused_finish: phases must name DSDF_FINISH_SCENE and / or DSDF_FINISH_PARAMS");
+  if (do_params) {
+    DSDF_LAUNCHED;
+    last_reduce_kernel<<<(FH + 1 + 31) / 32, 256, 0, st>>>(bufs->last_part, kLastBlocks);
+  }
+  if (do_scene) {
+    DSDF_LAUNCHED;
+    scene_sums_kernel<<<dim3(n_scenes, a.n_slots), FH, 0, st>>>(a.tile_part, tile_scene, a.n_tiles, a.n_slots, a.scene_sums);
+  }
+  if (lat_grad && do_scene) {
     if (!accumulate) DSDF_CHECK_CUDA(cudaMemsetAsync(lat_grad, 0, size_t(n_scenes_total) * desc->latent_size * sizeof(float), st));
     DSDF_LAUNCHED;
     latent_grad_kernel<<<dim3(n_scenes, (desc->latent_size + 7) / 8), 256, 0, st>>>(a);
   }
   int max_out = 0;
   for (int l = 0; l < desc->num_linear; ++l) max_out = desc->out_dim[l] > max_out ? desc->out_dim[l] : max_out;
-  DSDF_LAUNCHED;
-  assemble_grads_kernel<<<dim3(max_out, desc->num_linear), 128, 0, st>>>(a);
-  if (loss_out) {
+  if (do_params) {
+    DSDF_LAUNCHED;
+    assemble_grads_kernel<<<dim3(max_out, desc->num_linear), 128, 0, st>>>(a);
+  }
+  if (loss_out && do_params) {
     DSDF_REQUIRE(lat_grad || reg_lambda_eff == 0.f, "loss with regulariser needs the latent-grad pass");
     DSDF_LAUNCHED;
     loss_kernel<<<1, 256, 0, st>>>(a);

@@ -45,7 +45,7 @@ def _declare_train(lib) -> None:
     lib.dsdf_fused_wgrad.restype = C.c_int
     lib.dsdf_fused_wgrad.argtypes = [P(L.NetDesc), P(TrainBufs), i64, vp]
     lib.dsdf_fused_finish.restype = C.c_int
-    lib.dsdf_fused_finish.argtypes = [P(L.NetDesc), vp, P(L.Params), P(TrainBufs), vp, i64, vp, vp, i32, i64, f32, f32, i32, i32,
+    lib.dsdf_fused_finish.argtypes = [P(L.NetDesc), vp, P(L.Params), P(TrainBufs), vp, i64, vp, vp, i32, i64, f32, f32, i32, i32, i32,
                                       P(L.ParamGrads), vp, vp, vp]
     lib.dsdf_adam.restype = C.c_int
     lib.dsdf_adam.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp, vp]
@@ -325,7 +325,7 @@ class FusedEngine:
                        gt: torch.Tensor, *, clamp: float, reg_lambda_eff: float, n_total: int, code_bound: Optional[float],
                        seed: int, row0: int, PG: L.ParamGrads, lat_grad: torch.Tensor, training: bool = True,
                        point_stride: int = 3, gt_stride: int = 1, n_rows: Optional[int] = None, accumulate: bool = False,
-                       scene_capacity: int = 0) -> torch.Tensor:
+                       scene_capacity: int = 0, side_stream: Optional[torch.cuda.Stream] = None, after_scene=None) -> torch.Tensor:
         """train_deep_sdf.py:483-533 for one (local) batch: returns the 2-element loss tensor (total, data term); fills
         the decoder gradients behind ``PG`` and the dense latent gradient ``lat_grad`` [S_total, L] (``accumulate``: adds to
         them and to the loss instead - one chunk of ``--batch_split``).
@@ -371,12 +371,32 @@ class FusedEngine:
             L.check(lib.dsdf_fused_dgrad(C.byref(desc), self.pack.data_ptr(), C.byref(tb), xyz.data_ptr(), point_stride, N,
                                          int(training), STORE_DYS_TRAIN, SUMS_ALL, st))
             e2 = mark()
-            L.check(lib.dsdf_fused_wgrad(C.byref(desc), C.byref(tb), N, st))
-            e3 = mark()
-            L.check(lib.dsdf_fused_finish(C.byref(desc), self.pack.data_ptr(), C.byref(self._P), C.byref(tb), tile_scene.data_ptr(), N,
-                                          lat_table.data_ptr(), scene_ids.data_ptr(), S, lat_table.shape[0], float(reg_lambda_eff),
-                                          1.0 / float(n_total), int(training), int(accumulate), C.byref(PG), lat_grad.data_ptr(),
-                                          b["loss"].data_ptr(), st))
+
+            def finish(phases, stream_ptr):
+                L.check(lib.dsdf_fused_finish(C.byref(desc), self.pack.data_ptr(), C.byref(self._P), C.byref(tb), tile_scene.data_ptr(), N,
+                                              lat_table.data_ptr(), scene_ids.data_ptr(), S, lat_table.shape[0], float(reg_lambda_eff),
+                                              1.0 / float(n_total), int(training), int(accumulate), phases, C.byref(PG),
+                                              lat_grad.data_ptr(), b["loss"].data_ptr(), stream_ptr))
+
+            if side_stream is None:
+                L.check(lib.dsdf_fused_wgrad(C.byref(desc), C.byref(tb), N, st))
+                e3 = mark()
+                finish(3, st)
+                if after_scene is not None:
+                    after_scene()
+            else:
+                # the per-scene sums, the dense latent gradient (and whatever the caller hangs behind them: the latent Adam) need
+                # only the dgrad chain's per-tile sums: they run on a second stream under the HBM-bound wgrad contraction
+                main = torch.cuda.current_stream(self.device)
+                side_stream.wait_stream(main)
+                with torch.cuda.stream(side_stream):
+                    finish(1, side_stream.cuda_stream)
+                    if after_scene is not None:
+                        after_scene()
+                L.check(lib.dsdf_fused_wgrad(C.byref(desc), C.byref(tb), N, st))
+                e3 = mark()
+                main.wait_stream(side_stream)
+                finish(2, st)
             e4 = mark()
         if ev is not None:
             ev.extend([("fused_forward", e0, e1), ("fused_dgrad", e1, e2), ("wgrad", e2, e3), ("finish", e3, e4)])

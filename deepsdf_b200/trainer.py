@@ -133,6 +133,10 @@ class SceneTrainer:
         self._clip_scratch = torch.zeros(1024, device=self.device)
         self._clip_out = torch.ones(2, device=self.device)
         self._tile_scene_cache: Dict = {}
+        # second stream: per-scene sums, latent gradient and latent Adam run under the wgrad kernel (engine.loss_and_grads)
+        # (DSDF_NO_SIDE_STREAM=1 keeps everything on one stream: A/B timing)
+        import os
+        self.side_stream = None if os.environ.get("DSDF_NO_SIDE_STREAM") else torch.cuda.Stream(device=self.device)
 
     # ------------------------------------------------------------------ helpers
     def tile_scene_for(self, n_scenes: int, samples_per_scene: int) -> torch.Tensor:
@@ -186,11 +190,19 @@ class SceneTrainer:
         clamp = self.clamp if self.enforce_minmax else 0.0
         n_tiles = N // TILE
         k_split = max(1, min(int(self.batch_split), n_tiles))
+        lr_dec, lr_lat = self.learning_rates(epoch)
+        lat_adam_done = False
         if k_split == 1:
+            after = None
+            if not shared_lat:
+                # partitioned latents need no exchange: their Adam follows the latent gradient on the side stream, under wgrad
+                def after():
+                    eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat)
+                lat_adam_done = True
             loss = eng.loss_and_grads(self.lat_vecs, scene_ids, tile_scene, flat, flat[3:], clamp=clamp,
                                       reg_lambda_eff=lam, n_total=n_total, code_bound=code_bound, seed=seed,
                                       row0=row0, PG=self.PG, lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
-                                      n_rows=N)
+                                      n_rows=N, side_stream=self.side_stream, after_scene=after)
         else:
             # train_deep_sdf.py:495-535: the batch in `batch_split` row chunks (torch.chunk sizes: ceil(rows / k), here in whole
             # 128-row tiles), every chunk's loss divided by the WHOLE batch's row count (:519), gradients accumulated, one
@@ -213,16 +225,17 @@ class SceneTrainer:
                                           n_total=n_total, code_bound=code_bound, seed=seed, row0=row0 + t0 * TILE, PG=self.PG,
                                           lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
                                           n_rows=(t1 - t0) * TILE, accumulate=c > 0, scene_capacity=S)
-        # the decoder-gradient all-reduce (NCCL, its own stream) overlaps the latent Adam, which needs no exchange
+        # the one exchange of the step: all-reduce (sum) of the flat decoder gradient (strict mode: + the dense latent gradient
+        # behind it in the same buffer).  Replaces nn.DataParallel's gradient reduction (train_deep_sdf.py:353).
         work = None
         if self.world_size > 1:
             import torch.distributed as dist
             work = dist.all_reduce(self._gbuf, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
-        lr_dec, lr_lat = self.learning_rates(epoch)
-        if shared_lat:                                   # the latent gradient is part of the exchange
-            work.wait()
-            work = None
-        eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat)
+        if not lat_adam_done:
+            if shared_lat:                               # the latent gradient is part of the exchange
+                work.wait()
+                work = None
+            eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat)
         if work is not None:
             work.wait()
         scale_dev = None

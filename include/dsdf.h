@@ -199,6 +199,12 @@ int dsdf_train_buf_sizes(const dsdf_net_desc* desc, int64_t n_rows, int32_t n_sc
  * DSDF_STORE_DYS_TRAIN; input gradient: layer 0 and the latent_in layer; latent-only optimisation: 0).
  * sum_mask: bit t set = emit the per-tile column sums of dY_t (and the xyz-weighted ones of lin0 / latent_in layer)
  * into bufs->tile_part (training: all layers; latent-only optimisation: layer 0 and the latent_in layer). */
+/* dsdf_fused_finish phases.  SCENE needs only dsdf_fused_dgrad's per-tile sums (per-scene sums, dense latent gradient): a
+ * caller may run it on a second stream beside dsdf_fused_wgrad.  PARAMS needs SCENE and dsdf_fused_wgrad (decoder gradients,
+ * loss).  Both bits = the whole finish in order. */
+#define DSDF_FINISH_SCENE 1
+#define DSDF_FINISH_PARAMS 2
+#define DSDF_FINISH_ALL 3
 #define DSDF_STORE_DYS_TRAIN 0xFFFFFFFEu
 #define DSDF_SUMS_ALL 0xFFFFFFFFu
 int dsdf_fused_dgrad(const dsdf_net_desc* desc, const void* pack, const dsdf_train_bufs* bufs, const float* xyz,
@@ -208,8 +214,8 @@ int dsdf_fused_wgrad(const dsdf_net_desc* desc, const dsdf_train_bufs* bufs, int
 int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_params* params,
                       const dsdf_train_bufs* bufs, const int32_t* tile_scene, int64_t n_rows, const float* lat_table,
                       const int64_t* scene_ids, int32_t n_scenes, int64_t n_scenes_total, float reg_lambda_eff,
-                      float inv_n, int32_t training, int32_t accumulate, const dsdf_param_grads* pgrads, float* lat_grad,
-                      float* loss_out, void* stream);
+                      float inv_n, int32_t training, int32_t accumulate, int32_t phases, const dsdf_param_grads* pgrads,
+                      float* lat_grad, float* loss_out, void* stream);
 /* Row-latent forward: every row brings its own latent code (queries[r] = [latent(L), xyz(3)], row stride ldq floats) - the
  * microstructure consumers of deep_sdf/mesh.py:457-497, whose codes come from a spline over the domain (L = 1 or 2;
  * supported: L <= 4).  Same kernel and same dsdf_train_io as dsdf_fused_forward; the latent columns of lin0 and of the
