@@ -54,8 +54,9 @@ def subsample_counts(n_pos: int, n_neg: int, subsample: int):
 class DeviceSDFSamples:
     def __init__(self, data_source: Optional[str], split: Optional[Dict], subsample: int, geom_dimension: int = 3, device="cuda",
                  arrays: Optional[Sequence] = None):
-        """Same constructor meaning as ``SDFSamples(data_source, split, subsample, geom_dimension)``; ``arrays`` (a list of
-        (pos[n,4], neg[m,4]) numpy pairs) replaces the files for synthetic data."""
+        """Same constructor meaning as ``SDFSamples(data_source, split, subsample, geom_dimension)``; ``arrays`` (an iterable
+        of (pos[n,4], neg[m,4]) pairs, numpy or torch - device tensors stay on the device) replaces the files for synthetic
+        data."""
         if geom_dimension != 3:
             raise L.DsdfError("DeviceSDFSamples stores [n,4] rows (geom_dimension 3)")
         self.subsample = subsample
@@ -63,26 +64,39 @@ class DeviceSDFSamples:
         self.device = torch.device(device)
         if arrays is None:
             self.npyfiles = get_instance_filenames(data_source, split)
-            arrays = []
-            for f in self.npyfiles:
-                npz = np.load(os.path.join(data_source, sdf_samples_subdir, f))
-                arrays.append((npz["pos"], npz["neg"]))
+
+            def scenes():
+                for f in self.npyfiles:
+                    npz = np.load(os.path.join(data_source, sdf_samples_subdir, f))
+                    yield npz["pos"], npz["neg"]
+            it = scenes()
         else:
             self.npyfiles = [f"<array {i}>" for i in range(len(arrays))]
-        chunks, meta, off = [], [], 0
-        for pos, neg in arrays:
-            pos, neg = remove_nans_np(np.asarray(pos), 3), remove_nans_np(np.asarray(neg), 3)
-            meta.append([off, len(pos), off + len(pos), len(neg)])
-            off += len(pos) + len(neg)
-            chunks += [pos, neg]
+            it = iter(arrays)
+        # Streamed load: one scene at a time goes host -> device (the host never holds more than one scene; a scene handed
+        # over as a pair of DEVICE tensors is taken as it is), then ONE device-side concatenation builds the store.
+        parts, meta, off = [], [], 0
+        for pos, neg in it:
+            pos, neg = self._to_device_rows(pos), self._to_device_rows(neg)
+            meta.append([off, pos.shape[0], off + pos.shape[0], neg.shape[0]])
+            off += pos.shape[0] + neg.shape[0]
+            parts += [pos, neg]
         take = [subsample_counts(m[1], m[3], subsample) for m in meta]
         for f, m, (tp, tn) in zip(self.npyfiles, meta, take):
             if tp > m[1] or tn > m[3]:
                 raise L.DsdfError(f"{f}: {m[1]} positive + {m[3]} negative rows cannot supply {subsample} samples per scene")
         self.meta_host = np.asarray(meta, dtype=np.int64).reshape(-1, 4)
         self.meta = torch.from_numpy(self.meta_host).to(self.device)
-        self.store = torch.from_numpy(np.concatenate(chunks, 0) if chunks else np.zeros((0, 4), np.float32)).to(self.device)
+        self.store = torch.cat(parts, 0) if parts else torch.zeros(0, 4, device=self.device)
+        del parts
         self.total_rows = off
+
+    def _to_device_rows(self, rows) -> torch.Tensor:
+        """One sign's rows of one scene as an fp32 [n,4] device tensor, NaN rows dropped (``remove_nans``, data.py:61-63)."""
+        if isinstance(rows, torch.Tensor):
+            t = rows.to(self.device, torch.float32)
+            return t[~torch.isnan(t[:, 3])].contiguous()
+        return torch.from_numpy(remove_nans_np(np.asarray(rows), 3)).to(self.device)
 
     def __len__(self) -> int:
         return len(self.npyfiles)

@@ -193,16 +193,12 @@ class SceneTrainer:
         lr_dec, lr_lat = self.learning_rates(epoch)
         lat_adam_done = False
         if k_split == 1:
-            after = None
-            if not shared_lat:
-                # partitioned latents need no exchange: their Adam follows the latent gradient on the side stream, under wgrad
-                def after():
-                    eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat)
-                lat_adam_done = True
+            # (the latent Adam must NOT ride the side stream: the parameter phase of finish still reads the pre-update codes
+            #  for the gradients of the latent weight columns; it runs after finish, beside the all-reduce)
             loss = eng.loss_and_grads(self.lat_vecs, scene_ids, tile_scene, flat, flat[3:], clamp=clamp,
                                       reg_lambda_eff=lam, n_total=n_total, code_bound=code_bound, seed=seed,
                                       row0=row0, PG=self.PG, lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
-                                      n_rows=N, side_stream=self.side_stream, after_scene=after)
+                                      n_rows=N, side_stream=self.side_stream)
         else:
             # train_deep_sdf.py:495-535: the batch in `batch_split` row chunks (torch.chunk sizes: ceil(rows / k), here in whole
             # 128-row tiles), every chunk's loss divided by the WHOLE batch's row count (:519), gradients accumulated, one
