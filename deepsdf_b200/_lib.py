@@ -73,6 +73,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_fused_supported": (C.c_int, [P(NetDesc)]),
         "dsdf_pack_bytes": (sz, [P(NetDesc)]),
         "dsdf_pack_weights": (C.c_int, [P(NetDesc), P(Params), vp, vp]),
+        "dsdf_pack_weights_ex": (C.c_int, [P(NetDesc), P(Params), vp, u32, vp]),
         "dsdf_scene_aux_bytes": (sz, [i32]),
         "dsdf_scene_prepare": (C.c_int, [P(NetDesc), vp, vp, vp, i32, f32, vp, vp]),
         "dsdf_fused_forward": (C.c_int, [P(NetDesc), vp, vp, vp, vp, i32, i64, vp, P(TrainIO), vp]),

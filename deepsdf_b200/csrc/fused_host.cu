@@ -91,7 +91,7 @@ int fused_layout(const dsdf_net_desc* d, FusedLayout* lo) {
   lo->jac_rows = (LD + 15) / 16 * 16;
   lo->off_wjac = align_up(off, 1024);   off = align_up(lo->off_wjac + size_t(lo->jac_rows) * 2 * FH * 2, 1024);
   for (int l = 0; l < nl; ++l) {
-    lo->off_weff[l] = off;  off = align_up(off + size_t(d->out_dim[l]) * d->in_dim[l] * 4, 256);
+    lo->off_weff[l] = off;                 // (boundary marker: the fp32 folded copy was never read and is no longer written)
     lo->off_invn[l] = off;  off = align_up(off + size_t(d->out_dim[l]) * 4, 256);
   }
   lo->total_bytes = off;
@@ -104,6 +104,7 @@ struct PackArgs {
   dsdf_params params;
   FusedLayout lo;
   uint8_t* pack;
+  int32_t want_eval, want_train;      // which variants of the big bf16 blocks / w_last to write
 };
 
 // grid: (max out rows, num_linear); block 128.  One block folds one output row of one layer.
@@ -140,13 +141,12 @@ __global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
   }
   __syncthreads();
   const float scale = s_scale;
-  float* weff = reinterpret_cast<float*>(a.pack + a.lo.off_weff[l]) + size_t(o) * in;
   __nv_bfloat16* wp = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wp);
-  __nv_bfloat16* wpt = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wpt);
-  // training variants (dropout scale of the previous hidden layer folded into the activation columns)
+  // training variants (dropout scale of the previous hidden layer folded into the activation columns).  The W^T blocks of
+  // both variants are written by pack_transpose_kernel from the W blocks (a row-wise kernel would scatter 2-byte stores).
   const bool two = a.lo.off_wp_tr != a.lo.off_wp;
+  const bool ev = a.want_eval != 0 || !two, tr = a.want_train != 0 && two;
   __nv_bfloat16* wp_tr = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wp_tr);
-  __nv_bfloat16* wpt_tr = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wpt_tr);
   float* wlast_tr = reinterpret_cast<float*>(a.pack + a.lo.off_wlast_tr);
   const float ins = a.lo.in_scale[l];
   __nv_bfloat16* aux_row = reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_aux) + (size_t(l < nh ? l : 0) * FH + o) * AUX_W;
@@ -157,17 +157,12 @@ __global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
   const int L = d.latent_size;
   for (int k = threadIdx.x; k < in; k += blockDim.x) {
     const float w = vrow[k] * scale;
-    weff[k] = w;
-    if (l == nh) { wlast[k] = w; if (two) wlast_tr[k] = w * ins; continue; }
+    if (l == nh) { if (ev) wlast[k] = w; if (tr) wlast_tr[k] = w * ins; continue; }
     const int xw = a.lo.xw[l];
     if (k < xw) {
       if (l > 0) {
-        wp[size_t(a.lo.fwd_row0[l] + o) * FH + k] = __float2bfloat16_rn(w);
-        wpt[size_t(a.lo.bwd_row0[l] + k) * FH + o] = __float2bfloat16_rn(w);
-        if (two) {
-          wp_tr[size_t(a.lo.fwd_row0[l] + o) * FH + k] = __float2bfloat16_rn(w * ins);
-          wpt_tr[size_t(a.lo.bwd_row0[l] + k) * FH + o] = __float2bfloat16_rn(w * ins);
-        }
+        if (ev) wp[size_t(a.lo.fwd_row0[l] + o) * FH + k] = __float2bfloat16_rn(w);
+        if (tr) wp_tr[size_t(a.lo.fwd_row0[l] + o) * FH + k] = __float2bfloat16_rn(w * ins);
       }
     } else if (a.lo.lat_col0[l] >= 0 && k < a.lo.lat_col0[l] + L) {
       const int slot = (l == 0) ? 0 : 1;
@@ -190,6 +185,27 @@ __global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
       __nv_bfloat16* c = aux_row + AUX_COL_XYZ + 3 * dx;
       c[0] = hi; c[1] = hi; c[2] = lo2;
     }
+  }
+}
+
+// W^T blocks (the dgrad chain's B operand: rows = input features, K = output features) from the W blocks just written:
+// 32 x 32 tiles through shared memory, so that both the reads and the writes are 64-byte row segments.
+// grid (16, 16, hidden layers 1..nh-1), block (32, 8); src / dst select the variant.
+__global__ void pack_transpose_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst, FusedLayout lo,
+                                      dsdf_net_desc d) {
+  const int l = blockIdx.z + 1;
+  const int out = d.out_dim[l], xw = lo.xw[l];
+  const int o0 = blockIdx.y * 32, k0 = blockIdx.x * 32;
+  if (o0 >= out || k0 >= xw) return;
+  __shared__ __nv_bfloat16 t[32][34];
+  for (int r = threadIdx.y; r < 32; r += 8) {
+    const int o = o0 + r, k = k0 + threadIdx.x;
+    t[r][threadIdx.x] = (o < out && k < xw) ? src[size_t(lo.fwd_row0[l] + o) * FH + k] : __float2bfloat16_rn(0.f);
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += 8) {
+    const int k = k0 + r, o = o0 + threadIdx.x;
+    if (k < xw && o < out) dst[size_t(lo.bwd_row0[l] + k) * FH + o] = t[threadIdx.x][r];
   }
 }
 
@@ -228,9 +244,16 @@ __global__ void scene_bias_kernel(const float* __restrict__ table, const int64_t
   uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
   if (slot == 0 || lat_layer > 0) {
     const int l = (slot == 0) ? 0 : lat_layer;
-    float acc = bias[l * FH + o];
+    // four independent partial sums: the loop is a chain of dependent L2 loads otherwise (19 us for 8 scenes at L = 256)
     const float* wl = wlatT + size_t(slot) * L * FH + o;
-    for (int k = 0; k < L; ++k) acc += wl[size_t(k) * FH] * z[k];
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    int k = 0;
+    for (; k + 4 <= L; k += 4) {
+      a0 += wl[size_t(k) * FH] * z[k];         a1 += wl[size_t(k + 1) * FH] * z[k + 1];
+      a2 += wl[size_t(k + 2) * FH] * z[k + 2]; a3 += wl[size_t(k + 3) * FH] * z[k + 3];
+    }
+    for (; k < L; ++k) a0 += wl[size_t(k) * FH] * z[k];
+    const float acc = bias[l * FH + o] + ((a0 + a1) + (a2 + a3));
     __nv_bfloat16 e[AUX_SCENE_W];
 #pragma unroll
     for (int i = 0; i < AUX_SCENE_W; ++i) e[i] = __float2bfloat16_rn(0.f);
@@ -288,23 +311,45 @@ extern "C" size_t dsdf_pack_bytes(const dsdf_net_desc* desc) {
   return lo.total_bytes;
 }
 
-extern "C" int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, void* stream) {
+extern "C" int dsdf_pack_weights_ex(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, uint32_t flags, void* stream) {
   if (int e = require_sm100()) return e;
   PackArgs a;
   a.desc = *desc;
   a.params = *params;
   if (int e = fused_layout(desc, &a.lo)) return e;
   a.pack = static_cast<uint8_t*>(pack);
+  a.want_eval = (flags & DSDF_PACK_EVAL) != 0;
+  a.want_train = (flags & DSDF_PACK_TRAIN) != 0;
+  DSDF_REQUIRE(a.want_eval || a.want_train, "dsdf_pack_weights_ex: flags must name DSDF_PACK_EVAL and / or DSDF_PACK_TRAIN");
   DSDF_REQUIRE((reinterpret_cast<uintptr_t>(pack) & 1023) == 0, "pack buffer must be 1024-byte aligned");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  // zero the padded regions (bf16 blocks, bias, wxyz, wlatT, wlast)
-  DSDF_CHECK_CUDA(cudaMemsetAsync(pack, 0, a.lo.off_weff[0], st));
+  // the padded regions (rows / columns beyond the layer shapes) are never written: they only need zeroing once per buffer
+  if (flags & DSDF_PACK_ZERO) DSDF_CHECK_CUDA(cudaMemsetAsync(pack, 0, a.lo.off_weff[0], st));
   int max_out = 0;
   for (int l = 0; l < desc->num_linear; ++l) max_out = desc->out_dim[l] > max_out ? desc->out_dim[l] : max_out;
   DSDF_LAUNCHED;
   pack_weights_kernel<<<dim3(max_out, desc->num_linear), 128, 0, st>>>(a);
+  const bool two = a.lo.off_wp_tr != a.lo.off_wp;
+  const uint8_t* p = a.pack;
+  if (a.lo.num_hidden > 1) {
+    const dim3 grid(FH / 32, FH / 32, a.lo.num_hidden - 1), block(32, 8);
+    if (a.want_eval || !two) {
+      DSDF_LAUNCHED;
+      pack_transpose_kernel<<<grid, block, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(p + a.lo.off_wp),
+                                                    reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wpt), a.lo, a.desc);
+    }
+    if (a.want_train && two) {
+      DSDF_LAUNCHED;
+      pack_transpose_kernel<<<grid, block, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(p + a.lo.off_wp_tr),
+                                                    reinterpret_cast<__nv_bfloat16*>(a.pack + a.lo.off_wpt_tr), a.lo, a.desc);
+    }
+  }
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+extern "C" int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, void* stream) {
+  return dsdf_pack_weights_ex(desc, params, pack, DSDF_PACK_EVAL | DSDF_PACK_TRAIN | DSDF_PACK_ZERO, stream);
 }
 
 extern "C" size_t dsdf_scene_aux_bytes(int32_t n_scenes) { return size_t(n_scenes > 0 ? n_scenes : 0) * 2 * FH * AUX_SCENE_W * 2; }

@@ -210,7 +210,7 @@ extern "C" int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, co
   DSDF_REQUIRE(do_scene || do_params, "dsdf_fused_finish: phases must name DSDF_FINISH_SCENE and / or DSDF_FINISH_PARAMS");
   if (do_params) {
     DSDF_LAUNCHED;
-    last_reduce_kernel<<<(FH + 1 + 31) / 32, 256, 0, st>>>(bufs->last_part, kLastBlocks);
+    last_reduce_kernel<<<(FH + 1 + 31) / 32, 1024, 0, st>>>(bufs->last_part, kLastBlocks);
   }
   if (do_scene) {
     DSDF_LAUNCHED;

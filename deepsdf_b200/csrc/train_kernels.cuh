@@ -63,24 +63,24 @@ __global__ void __launch_bounds__(FH) scene_sums_kernel(const float* __restrict_
   scene_sums[(size_t(s) * n_slots + slot) * FH + c] = acc;
 }
 
-// last_part[0][k] = sum_b last_part[b][k] (fixed order: warp w adds blocks w, w+8, ...; then warps 0..7 in order).
-// grid ceil(513/32), block 256: lane = column within the 32-column group -> 128-byte reads.  In place: a block only ever
+// last_part[0][k] = sum_b last_part[b][k] (fixed order: warp w adds blocks w, w+32, ...; then warps 0..31 in order).
+// grid ceil(513/32), block 1024: lane = column within the 32-column group -> 128-byte reads.  In place: a block only ever
 // touches its own columns, and writes them after all its reads.
-__global__ void __launch_bounds__(256) last_reduce_kernel(float* __restrict__ last_part, int n_blocks) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+__global__ void __launch_bounds__(1024) last_reduce_kernel(float* __restrict__ last_part, int n_blocks) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;      // 32 warps: a quarter of the serial depth of 8
   const int k = blockIdx.x * 32 + lane;
-  __shared__ float red[8][32];
+  __shared__ float red[32][32];
   float acc = 0.f;
   if (k <= FH) {
 #pragma unroll 8
-    for (int b = warp; b < n_blocks; b += 8) acc += last_part[size_t(b) * (FH + 1) + k];
+    for (int b = warp; b < n_blocks; b += 32) acc += last_part[size_t(b) * (FH + 1) + k];
   }
   red[warp][lane] = acc;
   __syncthreads();
   if (warp == 0 && k <= FH) {
     float t = red[0][lane];
 #pragma unroll
-    for (int w = 1; w < 8; ++w) t += red[w][lane];
+    for (int w = 1; w < 32; ++w) t += red[w][lane];
     last_part[k] = t;
   }
 }

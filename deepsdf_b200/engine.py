@@ -78,24 +78,35 @@ class FusedEngine:
         self._bufs_key = None
         self._bufs: Dict[str, torch.Tensor] = {}
         self.kernel_events = None      # set to a list to collect (name, start_event, end_event) per fused kernel call
+        self._eval_fresh = False
         self.repack()
 
     # ------------------------------------------------------------------ weights
     def _st(self) -> int:
         return L.stream_ptr(self.device)
 
-    def repack(self, force: bool = True) -> None:
+    def repack(self, force: bool = True, train_only: bool = False) -> None:
         """Fold g*v/||v|| and rebuild the bf16 operand packs from the decoder's *current* parameters.  ``force=False``
         skips the launch when no parameter tensor changed since the last pack (``small.param_key``: torch's version
-        counters + the trainer's ``_param_epoch``)."""
+        counters + the trainer's ``_param_epoch``).  ``train_only`` rewrites only the training variants of the big blocks (the
+        dropout scale folded into the next layer's weights): what a training loop needs every step; the eval variants are
+        then rebuilt on demand by the first eval-mode call (``_ensure_eval``)."""
         from .small import param_key
         key = param_key(self.decoder)
-        if not force and key == getattr(self, "_pack_key", None):
+        if not force and key == getattr(self, "_pack_key", None) and (train_only or self._eval_fresh):
             return
         self._P = self.decoder.c_params()
+        PACK_EVAL, PACK_TRAIN, PACK_ZERO = 1, 2, 4
+        flags = (PACK_TRAIN if train_only else PACK_EVAL | PACK_TRAIN) | (0 if getattr(self, "_pack_key", None) is not None else PACK_ZERO)
         with torch.cuda.device(self.device):
-            L.check(self.lib.dsdf_pack_weights(C.byref(self.desc), C.byref(self._P), self.pack.data_ptr(), self._st()))
+            L.check(self.lib.dsdf_pack_weights_ex(C.byref(self.desc), C.byref(self._P), self.pack.data_ptr(), flags, self._st()))
         self._pack_key = key
+        self._eval_fresh = not train_only
+
+    def _ensure_eval(self) -> None:
+        """Eval-mode entry points read the plain (unscaled) blocks: rebuild them if the last re-pack skipped them."""
+        if not self._eval_fresh:
+            self.repack(force=True, train_only=False)
 
     def _b_last(self) -> torch.Tensor:
         return getattr(self.decoder, "lin" + str(self.spec.num_linear - 1)).bias
@@ -125,6 +136,7 @@ class FusedEngine:
         assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.shape[1] == 3
         assert tile_scene.dtype == torch.int32 and tile_scene.numel() == (N + TILE - 1) // TILE
         sdf = out if out is not None else torch.empty(N, device=self.device)
+        self._ensure_eval()
         io = L.TrainIO()
         io.b_last = self._b_last().data_ptr()
         io.training = 0
@@ -176,6 +188,7 @@ class FusedEngine:
         assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.shape[1] == 3
         assert tile_scene.dtype == torch.int32 and tile_scene.numel() == N // TILE
         Lz = self.spec.latent_size
+        self._ensure_eval()
         b = self.grad_buffers(N)
         sdf = sdf if sdf is not None else torch.empty(N, device=self.device)
         G = G if G is not None else torch.empty(N, Lz + 3, device=self.device)
@@ -210,6 +223,7 @@ class FusedEngine:
         if N == 0 or (with_grad and N % TILE):
             raise L.DsdfError("sdf_and_input_grad_rows needs a positive multiple of 128 rows (pad the queries)")
         assert queries.dtype == torch.float32 and queries.is_contiguous() and width == Lz + 3
+        self._ensure_eval()
         sdf = sdf if sdf is not None else torch.empty(N, device=self.device)
         io = L.TrainIO()
         io.b_last = self._b_last().data_ptr()
@@ -252,6 +266,7 @@ class FusedEngine:
         lat_grad [S, L] = d(mean|clamp(pred)-clamp(gt)| + l2reg*mean(z^2))/dz and shape_loss [S]."""
         N = samples.shape[0]
         S = scene_ids.numel()
+        self._ensure_eval()
         b = self.grad_buffers(N, need_dys=False)
         if "cbias" not in b or b["cbias"].shape[0] != S:
             b["cbias"] = torch.empty(S, 2, 512, 16, dtype=torch.bfloat16, device=self.device)
@@ -334,6 +349,8 @@ class FusedEngine:
         N = int(n_rows) if n_rows is not None else xyz.shape[0]
         if N % TILE:
             raise L.DsdfError("fused training needs a multiple of 128 rows (SamplesPerScene % 128 == 0)")
+        if not training:
+            self._ensure_eval()
         S = scene_ids.numel()
         b = self.train_buffers(N, max(S, int(scene_capacity)))
         tb = self._tb

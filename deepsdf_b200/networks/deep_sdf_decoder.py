@@ -235,16 +235,19 @@ class _DecoderFn(torch.autograd.Function):
                     C.byref(desc), C.byref(P), x[r0:r0 + n].data_ptr(), n, int(ctx.training), ctx.seed, r0,
                     go[r0:r0 + n].data_ptr(), gin[r0:r0 + n].data_ptr() if gin is not None else None,
                     C.byref(PG) if PG is not None else None, int(ci > 0), ws.data_ptr(), nbytes, st))
+        # create_graph=True: the kernel's input gradient is a constant of the higher-order graph; hang it on a guard node so that
+        # a request for ITS derivative (second order in x or in the parameters) raises instead of contributing a silent zero
+        deps = [t for t in ([ctx.inp_ref] if ctx.inp_ref is not None else []) + [p for p in params if p.requires_grad]]
         if double:
-            # first-order exact; differentiable w.r.t. grad_out (rows are independent scalars).  G itself is a constant of the
-            # graph: a request for ITS derivative raises (guard) instead of returning a silent zero.
-            deps = [t for t in ([ctx.inp_ref] if ctx.inp_ref is not None else []) + [p for p in params if p.requires_grad]]
+            # first-order exact; differentiable w.r.t. grad_out (rows are independent scalars)
             G = _SecondOrderGuard.apply(gin, *deps) if deps else gin
             gp = tuple(g if n else None for g, n in zip(pgrads2, ctx.needs_input_grad[4:])) if pgrads2 is not None else tuple(
                 None for _ in params)
             return (None, grad_out * G, None, None) + gp
         grads_p = tuple(g if n else None for g, n in zip(pgrads, ctx.needs_input_grad[4:])) if pgrads is not None else tuple(
             None for _ in params)
+        if need_in and torch.is_grad_enabled() and deps:
+            gin = _SecondOrderGuard.apply(gin, *deps)
         return (None, gin if need_in else None, None, None) + grads_p
 
     @staticmethod

@@ -241,7 +241,7 @@ class SceneTrainer:
         eng.adam(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.step_count, lr_dec, scale_dev=scale_dev)
         # the kernel wrote the parameters behind torch's version counters: cached packs of other engines key on this
         object.__setattr__(self.decoder, "_param_epoch", getattr(self.decoder, "_param_epoch", 0) + 1)
-        eng.repack()
+        eng.repack(train_only=True)      # the training variants only; an eval-mode call on this engine rebuilds the others
         return loss
 
     def step_from_host(self, samples_host: torch.Tensor, scene_ids_host: torch.Tensor, epoch: int, staging: Dict,

@@ -154,6 +154,14 @@ typedef struct dsdf_train_io {
 int dsdf_fused_supported(const dsdf_net_desc* desc);
 size_t dsdf_pack_bytes(const dsdf_net_desc* desc);
 int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, void* stream);
+/* The same with a choice of what to (re)write.  The big bf16 blocks and w_last exist in two variants: EVAL (plain folded
+ * weights: eval-mode forwards, input gradients, latent optimisation) and TRAIN (the inverted-dropout scale of hidden layer
+ * l-1 multiplied into the activation columns of layer l: the training step).  A training loop re-packs DSDF_PACK_TRAIN only.
+ * DSDF_PACK_ZERO also zeroes the padded regions; needed once per buffer (dsdf_pack_weights = all three). */
+#define DSDF_PACK_EVAL 1u
+#define DSDF_PACK_TRAIN 2u
+#define DSDF_PACK_ZERO 4u
+int dsdf_pack_weights_ex(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, uint32_t flags, void* stream);
 /* nn.Embedding(max_norm) renorm of the listed rows (in place, max_norm <= 0: off) + the per-scene aux rows
  * scene_aux [n_scenes][2][512][16] bf16 (dsdf_scene_aux_bytes, 16-byte aligned; NULL: renorm only): per output feature the
  * scene's bias of lin0 / the latent_in layer (layer bias + latent columns . z, fp32, split hi + lo) and the layer's xyz
