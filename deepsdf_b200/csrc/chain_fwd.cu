@@ -380,12 +380,22 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           for (int i = 0; i < 16; ++i) e[i] = 0u;
           if (valid) {
             const float* pl = args.row_lat + (int64_t(tile_c) * TILE_M + rt) * args.row_lat_stride;
+            if (args.row_lat_dim <= AUX_MAX_ROW_LAT) {
 #pragma unroll
-            for (int d = 0; d < AUX_MAX_ROW_LAT; ++d)
-              if (d < args.row_lat_dim) {
-                const Tri t = split3(__ldg(pl + d));
-                e[3 * d] = t.h; e[3 * d + 1] = t.l; e[3 * d + 2] = t.h;
+              for (int d = 0; d < AUX_MAX_ROW_LAT; ++d)
+                if (d < args.row_lat_dim) {
+                  const Tri t = split3(__ldg(pl + d));
+                  e[3 * d] = t.h; e[3 * d + 1] = t.l; e[3 * d + 2] = t.h;
+                }
+            } else {
+              // 4 < L <= 16: one bf16 term per component (this thread's k-core only: components 8 (j - 2) .. 8 (j - 2) + 7)
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const int d = (j - 2) * 8 + i;
+                const uint32_t v = (d < args.row_lat_dim) ? uint32_t(__bfloat16_as_ushort(__float2bfloat16_rn(__ldg(pl + d)))) : 0u;
+                if (j == 2) e[i] = v; else e[8 + i] = v;
               }
+            }
           }
           if (j == 2) { w0 = e[0] | (e[1] << 16); w1 = e[2] | (e[3] << 16); w2 = e[4] | (e[5] << 16); w3 = e[6] | (e[7] << 16); }
           else { w0 = e[8] | (e[9] << 16); w1 = e[10] | (e[11] << 16); w2 = e[12] | (e[13] << 16); w3 = e[14] | (e[15] << 16); }

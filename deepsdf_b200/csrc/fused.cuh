@@ -29,14 +29,17 @@ constexpr int MASK_WORDS = FH / 32;               // 16 x u32 keep/relu bits per
 //   col 11, 12  A = 0, 0 (rank 0) / 1, 1 (rank 1)                     B = bias_hi, bias_lo   (the pair shares ONE B operand:
 //               the two CTAs' tiles may belong to different scenes, so k-core 0 comes from rank 0's scene and k-core 1 from
 //               rank 1's, and each CTA switches on its own copy of the bias with its 'one' columns)
-//   col 16+3d.. A = (z_d hi, lo, hi), d < 4 (row-latent mode)         B = (w hi, hi, lo) of latent column d
+//   col 16+3d.. A = (z_d hi, lo, hi), d < 4 (row-latent mode, L <= 4) B = (w hi, hi, lo) of latent column d
+//   col 16+d    A = bf16(z_d), d < 16 (row-latent mode, 4 < L <= 16)   B = bf16(w) of latent column d - one term each: the
+//               precision of every other bf16 operand of the chain (codes of the reference's L = 16 experiments)
 // Both sides use the SWIZZLE_NONE K-major canonical layout: 8-row x 16-byte core matrices, rows of a k-core contiguous
 // (SBO = 128 B), k-cores 2 KB apart (LBO = 2048 B).
 constexpr int AUX_W = 32;
 constexpr int AUX_SCENE_W = 16;
 constexpr int AUX_CORE_BYTES = TILE_M * 16;       // one k-core of 128 rows: 2 KB
 constexpr int AUX_COL_ONE0 = 0, AUX_COL_XYZ = 2, AUX_COL_ONE1 = 11, AUX_COL_LAT = 16;
-constexpr int AUX_MAX_ROW_LAT = 4;
+constexpr int AUX_MAX_ROW_LAT = 4;            // hi/lo-split (3-term) per-row codes
+constexpr int AUX_MAX_ROW_LAT1 = 16;          // single-term per-row codes
 
 // One hidden layer of a chain (forward: lin{l}; backward: dgrad of lin{l}).
 struct ChainLayer {
@@ -80,7 +83,8 @@ struct FwdArgs {
   int32_t dy_unit;                          // gt == null: dy_out = d sdf / d(pre-tanh output)  (input-gradient path)
   const int32_t* tile_rows;                 // [n_tiles] valid rows of each tile (ragged scenes padded to 128), or null
   uint32_t philox_rk[16];                   // Philox round keys of `seed` (common.cuh philox_round_keys)
-  // row-latent mode (every row brings its own latent code, L <= 4: the microstructure consumers of deep_sdf/mesh.py:457-497)
+  // row-latent mode (every row brings its own latent code, L <= 16: the microstructure consumers of deep_sdf/mesh.py:457-497
+  // with L = 1, 2, and decoder(input[N, L+3]) of the L = 16 experiments)
   const float* row_lat;                     // row r's code at row_lat + r*row_lat_stride, or null (scene mode)
   int32_t row_lat_stride;
   int32_t row_lat_dim;                      // L

@@ -174,6 +174,8 @@ __global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
         split_bf16(w, hi, lo2);
         __nv_bfloat16* c = aux_row + AUX_COL_LAT + 3 * dlat;
         c[0] = hi; c[1] = hi; c[2] = lo2;
+      } else if (L <= AUX_MAX_ROW_LAT1) {   // 4 < L <= 16: one bf16 term per latent column
+        aux_row[AUX_COL_LAT + dlat] = __float2bfloat16_rn(w);
       }
     } else if (a.lo.xyz_col0[l] >= 0 && k >= a.lo.xyz_col0[l]) {
       const int slot = (l == 0) ? 0 : 1;
@@ -232,33 +234,45 @@ __global__ void latent_renorm_kernel(float* table, const int64_t* scene_ids, int
 
 // Per-scene aux B rows (fused.cuh): scene_aux[s][slot][o][16] bf16 with
 //   b = bias_l[o] + sum_k Weff_l[o, lat_col0 + k] * z[scene_ids[s]][k]   (fp32, then split hi + lo)
-// at columns 0,1 and 11,12 and the xyz columns of the layer at 2..10.  grid (S, 2), block 512
-__global__ void scene_bias_kernel(const float* __restrict__ table, const int64_t* __restrict__ scene_ids, int L,
-                                  const float* __restrict__ wlatT, const float* __restrict__ bias, const float* __restrict__ wxyz,
-                                  int lat_layer, __nv_bfloat16* __restrict__ scene_aux) {
-  const int s = blockIdx.x, slot = blockIdx.y, o = threadIdx.x;
-  extern __shared__ float z[];
+// at columns 0,1 and 11,12 and the xyz columns of the layer at 2..10.
+// grid (S, 2, 512 / SB_OUT), block (SB_OUT, SB_KS): the K = L sum of an output is cut into SB_KS slices that run side by
+// side (a single thread walking all L latent columns is one long chain of dependent L2 loads: 19-29 us for 8 scenes at
+// L = 256), folded in a fixed order through shared memory.
+constexpr int SB_OUT = 128, SB_KS = 8;
+__global__ void __launch_bounds__(SB_OUT * SB_KS)
+scene_bias_kernel(const float* __restrict__ table, const int64_t* __restrict__ scene_ids, int L,
+                  const float* __restrict__ wlatT, const float* __restrict__ bias, const float* __restrict__ wxyz,
+                  int lat_layer, __nv_bfloat16* __restrict__ scene_aux) {
+  const int s = blockIdx.x, slot = blockIdx.y, o = blockIdx.z * SB_OUT + threadIdx.x, ks = threadIdx.y;
+  extern __shared__ float z[];                     // [L] the scene's code, then [SB_KS][SB_OUT] partial sums
+  float* part = z + ((L + 3) & ~3);
   const float* row = table + size_t(scene_ids[s]) * L;
-  for (int k = threadIdx.x; k < L; k += blockDim.x) z[k] = row[k];
+  const int tid = threadIdx.y * SB_OUT + threadIdx.x;
+  for (int k = tid; k < L; k += SB_OUT * SB_KS) z[k] = row[k];
   __syncthreads();
-  uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
-  if (slot == 0 || lat_layer > 0) {
-    const int l = (slot == 0) ? 0 : lat_layer;
-    // four independent partial sums: the loop is a chain of dependent L2 loads otherwise (19 us for 8 scenes at L = 256)
+  const bool live = (slot == 0 || lat_layer > 0);
+  float acc = 0.f;
+  if (live) {
     const float* wl = wlatT + size_t(slot) * L * FH + o;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    int k = 0;
-    for (; k + 4 <= L; k += 4) {
-      a0 += wl[size_t(k) * FH] * z[k];         a1 += wl[size_t(k + 1) * FH] * z[k + 1];
-      a2 += wl[size_t(k + 2) * FH] * z[k + 2]; a3 += wl[size_t(k + 3) * FH] * z[k + 3];
-    }
-    for (; k < L; ++k) a0 += wl[size_t(k) * FH] * z[k];
-    const float acc = bias[l * FH + o] + ((a0 + a1) + (a2 + a3));
+    const int per = (L + SB_KS - 1) / SB_KS;
+    const int k0 = ks * per, k1 = (k0 + per < L) ? k0 + per : L;
+#pragma unroll 8
+    for (int k = k0; k < k1; ++k) acc += wl[size_t(k) * FH] * z[k];
+  }
+  part[ks * SB_OUT + threadIdx.x] = acc;
+  __syncthreads();
+  if (ks != 0) return;
+  uint32_t w[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+  if (live) {
+    const int l = (slot == 0) ? 0 : lat_layer;
+    float tot = bias[l * FH + o];
+#pragma unroll
+    for (int i = 0; i < SB_KS; ++i) tot += part[i * SB_OUT + threadIdx.x];
     __nv_bfloat16 e[AUX_SCENE_W];
 #pragma unroll
     for (int i = 0; i < AUX_SCENE_W; ++i) e[i] = __float2bfloat16_rn(0.f);
     __nv_bfloat16 hi, lo2;
-    split_bf16(acc, hi, lo2);
+    split_bf16(tot, hi, lo2);
     e[AUX_COL_ONE0] = hi; e[AUX_COL_ONE0 + 1] = lo2; e[AUX_COL_ONE1] = hi; e[AUX_COL_ONE1 + 1] = lo2;
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
@@ -370,7 +384,7 @@ extern "C" int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, f
   if (scene_aux != nullptr) {
     DSDF_REQUIRE((reinterpret_cast<uintptr_t>(scene_aux) & 15) == 0, "scene_aux must be 16-byte aligned");
     DSDF_LAUNCHED;
-    scene_bias_kernel<<<dim3(n_scenes, 2), FH, L * sizeof(float), st>>>(
+    scene_bias_kernel<<<dim3(n_scenes, 2, FH / SB_OUT), dim3(SB_OUT, SB_KS), (((L + 3) & ~3) + SB_KS * SB_OUT) * sizeof(float), st>>>(
         lat_table, scene_ids, L, reinterpret_cast<const float*>(p + lo.off_wlatT), reinterpret_cast<const float*>(p + lo.off_bias),
         reinterpret_cast<const float*>(p + lo.off_wxyz), lo.lat_layer, static_cast<__nv_bfloat16*>(scene_aux));
   }
@@ -424,7 +438,7 @@ static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const
   a.dy_unit = tr->dy_unit;
   a.tile_rows = tr->tile_rows;
   if (row_lat != nullptr) {
-    DSDF_REQUIRE(desc->latent_size <= 4, "row-latent mode supports latent_size <= 4");
+    DSDF_REQUIRE(desc->latent_size <= AUX_MAX_ROW_LAT1, "row-latent mode supports latent_size <= 16");
     DSDF_REQUIRE(row_lat_stride >= desc->latent_size, "row_lat_stride must be >= latent_size");
     a.row_lat = row_lat;
     a.row_lat_stride = row_lat_stride;

@@ -116,11 +116,25 @@ class Decoder(nn.Module):
         return P
 
     # ------------------------------------------------------------------ forward
+    fused_eval = True      # eval-mode forward of fused-class networks with CodeLength <= 16 on the tensor-core chain
+
+    def _fused_rows_supported(self) -> bool:
+        ok = getattr(self, "_fused_rows_ok", None)
+        if ok is None:
+            ok = self.spec.latent_size <= 16 and L.lib().dsdf_fused_supported(C.byref(self._desc)) == 1
+            object.__setattr__(self, "_fused_rows_ok", ok)
+        return ok
+
     def forward(self, input):
         if input.dim() != 2 or input.shape[1] != self.spec.full_dims[0]:
             raise RuntimeError(
                 f"Decoder expects input [N, {self.spec.full_dims[0]}] (latent ++ xyz), got {tuple(input.shape)}")
         L.require_cuda(input, *self.flat_param_list())
+        if not self.training and self.fused_eval and input.shape[0] > 0 and self._fused_rows_supported():
+            # eval-mode boundary call of an 8x512-class network with a short per-row code (CodeLength <= 16): the bf16
+            # tcgen05 chain in row-latent mode instead of the fp32 CUDA-core path (set ``decoder.fused_eval = False`` for
+            # the exact fp32 mode)
+            return _FusedRowsFn.apply(self, input, *self.flat_param_list())
         seed = 0
         if self.training and (self.spec.uses_dropout() or self.spec.latent_dropout):
             # one Philox key per call, drawn from torch's CPU generator -> torch.manual_seed makes runs repeatable.  Only
@@ -145,6 +159,53 @@ class _SecondOrderGuard(torch.autograd.Function):
         raise RuntimeError("deepsdf_b200.Decoder: second-order derivatives (d/dx or d/dparams of dSDF/dinput) are not provided; "
                            "only the first-order double-backward trick of torch.autograd.functional.jvp (deep_sdf/mesh.py:405-422) "
                            "and first-order parameter gradients under create_graph=True are")
+
+
+class _FusedRowsFn(torch.autograd.Function):
+    """Eval-mode ``decoder(input[N, L+3])`` of an 8x512-class network with CodeLength <= 16 on the fused tcgen05 chain in
+    row-latent mode (bf16 operands, fp32 accumulate: SDF within 2e-3 of the fp32 arithmetic).  The input gradient comes from
+    the fused dgrad chain + input-gradient GEMM (one ``G`` per call, also under the double-backward trick of
+    ``torch.autograd.functional.jvp``); parameter gradients - rare in eval mode - are taken from the fp32 generic path."""
+
+    @staticmethod
+    def forward(ctx, module, inp, *params):
+        from ..utils import fused_engine_for
+        eng = fused_engine_for(module)
+        x = inp.detach().to(torch.float32).contiguous()
+        sdf, _ = eng.sdf_and_input_grad_rows(x, with_grad=False)
+        ctx.module = module
+        ctx.save_for_backward(x, *params)
+        ctx.inp_ref = inp if inp.requires_grad else None
+        return sdf.unsqueeze(1)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        from ..utils import fused_engine_for
+        x, *params = ctx.saved_tensors
+        module = ctx.module
+        need_in = ctx.needs_input_grad[1]
+        need_p = any(ctx.needs_input_grad[2:])
+        N = x.shape[0]
+        gin = None
+        deps = [t for t in ([ctx.inp_ref] if ctx.inp_ref is not None else []) + [p for p in params if p.requires_grad]]
+        if need_in:
+            eng = fused_engine_for(module)
+            n_pad = (N + 127) // 128 * 128
+            q = x if n_pad == N else torch.cat([x, x.new_zeros(n_pad - N, x.shape[1])], 0)
+            _, G = eng.sdf_and_input_grad_rows(q)
+            G = G[:N].clone()
+            if torch.is_grad_enabled() and deps:
+                G = _SecondOrderGuard.apply(G, *deps)
+            gin = grad_out * G                      # differentiable w.r.t. grad_out: the jvp trick of deep_sdf/mesh.py:405-422
+        gp = tuple(None for _ in params)
+        if need_p:
+            with torch.enable_grad():
+                ps = [p.detach().requires_grad_(n) for p, n in zip(params, ctx.needs_input_grad[2:])]
+                y = _DecoderFn.apply(module, x, False, 0, *ps)
+                want = [p for p in ps if p.requires_grad]
+                got = iter(torch.autograd.grad(y, want, grad_out.detach()))
+            gp = tuple(next(got) if n else None for n in ctx.needs_input_grad[2:])
+        return (None, gin) + gp
 
 
 class _DecoderFn(torch.autograd.Function):

@@ -225,9 +225,10 @@ int dsdf_fused_finish(const dsdf_net_desc* desc, const void* pack, const dsdf_pa
                       float inv_n, int32_t training, int32_t accumulate, int32_t phases, const dsdf_param_grads* pgrads,
                       float* lat_grad, float* loss_out, void* stream);
 /* Row-latent forward: every row brings its own latent code (queries[r] = [latent(L), xyz(3)], row stride ldq floats) - the
- * microstructure consumers of deep_sdf/mesh.py:457-497, whose codes come from a spline over the domain (L = 1 or 2;
- * supported: L <= 4).  Same kernel and same dsdf_train_io as dsdf_fused_forward; the latent columns of lin0 and of the
- * latent_in layer are applied per row in fp32 like the xyz columns.  Followed by dsdf_fused_dgrad (xyz = queries + L,
+ * microstructure consumers of deep_sdf/mesh.py:457-497, whose codes come from a spline over the domain (L = 1 or 2), and
+ * decoder(input[N, L+3]) calls of the L = 16 experiments; supported: L <= 16.  Same kernel and same dsdf_train_io as
+ * dsdf_fused_forward; the latent columns of lin0 and of the latent_in layer enter through the aux tensor-core step like the
+ * xyz columns (L <= 4: hi/lo-split products, ~16 mantissa bits; 4 < L <= 16: one bf16 term per component).  Followed by dsdf_fused_dgrad (xyz = queries + L,
  * xyz_stride = ldq) and dsdf_fused_input_grad it yields G = dSDF/d[latent, xyz] for per-point codes. */
 int dsdf_fused_forward_rows(const dsdf_net_desc* desc, const void* pack, const float* queries, int32_t ldq, int64_t n_rows,
                             float* sdf_out, const dsdf_train_io* tr, void* stream);

@@ -100,8 +100,12 @@ def test_decode_sdf_matches_reference_semantics():
     with torch.no_grad():
         got = decode_sdf(mod, z.to(DEV), q.to(DEV)).cpu()                          # fused path
         got_none = decode_sdf(mod, None, torch.cat([z.expand(1000, -1), q], 1).to(DEV)).cpu()   # fused row-latent mode (L <= 4)
-        got_generic = mod(torch.cat([z.expand(1000, -1), q], 1).to(DEV)).cpu()                  # the module itself: generic fp32
+        got_module = mod(torch.cat([z.expand(1000, -1), q], 1).to(DEV)).cpu()                   # the module itself, eval mode: fused rows
+        mod.fused_eval = False
+        got_generic = mod(torch.cat([z.expand(1000, -1), q], 1).to(DEV)).cpu()                  # ... pinned to its exact fp32 mode
+        mod.fused_eval = True
     assert got.shape == (1000, 1) and got_none.shape == (1000, 1)
+    assert (got_module - ref).abs().max().item() <= 2e-3
     assert (got - ref).abs().max().item() <= 2e-3
     assert (got_none - ref).abs().max().item() <= 2e-3
     assert (got_generic - ref).abs().max().item() <= 1e-5

@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import decoder_oracle as O
-from tests.util import build_module, load_cases, sdf_scale_params
+from tests.util import build_exact_module as build_module, load_cases, sdf_scale_params
 
 pytestmark = pytest.mark.gpu
 META, BLOB = load_cases()

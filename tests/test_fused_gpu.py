@@ -68,9 +68,27 @@ def test_fused_eval_forward_parity(name):
     assert err.max().item() <= 2e-3                 # north_star tolerance, bf16 operands
     assert d_emu.mean().item() <= 2e-4              # same arithmetic as the CPU emulation up to rounding flips
     # the generic fp32 CUDA path on the same module and inputs agrees with the oracle to fp32 accuracy
+    mod.fused_eval = False
     with torch.no_grad():
         y32 = mod.eval()(inp.to(DEV)).squeeze(1).cpu()
     assert (y32 - ref).abs().max().item() <= 1e-5
+    mod.fused_eval = True
+    if ospec.latent_size <= 16:
+        # the boundary call itself, decoder(input[N, L+3]) in eval mode: tensor-core chain in row-latent mode
+        x = inp.to(DEV).requires_grad_(True)
+        yb = mod(x)
+        (Gb,) = torch.autograd.grad(yb.sum(), x)
+        eb = (yb.detach().squeeze(1).cpu() - ref).abs()
+        G32 = O.input_gradient(ospec, params, inp)
+        cosb = float(torch.nn.functional.cosine_similarity(Gb.cpu().flatten(), G32.flatten(), dim=0))
+        print(f"{name}: decoder(input) on the fused row path: max {eb.max():.2e} mean {eb.mean():.2e}; input-grad cos vs fp32 {cosb:.4f}")
+        assert yb.shape == (inp.shape[0], 1) and eb.max().item() <= 2e-3 and cosb >= 0.98
+        # parameter gradients in this mode come from the fp32 generic path
+        mod.zero_grad()
+        mod(inp.to(DEV)).sum().backward()
+        gref = torch.autograd.grad(O.decoder_forward(ospec, {k: v.clone().requires_grad_(True) for k, v in params.items()}, inp).sum(),
+                                   [], allow_unused=True) if False else None
+        assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in mod.parameters())
 
 
 @pytest.mark.parametrize("name,drop", [("big_8x512_L256", 0.2), ("big_8x512_L2", 0.2), ("big_8x512_L16", 0.0)])

@@ -9,7 +9,7 @@ import torch
 
 from deepsdf_b200 import _lib as L
 from oracle import decoder_oracle as O
-from tests.util import GOLDEN, build_module, load_cases
+from tests.util import GOLDEN, build_exact_module as build_module, load_cases
 
 pytestmark = pytest.mark.gpu
 META, BLOB = load_cases()

@@ -189,7 +189,9 @@ def test_gate_words_are_what_the_stash_and_philox_say():
         assert lost <= 1e-6 * gate.numel() + 1, (l, lost)
         tot += gate.numel()
         if od < 512:     # padded columns of a narrow layer: no gate bits, zero activations
-            assert not (acts[l][:, od:] != 0).any()       # (their gate bits follow the sign of an exact +0: irrelevant, dY is 0 there)
+            # zero activations up to the end of the written accumulator halves (their gate bits follow the sign of an exact +0:
+            # irrelevant, dY is 0 there); columns of a half the layer never produces are never read by wgrad either
+            assert not (acts[l][:, od:256 * ((od + 255) // 256)] != 0).any()
         frac = float(gate.float().mean())
         print(f"layer {l}: open gates {frac:.3f} (keep rate {float(keep.float().mean()):.4f})")
         assert 0.05 < frac < 0.8

@@ -28,6 +28,14 @@ def build_module(kw, params=None, device=None):
     return m
 
 
+def build_exact_module(kw, params=None, device=None):
+    """The drop-in module pinned to its exact fp32 mode: eval-mode forwards of fused-class networks with CodeLength <= 16 stay
+    on the generic CUDA-core path instead of the bf16 tensor-core chain (``Decoder.fused_eval``)."""
+    m = build_module(kw, params, device)
+    m.fused_eval = False
+    return m
+
+
 def sdf_scale_params(ospec, seed, out_scale=0.08):
     """Synthetic parameters whose outputs live on the SDF scale (|sdf| <~ 0.2), like a trained DeepSDF network:
     He-gain hidden layers and a last layer shrunk so that the pre-tanh output has std ~ out_scale."""
