@@ -444,7 +444,7 @@ def run_gpu(args):
         # secondary metrics LAST (driver tails keep the end of the line): sampler, iso-surface, microstructure consumers,
         # config #5, config #3 (latent_opt), config #4 (grid), strong scaling
         "sampler": extras.get("sampler"), "isosurface": extras.get("isosurface"), "microstructure": extras.get("microstructure"),
-        "small_nets": extras.get("small_nets"), "extras_error": extras.get("error"),
+        "small_nets": extras.get("small_nets"), "compat": extras.get("compat"), "extras_error": extras.get("error"),
         "config5": extras.get("config5"), "latent_opt": extras.get("latent_opt"), "grid": extras.get("grid"),
         "strong": strong_obj,
     }
@@ -552,6 +552,88 @@ def run_extras(trainer, dev, rank, world, barrier, max_over_ranks):
         torch.cuda.empty_cache()
     except Exception as exc:  # noqa: BLE001
         out["microstructure"] = {"error": repr(exc)[:200]}
+
+    # the networks the reference's optimisation runs actually use (optimization_runs/*/config.json:8), at the point counts its logs
+    # record: evaluate_network_sdf = tiling transform + SDF + caps + d sdf / d latent for every vertex,
+    # ONE fused fp32 launch of csrc/smallnet.cu instead of the per-(latent, control point) jvp loop
+    try:
+        from deepsdf_b200.mesh import evaluate_network_sdf
+        from deepsdf_b200.networks.deep_sdf_decoder import Decoder as _Dec
+        small = {}
+        for tag, Lz, dims, lat_in, n_v, ref_s in (("4x32_L2", 2, [32] * 4, [2], 316030, "0.90-1.17 s"),
+                                                  ("6x128_L1", 1, [128] * 6, [2], 450241, "0.80-5.8 s")):
+            torch.manual_seed(7)
+            d3 = _Dec(Lz, dims=dims, geom_dimension=3, dropout=list(range(8)), dropout_prob=0.2, norm_layers=list(range(8)),
+                      latent_in=lat_in, weight_norm=True, xyz_in_all=False, use_tanh=False, latent_dropout=False).to(dev).eval()
+            so = (torch.rand(n_v, 3, device=dev) - 0.5) * 2.1
+            lv = torch.randn(n_v, Lz, device=dev) * 0.3
+            capd = {"x0": {"cap": 1, "measure": 0.1}, "x1": {"cap": 1, "measure": 0.1}}
+            evaluate_network_sdf(d3, lv, so, [2, 2, 2], capd, with_grad=True)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(10):
+                evaluate_network_sdf(d3, lv, so, [2, 2, 2], capd, with_grad=True)
+            b.record()
+            torch.cuda.synchronize()
+            ms = a.elapsed_time(b) / 10
+            small[tag] = {"vertices": n_v, "ms": ms, "vertices_per_s": n_v / (ms / 1e3), "reference_log_per_call": ref_s + " (A100, jvp loop)"}
+            del d3, so, lv
+        out["small_nets"] = small
+        torch.cuda.empty_cache()
+    except Exception as exc:  # noqa: BLE001
+        out["small_nets"] = {"error": repr(exc)[:200]}
+
+    # the drop-in module's own boundary call, decoder(input[N, L+3]) (what unchanged reference scripts execute): exact fp32
+    # CUDA-core mode at config #2's network (fwd + bwd with parameter gradients), and the eval-mode tensor-core route (L = 16)
+    try:
+        from deepsdf_b200.networks.deep_sdf_decoder import Decoder as _Dec2
+        comp = {}
+        n_c = 1 << 16
+        torch.manual_seed(9)
+        d4 = _Dec2(256, **SPECS["NetworkSpecs"]).to(dev).train()
+        x4 = torch.cat([torch.randn(n_c, 256, device=dev) / 16, torch.rand(n_c, 3, device=dev) * 2 - 1], 1)
+        for _ in range(2):
+            d4.zero_grad(); d4(x4).sum().backward()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(3):
+            d4.zero_grad(); d4(x4).sum().backward()
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / 3
+        comp["fp32_generic_train_L256"] = {"rows": n_c, "ms_fwd_bwd": ms, "samples_per_s": n_c / (ms / 1e3),
+                                           "what": "Decoder.forward + backward (parameter gradients), fp32 CUDA-core kernels: the exact (1e-5) mode"}
+        del d4, x4
+        d5 = _Dec2(16, **SPECS["NetworkSpecs"]).to(dev).eval()
+        n_e = 1 << 20
+        x5 = torch.cat([torch.randn(n_e, 16, device=dev) / 4, torch.rand(n_e, 3, device=dev) * 2 - 1], 1)
+        with torch.no_grad():
+            d5(x5)
+            torch.cuda.synchronize()
+            a.record()
+            for _ in range(5):
+                d5(x5)
+            b.record()
+            torch.cuda.synchronize()
+            ms_f = a.elapsed_time(b) / 5
+            d5.fused_eval = False
+            d5(x5[:n_c])
+            torch.cuda.synchronize()
+            a.record()
+            d5(x5[:n_c])
+            b.record()
+            torch.cuda.synchronize()
+            ms_g = a.elapsed_time(b)
+        comp["eval_L16"] = {"rows": n_e, "ms_tensor_core_rows_mode": ms_f, "queries_per_s": n_e / (ms_f / 1e3),
+                            "fp32_generic_queries_per_s": n_c / (ms_g / 1e3),
+                            "what": "decoder(input[N, 19]) in eval mode: bf16 tcgen05 chain (row-latent mode) vs the fp32 generic path"}
+        out["compat"] = comp
+        del d5, x5
+        torch.cuda.empty_cache()
+    except Exception as exc:  # noqa: BLE001
+        out["compat"] = {"error": repr(exc)[:200]}
 
     # device-resident dataset + sampler (deep_sdf/data.py:75-110 on the GPU): 64 scenes x 16384 of 100000 stored rows
     from deepsdf_b200.data import DeviceSDFSamples

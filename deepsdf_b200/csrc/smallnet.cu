@@ -135,6 +135,14 @@ struct SmallArgs {
   float* G;                    // [n_rows][ldg] = dSDF / d[latent, xyz], or null
   int64_t ldg;
   int32_t n_tiles;
+  // frozen-decoder latent optimisation (upstream reconstruct.py): one code per `rows_per_latent` consecutive rows taken from
+  // lat_table, and the clamped-L1 seed dL/dsdf = sign(clamp(sdf) - clamp(gt)) * [|sdf| <= clamp] * inv_n instead of 1
+  const float* lat_table;      // [n_rows / rows_per_latent][L], or null
+  int64_t rows_per_latent;
+  const float* gt;             // value of row r at gt[r * gt_stride], or null
+  int64_t gt_stride;
+  float clamp, inv_n;
+  float* row_loss;             // [n_rows] |clamp(sdf) - clamp(gt)|, or null
 };
 
 // acc[8 rows][CPT features] += sum_k A[k][8 rows of this thread] * B[k][tx + 16 j]
@@ -187,7 +195,8 @@ __global__ void __launch_bounds__(SN_THREADS) small_forward_kernel(const __grid_
       const int64_t row = row0 + r;
       float v = 0.f;
       if (row < a.n_rows) {
-        if (a.latent != nullptr) v = (c < L) ? __ldg(a.latent + c) : __ldg(a.queries + row * a.ldq + (c - L));
+        if (a.lat_table != nullptr) v = (c < L) ? __ldg(a.lat_table + (row / a.rows_per_latent) * L + c) : __ldg(a.queries + row * a.ldq + (c - L));
+        else if (a.latent != nullptr) v = (c < L) ? __ldg(a.latent + c) : __ldg(a.queries + row * a.ldq + (c - L));
         else v = __ldg(a.queries + row * a.ldq + c);
       }
       sIn[c * SN_ROWS + r] = v;
@@ -247,6 +256,23 @@ __global__ void __launch_bounds__(SN_THREADS) small_forward_kernel(const __grid_
       if (d.use_tanh) { dt = 1.f - t1 * t1; t1 = tanhf(t1); }      // deep_sdf_decoder.py:94-95 then the final self.th (:108-109)
       dt *= 1.f - t1 * t1;
       if (row0 + tid < a.n_rows) a.sdf_out[row0 + tid] = t1;
+      if (a.gt != nullptr) {
+        // clamped-L1 seed of the latent optimisation (same expression as the fused chain's last epilogue)
+        float diff = 0.f, inside = 1.f;
+        if (row0 + tid < a.n_rows) {
+          const float g = __ldg(a.gt + (row0 + tid) * a.gt_stride);
+          float pc = t1, gc = g;
+          if (a.clamp > 0.f) {
+            pc = fminf(fmaxf(t1, -a.clamp), a.clamp);
+            gc = fminf(fmaxf(g, -a.clamp), a.clamp);
+            inside = (t1 >= -a.clamp && t1 <= a.clamp) ? 1.f : 0.f;
+          }
+          diff = pc - gc;
+          if (a.row_loss != nullptr) a.row_loss[row0 + tid] = fabsf(diff);
+        }
+        const float sgn = (diff > 0.f) ? 1.f : ((diff < 0.f) ? -1.f : 0.f);
+        dt *= sgn * inside * a.inv_n;
+      }
       sY[tid] = dt;
     }
     __syncthreads();               // the last-layer reads of `cur` are done before anybody stages the next tile / seeds dY
@@ -328,6 +354,36 @@ __global__ void __launch_bounds__(SN_THREADS) small_forward_kernel(const __grid_
   }
 }
 
+// Per shape s (rows [s R, s R + R)): lat_grad[s][c] = sum_r G[r][c] + 2 l2reg z[c] / L,  shape_loss[s] = inv_n sum_r row_loss[r]
+// + l2reg mean(z^2).  One block per shape, fixed summation order (thread-strided partial sums, then a shared-memory tree).
+__global__ void __launch_bounds__(256) small_latent_finish_kernel(const float* __restrict__ G, int64_t ldg, const float* __restrict__ row_loss,
+                                                                  const float* __restrict__ lat_table, int L, int64_t R, float inv_n,
+                                                                  float l2reg, float* __restrict__ lat_grad, float* __restrict__ shape_loss) {
+  const int s = blockIdx.x;
+  __shared__ float red[256];
+  const float* z = lat_table + size_t(s) * L;
+  for (int c = 0; c <= L; ++c) {
+    float acc = 0.f;
+    for (int64_t r = threadIdx.x; r < R; r += 256) acc += (c < L) ? G[(int64_t(s) * R + r) * ldg + c] : row_loss[int64_t(s) * R + r];
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+      if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      if (c < L) {
+        lat_grad[size_t(s) * L + c] = red[0] + 2.f * l2reg * z[c] / float(L);
+      } else {
+        float q = 0.f;
+        for (int k = 0; k < L; ++k) q += z[k] * z[k];
+        shape_loss[s] = red[0] * inv_n + l2reg * q / float(L);
+      }
+    }
+    __syncthreads();
+  }
+}
+
 template <int WP>
 size_t small_smem_bytes(int nh) {
   return size_t(2 * WP * SN_PITCH + WP * WP + 2 * SN_MAX_IN * SN_ROWS + SN_ROWS) * 4 + size_t(nh) * WP * 16;
@@ -379,6 +435,44 @@ extern "C" int dsdf_small_pack_weights(const dsdf_net_desc* desc, const dsdf_par
   return 0;
 }
 
+static int small_dispatch(const SmallArgs& a, cudaStream_t st) {
+  switch (a.lo.wp) {
+    case 32: return launch_small<32>(a, st);
+    case 64: return launch_small<64>(a, st);
+    case 96: return launch_small<96>(a, st);
+    case 128: return launch_small<128>(a, st);
+    default: return set_error("small-network kernel: unexpected padded width");
+  }
+}
+
+extern "C" int dsdf_small_latent_step(const dsdf_net_desc* desc, const void* pack, const float* samples, int64_t lds,
+                                      const float* lat_table, int32_t n_shapes, int64_t rows_per_shape, float clamp, float l2reg,
+                                      float* sdf_scratch, float* G_scratch, float* row_loss_scratch, float* lat_grad,
+                                      float* shape_loss, void* stream) {
+  if (int e = require_sm100()) return e;
+  SmallArgs a;
+  memset(&a, 0, sizeof(a));
+  a.desc = *desc;
+  if (int e = small_layout(desc, &a.lo)) return e;
+  DSDF_REQUIRE(desc->geom_dim == 3 && lds >= 4, "dsdf_small_latent_step: samples are [rows][>= 4] (x, y, z, sdf)");
+  DSDF_REQUIRE(n_shapes > 0 && rows_per_shape > 0 && samples && lat_table && sdf_scratch && G_scratch && row_loss_scratch && lat_grad &&
+               shape_loss, "dsdf_small_latent_step: bad arguments");
+  const int L = desc->latent_size;
+  a.pack = static_cast<const float*>(pack);
+  a.queries = samples; a.ldq = lds; a.n_rows = int64_t(n_shapes) * rows_per_shape; a.sdf_out = sdf_scratch;
+  a.G = G_scratch; a.ldg = L + 3;
+  a.lat_table = lat_table; a.rows_per_latent = rows_per_shape;
+  a.gt = samples + 3; a.gt_stride = lds; a.clamp = clamp; a.inv_n = 1.0f / float(rows_per_shape); a.row_loss = row_loss_scratch;
+  a.n_tiles = int((a.n_rows + SN_ROWS - 1) / SN_ROWS);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (int e = small_dispatch(a, st)) return e;
+  DSDF_LAUNCHED;
+  small_latent_finish_kernel<<<n_shapes, 256, 0, st>>>(G_scratch, L + 3, row_loss_scratch, lat_table, L, rows_per_shape, a.inv_n, l2reg,
+                                                       lat_grad, shape_loss);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int dsdf_small_forward(const dsdf_net_desc* desc, const void* pack, const float* queries, int64_t ldq,
                                   const float* latent, int64_t n_rows, float* sdf_out, float* G, int64_t ldg, void* stream) {
   if (int e = require_sm100()) return e;
@@ -393,12 +487,5 @@ extern "C" int dsdf_small_forward(const dsdf_net_desc* desc, const void* pack, c
   a.pack = static_cast<const float*>(pack);
   a.queries = queries; a.ldq = ldq; a.latent = latent; a.n_rows = n_rows; a.sdf_out = sdf_out; a.G = G; a.ldg = ldg;
   a.n_tiles = int((n_rows + SN_ROWS - 1) / SN_ROWS);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  switch (a.lo.wp) {
-    case 32: return launch_small<32>(a, st);
-    case 64: return launch_small<64>(a, st);
-    case 96: return launch_small<96>(a, st);
-    case 128: return launch_small<128>(a, st);
-    default: return set_error("small-network kernel: unexpected padded width");
-  }
+  return small_dispatch(a, static_cast<cudaStream_t>(stream));
 }

@@ -24,9 +24,11 @@ TILE = 128
 class LatentOptimizer:
     def __init__(self, decoder, num_shapes: int, num_samples: int = 8000, clamp_dist: float = 0.1, lr: float = 5e-3,
                  l2reg: bool = True, init_std: float = 0.01, seed: int = 0, init: Optional[torch.Tensor] = None):
-        eng = fused_engine_for(decoder)
+        from .small import small_engine_for
+        self.small = small_engine_for(decoder)            # 4x32 / 4x64 / 6x128: the fused fp32 small-network kernel
+        eng = self.small if self.small is not None else fused_engine_for(decoder)
         if eng is None:
-            raise L.DsdfError("LatentOptimizer needs a decoder supported by the fused path (8x512 class)")
+            raise L.DsdfError("LatentOptimizer needs a decoder of the fused 8x512 class or of the small-network class (hidden width <= 128)")
         self.engine, self.device = eng, eng.device
         self.S, self.num_samples, self.clamp, self.lr0 = num_shapes, num_samples, clamp_dist, lr
         self.l2 = 1e-4 if l2reg else 0.0
@@ -52,12 +54,17 @@ class LatentOptimizer:
     def step(self, samples: torch.Tensor, lr: float) -> torch.Tensor:
         """One Adam iteration on every shape.  ``samples`` [S, num_samples, 4] (x, y, z, sdf) device tensor: this
         iteration's subsample of each shape.  Returns the per-shape losses [S] (device tensor, pre-update)."""
-        self.batch[:, :self.num_samples].copy_(samples)
-        self.engine.latent_loss_and_grad(self.latents, self.scene_ids, self.tile_scene, self.tile_rows,
-                                         self.batch.view(-1, 4), clamp=self.clamp, rows_per_shape=self.num_samples,
-                                         l2reg=self.l2, lat_grad=self.grad, shape_loss=self.shape_loss)
+        from .small import adam_step
+        if self.small is not None:
+            self.small.latent_loss_and_grad(samples.contiguous(), self.latents, clamp=self.clamp, l2reg=self.l2, lat_grad=self.grad,
+                                            shape_loss=self.shape_loss)
+        else:
+            self.batch[:, :self.num_samples].copy_(samples)
+            self.engine.latent_loss_and_grad(self.latents, self.scene_ids, self.tile_scene, self.tile_rows,
+                                             self.batch.view(-1, 4), clamp=self.clamp, rows_per_shape=self.num_samples,
+                                             l2reg=self.l2, lat_grad=self.grad, shape_loss=self.shape_loss)
         self.step_count += 1
-        self.engine.adam(self.latents, self.grad, self.exp_avg, self.exp_avg_sq, self.step_count, lr)
+        adam_step(self.latents, self.grad, self.exp_avg, self.exp_avg_sq, self.step_count, lr)
         return self.shape_loss
 
     def reconstruct(self, data: torch.Tensor, num_iterations: int = 800, sample_idx: Optional[torch.Tensor] = None,

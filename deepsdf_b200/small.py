@@ -82,6 +82,34 @@ class SmallEngine:
                                                 L.stream_ptr(self.device)))
         return sdf, G
 
+    def latent_loss_and_grad(self, samples: torch.Tensor, latents: torch.Tensor, *, clamp: float, l2reg: float,
+                             lat_grad: torch.Tensor, shape_loss: torch.Tensor) -> None:
+        """One iteration of upstream reconstruct.py for every shape: ``samples`` [S, R, 4] (x, y, z, sdf) device tensor,
+        ``latents`` [S, L].  Writes lat_grad [S, L] = d(mean|clamp(pred)-clamp(gt)| + l2reg*mean(z^2))/dz and shape_loss [S]."""
+        L.require_cuda(samples, latents)
+        S, R, w = samples.shape
+        Lz = self.spec.latent_size
+        assert w == 4 and samples.is_contiguous() and samples.dtype == torch.float32 and latents.shape == (S, Lz)
+        key = (S, R)
+        if getattr(self, "_lat_key", None) != key:
+            self._lat_scratch = (torch.empty(S * R, device=self.device), torch.empty(S * R, Lz + 3, device=self.device),
+                                 torch.empty(S * R, device=self.device))
+            self._lat_key = key
+        sdf, G, rl = self._lat_scratch
+        self.repack()
+        with torch.cuda.device(self.device):
+            L.check(self.lib.dsdf_small_latent_step(C.byref(self.desc), self.pack.data_ptr(), samples.data_ptr(), 4, latents.data_ptr(),
+                                                    S, R, float(clamp), float(l2reg), sdf.data_ptr(), G.data_ptr(), rl.data_ptr(),
+                                                    lat_grad.data_ptr(), shape_loss.data_ptr(), L.stream_ptr(self.device)))
+
+
+def adam_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int, lr: float,
+              betas=(0.9, 0.999), eps: float = 1e-8) -> None:
+    """torch.optim.Adam update of one flat fp32 tensor through ``dsdf_adam`` (shared by the engines)."""
+    with torch.cuda.device(p.device):
+        L.check(L.lib().dsdf_adam(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), float(lr), betas[0], betas[1],
+                                  eps, int(step), 1.0, None, L.stream_ptr(p.device)))
+
 
 def small_engine_for(decoder) -> Optional[SmallEngine]:
     """The module's cached SmallEngine, or None if its NetworkSpecs is outside the small-network kernel's class."""

@@ -119,6 +119,14 @@ size_t dsdf_small_pack_bytes(const dsdf_net_desc* desc);
 int dsdf_small_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, void* stream);
 int dsdf_small_forward(const dsdf_net_desc* desc, const void* pack, const float* queries, int64_t ldq, const float* latent,
                        int64_t n_rows, float* sdf_out, float* G, int64_t ldg, void* stream);
+/* One iteration's loss and latent gradient of the frozen-decoder latent optimisation (upstream reconstruct.py) on a small
+ * network: samples [n_shapes * rows_per_shape][lds >= 4] (x, y, z, sdf) shape-major, one code per shape from lat_table
+ * [n_shapes][L];   lat_grad[s] = d/dz ( mean |clamp(pred) - clamp(gt)| + l2reg * mean(z^2) ),  shape_loss[s] = that
+ * expression.  Scratch: sdf [rows], G [rows][L+3], row_loss [rows].  Deterministic (fixed summation order). */
+int dsdf_small_latent_step(const dsdf_net_desc* desc, const void* pack, const float* samples, int64_t lds,
+                           const float* lat_table, int32_t n_shapes, int64_t rows_per_shape, float clamp, float l2reg,
+                           float* sdf_scratch, float* G_scratch, float* row_loss_scratch, float* lat_grad, float* shape_loss,
+                           void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Fused tcgen05 path (hidden width 512, weight-norm or plain layers, one latent_in layer, geom_dim 3).

@@ -168,3 +168,43 @@ def test_consumers_route_small_networks():
         free = ~capped
         _grad_close(dl.cpu()[free], G_ref[free], "evaluate_network")
         assert (dl.cpu()[capped] == 0).all()
+
+
+@pytest.mark.parametrize("name", ["small_4x32_L1", "mid_6x128_L1"])
+def test_latent_optimizer_on_small_networks_tracks_oracle_reconstruct(name):
+    """LatentOptimizer (upstream reconstruct.py, batched over shapes) on the small-network kernel: fp32 arithmetic, so the loss
+    curve follows the oracle's torch loop closely (the clamped-L1 sign gradient still amplifies last-bit differences)."""
+    from deepsdf_b200.reconstruct import LatentOptimizer
+    m, pre, ospec, params, mod, _ = _case(name)
+    Lz = ospec.latent_size
+    rng = np.random.RandomState(21)
+    S, M, ns, iters = 3, 1500, 200, 30            # ragged: 200 rows per shape, shapes not tile aligned
+    z_true = torch.from_numpy(rng.normal(0, 0.5, (S, Lz)).astype(np.float32))
+    xyz = torch.from_numpy(rng.uniform(-1, 1, (S, M, 3)).astype(np.float32))
+    with torch.no_grad():
+        gt = torch.stack([0.2 * O.decode_sdf(ospec, params, z_true[s], xyz[s]).squeeze(1) for s in range(S)])
+    data = torch.cat([xyz, gt.unsqueeze(-1)], -1)
+    idx = torch.from_numpy(rng.randint(0, M, (iters, S, ns)))
+    init = torch.from_numpy(rng.normal(0, 0.01, (S, Lz)).astype(np.float32))
+    opt = LatentOptimizer(mod, S, num_samples=ns, init=init)
+    assert opt.small is not None
+    hist = opt.reconstruct(data.to(DEV), num_iterations=iters, sample_idx=idx, record_every=1)
+    got_loss = torch.stack(hist).cpu()
+    for s in range(S):
+        z = init[s:s + 1].clone().requires_grad_(True)
+        o = torch.optim.Adam([z], lr=5e-3)
+        losses = []
+        for e in range(iters):
+            for pg in o.param_groups:
+                pg["lr"] = 5e-3 * (0.1 ** (e // int(iters / 2)))
+            q, g = xyz[s][idx[e, s]], torch.clamp(gt[s][idx[e, s]].reshape(-1, 1), -0.1, 0.1)
+            o.zero_grad()
+            pred = torch.clamp(O.decoder_forward(ospec, params, torch.cat([z.expand(ns, -1), q], 1)), -0.1, 0.1)
+            loss = (pred - g).abs().mean() + 1e-4 * torch.mean(z.pow(2))
+            loss.backward()
+            o.step()
+            losses.append(float(loss.detach()))
+        ref_loss = torch.tensor(losses)
+        rel = ((got_loss[:, s] - ref_loss).abs() / ref_loss).max().item()
+        print(f"{name} shape {s}: loss {ref_loss[0]:.5f} -> {ref_loss[-1]:.5f}; max rel loss diff {rel:.2e}")
+        assert rel <= 5e-3 and abs(float(got_loss[0, s]) - float(ref_loss[0])) <= 1e-5 * float(ref_loss[0]) + 1e-7
