@@ -87,6 +87,8 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_iso_num_blocks": (i64, [i32, i32, i32]),
         "dsdf_iso_count": (C.c_int, [vp, i32, i32, i32, f32, vp, vp]),
         "dsdf_iso_emit": (C.c_int, [vp, i32, i32, i32, f32, P(f32), P(f32), vp, vp, vp]),
+        "dsdf_adam": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp, vp]),
+        "dsdf_clip_coef": (C.c_int, [vp, i64, f32, vp, vp, vp]),
         "dsdf_selftest_umma_pair": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp]),
         "dsdf_selftest_umma_aux": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, vp]),
         "dsdf_selftest_umma": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint,

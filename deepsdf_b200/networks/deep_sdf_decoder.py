@@ -130,6 +130,10 @@ class Decoder(nn.Module):
             raise RuntimeError(
                 f"Decoder expects input [N, {self.spec.full_dims[0]}] (latent ++ xyz), got {tuple(input.shape)}")
         L.require_cuda(input, *self.flat_param_list())
+        if torch.jit.is_tracing() and not self.training:
+            # torch.jit.trace (create_libtorch_executable.py:19): one registered op instead of an autograd.Function over ctypes
+            from ..torch_op import decoder_eval, encode_spec
+            return decoder_eval(input, list(self.flat_param_list()), encode_spec(self.spec), float(self.spec.dropout_prob))
         if not self.training and self.fused_eval and input.shape[0] > 0 and self._fused_rows_supported():
             # eval-mode boundary call of an 8x512-class network with a short per-row code (CodeLength <= 16): the bf16
             # tcgen05 chain in row-latent mode instead of the fp32 CUDA-core path (set ``decoder.fused_eval = False`` for

@@ -271,3 +271,23 @@ def test_forward_without_dropout_leaves_the_rng_alone():
     mod(x)
     b = torch.rand(3)
     assert torch.equal(a, b)
+
+
+def test_jit_trace_records_the_registered_op(tmp_path):
+    """create_libtorch_executable.py:19-20 on a CUDA example input: torch.jit.trace of the drop-in module records the
+    torch.library op deepsdf_b200::decoder_eval; the traced / scripted / saved + reloaded module reproduces the module."""
+    m, pre, table, rows, xyz, gt = _inputs("small_4x64_L2_tanh")
+    ospec = O.OracleSpec(**m["spec"])
+    params = O.make_params(ospec, m["seed"])
+    mod = build_module(m["spec"], params, DEV).eval()
+    inp = torch.cat([table[rows], xyz], 1).to(DEV)
+    with torch.no_grad():
+        want = mod(inp)
+        traced = torch.jit.trace(mod, inp[:1])
+    assert "deepsdf_b200::decoder_eval" in str(traced.graph)
+    sm = torch.jit.script(traced)
+    fn = str(tmp_path / "cpp_model.pt")
+    sm.save(fn)
+    again = torch.jit.load(fn)
+    with torch.no_grad():
+        assert torch.equal(traced(inp), want) and torch.equal(again(inp), want)
