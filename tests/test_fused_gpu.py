@@ -91,10 +91,13 @@ def test_fused_eval_forward_parity(name):
         assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in mod.parameters())
 
 
-@pytest.mark.parametrize("name,drop", [("big_8x512_L256", 0.2), ("big_8x512_L2", 0.2), ("big_8x512_L16", 0.0)])
-def test_fused_train_step_grads(name, drop):
+@pytest.mark.parametrize("name,drop,tps", [("big_8x512_L256", 0.2, 2), ("big_8x512_L2", 0.2, 2), ("big_8x512_L16", 0.0, 2),
+                                           ("big_8x512_L256", 0.2, 3), ("big_8x512_L2", 0.2, 5)])
+def test_fused_train_step_grads(name, drop, tps):
+    # tps = tiles per scene.  An ODD count (SamplesPerScene 16000 = 125 tiles, config #5) makes CTA pairs straddle two scenes:
+    # the per-scene aux block of a pair is then assembled from both scenes (k-core 0 from rank 0's, k-core 1 from rank 1's)
     kw, ospec, params, mod, eng = _setup(name, p_drop=drop)
-    table, scene_ids, tile_scene, xyz, gt, row_scene = _batch(ospec)
+    table, scene_ids, tile_scene, xyz, gt, row_scene = _batch(ospec, tiles_per_scene=tps)
     N = xyz.shape[0]
     n_total = 2 * N                     # as if another rank held the other half of the global batch
     clampd, lam_eff, bound, seed = 0.1, 1e-4 * 0.37, 1.0, 4242
