@@ -72,6 +72,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_small_forward": (C.c_int, [P(NetDesc), vp, vp, i64, vp, i64, vp, vp, i64, vp]),
         "dsdf_small_latent_step": (C.c_int, [P(NetDesc), vp, vp, i64, vp, i32, i64, f32, f32, vp, vp, vp, vp, vp, vp]),
         "dsdf_fused_supported": (C.c_int, [P(NetDesc)]),
+        "dsdf_fused_rows_supported": (C.c_int, [P(NetDesc)]),
         "dsdf_pack_bytes": (sz, [P(NetDesc)]),
         "dsdf_pack_weights": (C.c_int, [P(NetDesc), P(Params), vp, vp]),
         "dsdf_pack_weights_ex": (C.c_int, [P(NetDesc), P(Params), vp, u32, vp]),

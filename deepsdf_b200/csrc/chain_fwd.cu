@@ -350,12 +350,33 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     const uint32_t one = 0x3F80u;       // bf16 1.0
     const uint32_t one0 = leader ? one : 0u, one1 = leader ? 0u : one;
 
+    const int dense_chunks = args.dense_chunks;
     for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
       const int tile = 2 * tp + int(rank);
       const bool tile_ok = tile < args.n_tiles;
       const int tile_c = tile_ok ? tile : args.n_tiles - 1;
       const bool valid = tile_ok && (int64_t(tile_c) * TILE_M + rt) < args.n_rows &&
                          (args.tile_rows == nullptr || int(rt) < __ldg(args.tile_rows + tile_c));
+      // dense per-row codes: this row's code as bf16 K chunks [chunk0, chunk0 + dense_chunks) of the activation tile
+      // (thread j of the row writes chunks j, j + 4, ...; columns beyond L are zero)
+      auto write_code_chunks = [&](int chunk0) {
+        const float* pl = args.row_lat + (int64_t(tile_c) * TILE_M + rt) * args.row_lat_stride;
+        for (int c = j; c < dense_chunks; c += 4) {
+          const uint32_t line = smem_a + uint32_t(chunk0 + c) * A_CHUNK_BYTES + rt * 128u;
+#pragma unroll
+          for (int p = 0; p < 8; ++p) {
+            float f[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int col = c * 64 + p * 8 + i;
+              f[i] = (valid && col < args.row_lat_dim) ? __ldg(pl + col) : 0.0f;
+            }
+            sts_u32x4(line + ((uint32_t(p) ^ (rt & 7u)) << 4), pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                      pack_bf16x2(f[6], f[7]));
+          }
+        }
+      };
+      if (dense_chunks > 0) write_code_chunks(0);      // lin0's K operand (all earlier MMAs of this pair have completed, see below)
       // ---- aux A block of this tile: k-core j of row rt (every previous MMA of this CTA pair has completed: the last
       //      epilogue of the previous tile waited for its tmem_full)
       {
@@ -373,7 +394,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
             const Tri z = split3(pz);
             w0 = z.h | (z.l << 16); w1 = z.h | (one1 << 16); w2 = one1; w3 = 0u;
           }
-        } else if (row_mode) {
+        } else if (row_mode && dense_chunks == 0) {
           // cols 16 + 3d ..: (hi, lo, hi) of latent component d < 4 -> 12 bf16 over k-cores 2 and 3
           uint32_t e[16];
 #pragma unroll
@@ -482,6 +503,16 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           quarter(3, kwd, nullptr);
         } else {
           if (kTrain && gdst != nullptr) { gdst[size_t(2) * 4 * TILE_M] = 0u; gdst[size_t(3) * 4 * TILE_M] = 0u; }
+          if (dense_chunks > 0 && l + 1 == args.dense_layer) {
+            // the upper half of the tile is free (this layer's MMAs are done: tmem_full[1]; its output fills chunks 0..3 only):
+            // the next layer's latent K chunks go there
+            if (stash) {
+              if ((wany >> 2) & 1u) mbar_wait(&bar_q_stashed[2], ((wpar >> 2) & 1u) ^ 1u);
+              if ((wany >> 3) & 1u) mbar_wait(&bar_q_stashed[3], ((wpar >> 3) & 1u) ^ 1u);
+            }
+            write_code_chunks(4);
+            fence_proxy_async_smem();
+          }
           tc_fence_before();
           __syncwarp();
           if (produce_a && lane == 0) { mbar_arrive_remote(ready_leader + 16u); mbar_arrive_remote(ready_leader + 24u); }

@@ -88,6 +88,11 @@ struct FwdArgs {
   const float* row_lat;                     // row r's code at row_lat + r*row_lat_stride, or null (scene mode)
   int32_t row_lat_stride;
   int32_t row_lat_dim;                      // L
+  // dense per-row codes (L > 16, e.g. 256): the code is a real tensor-core operand - bf16 K chunks of the activation tile:
+  // chunks [0, dense_chunks) for lin0 (the tile is empty there), chunks [4, 4 + dense_chunks) for the latent_in layer
+  // (written by the epilogue of the layer before it, whose single accumulator half leaves them free)
+  int32_t dense_chunks;                     // 0: codes (if any) ride the aux step
+  int32_t dense_layer;                      // the latent_in layer
 };
 
 struct BwdArgs {

@@ -62,8 +62,21 @@ int fused_layout(const dsdf_net_desc* d, FusedLayout* lo) {
     lo->bwd_kchunks[l] = (d->out_dim[l] + 63) / 64;
     if (l > 0) rows_b += lo->bwd_halves[l] * HALF_N;
   }
+  // lin0's dense latent block sits behind the others (scene mode never reads it: lin0 has no K chunks there)
+  lo->fwd_row0[0] = rows_f;
+  rows_f += FH;
   lo->fwd_rows = rows_f;
   lo->bwd_rows = rows_b;
+  lo->dense_lat_chunks = 0;
+  lo->dense_kx = 0;
+  if (lo->lat_layer > 1) {
+    const int xw = lo->xw[lo->lat_layer], xc = (xw + 63) / 64, lc = (L + 63) / 64;
+    // the layer before the latent_in layer must leave the upper half of the activation tile free (one accumulator half)
+    if (L > AUX_MAX_ROW_LAT1 && xc <= 4 && lc <= 4 && lo->fwd_halves[lo->lat_layer - 1] == 1) {
+      lo->dense_lat_chunks = lc;
+      lo->dense_kx = 256;
+    }
+  }
   size_t off = 0;
   lo->off_wp = off;      off = align_up(off + size_t(rows_f) * FH * 2, 1024);
   lo->off_wpt = off;     off = align_up(off + size_t(rows_b) * FH * 2, 1024);
@@ -169,6 +182,11 @@ __global__ void pack_weights_kernel(const __grid_constant__ PackArgs a) {
       const int dlat = k - a.lo.lat_col0[l];
       wlatT[(size_t(slot) * L + dlat) * FH + o] = w;
       wjac[size_t(dlat) * (2 * FH) + slot * FH + o] = __float2bfloat16_rn(w);
+      if (a.lo.dense_lat_chunks > 0 && ev) {
+        // dense per-row codes: the latent columns as tensor-core K columns (eval variant: the mode is eval / gates only)
+        const int kcol = (l == 0 ? 0 : a.lo.dense_kx) + dlat;
+        wp[size_t(a.lo.fwd_row0[l] + o) * FH + kcol] = __float2bfloat16_rn(w);
+      }
       if (L <= AUX_MAX_ROW_LAT) {           // row-latent mode: (w_hi, w_hi, w_lo) meets the A side's (z_hi, z_lo, z_hi)
         __nv_bfloat16 hi, lo2;
         split_bf16(w, hi, lo2);
@@ -319,6 +337,12 @@ using namespace dsdf;
 
 extern "C" int dsdf_fused_supported(const dsdf_net_desc* desc) { return fused_unsupported_reason(desc, nullptr) == 0; }
 
+extern "C" int dsdf_fused_rows_supported(const dsdf_net_desc* desc) {
+  FusedLayout lo;
+  if (fused_unsupported_reason(desc, nullptr) != 0 || fused_layout(desc, &lo) != 0) return 0;
+  return desc->latent_size <= AUX_MAX_ROW_LAT1 || lo.dense_lat_chunks > 0;
+}
+
 extern "C" size_t dsdf_pack_bytes(const dsdf_net_desc* desc) {
   FusedLayout lo;
   if (fused_layout(desc, &lo)) return 0;
@@ -438,11 +462,21 @@ static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const
   a.dy_unit = tr->dy_unit;
   a.tile_rows = tr->tile_rows;
   if (row_lat != nullptr) {
-    DSDF_REQUIRE(desc->latent_size <= AUX_MAX_ROW_LAT1, "row-latent mode supports latent_size <= 16");
+    DSDF_REQUIRE(desc->latent_size <= AUX_MAX_ROW_LAT1 || lo.dense_lat_chunks > 0,
+                 "row-latent mode supports latent_size <= 16, or long codes whose latent_in layer has <= 256 hidden inputs (e.g. L = 256)");
     DSDF_REQUIRE(row_lat_stride >= desc->latent_size, "row_lat_stride must be >= latent_size");
     a.row_lat = row_lat;
     a.row_lat_stride = row_lat_stride;
     a.row_lat_dim = desc->latent_size;
+    if (desc->latent_size > AUX_MAX_ROW_LAT1) {
+      // dense codes: the latent columns are K chunks of lin0 / the latent_in layer (eval-variant pack)
+      DSDF_REQUIRE(!tr_variant, "dense per-row codes run in eval / gates mode only (no dropout)");
+      a.dense_chunks = lo.dense_lat_chunks;
+      a.dense_layer = lo.lat_layer;
+      a.prog[0].k_chunks = lo.dense_lat_chunks;
+      a.prog[lo.lat_layer].k_chunks = lo.dense_kx / 64 + lo.dense_lat_chunks;
+      for (int l = 0; l < lo.num_hidden; ++l) a.aux_steps[l] = 1;
+    }
   } else {
     DSDF_REQUIRE(cbias != nullptr && tile_scene != nullptr, "scene mode needs cbias and tile_scene");
   }

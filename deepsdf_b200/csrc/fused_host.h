@@ -15,6 +15,11 @@ struct FusedLayout {
   int32_t fwd_row0[DSDF_MAX_LAYERS], fwd_halves[DSDF_MAX_LAYERS], fwd_kchunks[DSDF_MAX_LAYERS];
   int32_t bwd_row0[DSDF_MAX_LAYERS], bwd_halves[DSDF_MAX_LAYERS], bwd_kchunks[DSDF_MAX_LAYERS];
   int32_t fwd_rows, bwd_rows;
+  // dense per-row codes (row-latent mode for long codes, e.g. L = 256): lin0's latent columns as a real [512 x Lpad] B block
+  // (rows fwd_row0[0] ..: behind all other layers' blocks of the same array) and the latent_in layer's latent columns
+  // appended to its block at K offset dense_kx; 0 chunks = the network is outside this mode (see fused_layout)
+  int32_t dense_lat_chunks;              // ceil(L / 64), or 0
+  int32_t dense_kx;                      // first K column of the latent part in the latent_in layer's block (64 * ceil(xw / 64))
   size_t off_wp;                         // bf16 [fwd_rows][512]   forward B operand  (rows = out features, K = in)
   size_t off_wpt;                        // bf16 [bwd_rows][512]   dgrad B operand    (rows = in features,  K = out)
   // training variants: the inverted-dropout scale 1/(1 - p_eff) of hidden layer l-1 multiplied into the hidden-activation

@@ -214,7 +214,8 @@ class FusedEngine:
     def sdf_and_input_grad_rows(self, queries: torch.Tensor, G: Optional[torch.Tensor] = None, sdf: Optional[torch.Tensor] = None,
                                 with_grad: bool = True):
         """Eval-mode SDF [N] (and G [N, L+3] = dSDF/d[latent, xyz]) of ``queries`` [N, L+3] whose rows carry their OWN latent
-        code (``decode_sdf(decoder, None, queries)``, deep_sdf/utils.py:62-63 / mesh.py:490-497), L <= 4, N % 128 == 0.
+        code (``decode_sdf(decoder, None, queries)``, deep_sdf/utils.py:62-63 / mesh.py:490-497), N % 128 == 0; supported code lengths: ``dsdf_fused_rows_supported`` (L <= 16,
+        or long codes such as L = 256).
         One ``G`` replaces the per-(latent, control point) jvp loop of mesh.py:405-422: the jvp along a control point is
         ``G[:, i_lat] * basis[:, i_cpt]``."""
         L.require_cuda(queries)

@@ -215,9 +215,10 @@ def evaluate_network_sdf(decoder, lat_vec_red: torch.Tensor, samples_orig: torch
     from .small import small_engine_for
     sm = small_engine_for(decoder)                       # 4x32 / 4x64 / 6x128: the networks the optimisation runs use
     eng = None if sm is not None else fused_engine_for(decoder)
-    if sm is None and (eng is None or eng.spec.latent_size > 4):
+    import ctypes as _C
+    if sm is None and (eng is None or L.lib().dsdf_fused_rows_supported(_C.byref(eng.desc)) != 1):
         raise L.DsdfError("evaluate_network_sdf needs a small-network-class decoder (hidden width <= 128) or an 8x512-class decoder "
-                          "with CodeLength <= 4")
+                          "whose per-row codes the fused row mode supports (CodeLength <= 16, or 256)")
     if (sm or eng).spec.geom_dimension != 3:
         raise L.DsdfError("evaluate_network_sdf works on 3-D samples (geom_dimension 3)")
     dev, Lz = (sm or eng).device, (sm or eng).spec.latent_size

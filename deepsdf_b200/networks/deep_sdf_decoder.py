@@ -121,7 +121,7 @@ class Decoder(nn.Module):
     def _fused_rows_supported(self) -> bool:
         ok = getattr(self, "_fused_rows_ok", None)
         if ok is None:
-            ok = self.spec.latent_size <= 16 and L.lib().dsdf_fused_supported(C.byref(self._desc)) == 1
+            ok = L.lib().dsdf_fused_rows_supported(C.byref(self._desc)) == 1
             object.__setattr__(self, "_fused_rows_ok", ok)
         return ok
 

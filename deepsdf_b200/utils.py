@@ -3,8 +3,8 @@
 ``decode_sdf(decoder, latent_vector, queries)`` keeps the reference's meaning: ``latent_vector`` ([L] or [1, L]) is
 broadcast over ``queries`` [n, 3]; with ``latent_vector=None`` the queries already carry their latent columns
 ([n, L+3]).  For the 8x512-class decoders and a broadcast latent the call runs on the fused tcgen05 forward (the latent
-collapses into one per-scene bias vector, nothing of size [n, L+3] is materialised); per-row codes of length <= 4 (the
-microstructure consumers) run on the same kernel in row-latent mode; the small decoders (hidden width <= 128: 4x32, 4x64,
+collapses into one per-scene bias vector, nothing of size [n, L+3] is materialised); per-row codes (length <= 16: the
+microstructure consumers and the L = 16 experiments; or long codes such as L = 256) run on the same kernel in row-latent mode; the small decoders (hidden width <= 128: 4x32, 4x64,
 6x128) run on the fused fp32 small-network kernel in both forms; everything else (and every differentiable call) goes
 through the module's generic CUDA path.  No CPU path.
 """
@@ -50,7 +50,7 @@ def decode_sdf(decoder, latent_vector, queries):
         # rows carry their own codes (mesh.py:490-497): short codes run on the fused forward in row-latent mode
         dec = decoder.module if isinstance(decoder, torch.nn.DataParallel) else decoder
         plain = not (torch.is_grad_enabled() and queries.requires_grad) and not decoder.training and num_samples > 0
-        if plain and queries.is_cuda and getattr(dec, "latent_size", 99) <= 4:
+        if plain and queries.is_cuda and hasattr(dec, "_desc") and L.lib().dsdf_fused_rows_supported(C.byref(dec._desc)) == 1:
             eng = fused_engine_for(decoder)
             if eng is not None:
                 q = queries.detach().to(eng.device, torch.float32).contiguous()

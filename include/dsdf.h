@@ -160,6 +160,9 @@ typedef struct dsdf_train_io {
 } dsdf_train_io;
 
 int dsdf_fused_supported(const dsdf_net_desc* desc);
+/* 1 if dsdf_fused_forward_rows (per-row latent codes) supports this network: CodeLength <= 16 (codes through the aux step) or a
+ * long code whose latent_in layer has <= 256 hidden inputs, e.g. the original DeepSDF L = 256 (codes as bf16 K chunks) */
+int dsdf_fused_rows_supported(const dsdf_net_desc* desc);
 size_t dsdf_pack_bytes(const dsdf_net_desc* desc);
 int dsdf_pack_weights(const dsdf_net_desc* desc, const dsdf_params* params, void* pack, void* stream);
 /* The same with a choice of what to (re)write.  The big bf16 blocks and w_last exist in two variants: EVAL (plain folded

@@ -73,8 +73,9 @@ def test_fused_eval_forward_parity(name):
         y32 = mod.eval()(inp.to(DEV)).squeeze(1).cpu()
     assert (y32 - ref).abs().max().item() <= 1e-5
     mod.fused_eval = True
-    if ospec.latent_size <= 16:
-        # the boundary call itself, decoder(input[N, L+3]) in eval mode: tensor-core chain in row-latent mode
+    if mod._fused_rows_supported():
+        # the boundary call itself, decoder(input[N, L+3]) in eval mode: tensor-core chain in row-latent mode (L <= 16: codes
+        # through the aux step; L = 256: codes as bf16 K chunks of lin0 / the latent_in layer)
         x = inp.to(DEV).requires_grad_(True)
         yb = mod(x)
         (Gb,) = torch.autograd.grad(yb.sum(), x)
@@ -218,8 +219,15 @@ def test_fused_vs_generic_many_tiles():
     assert torch.equal(a, b2)                                   # run-to-run identical
     row_scene = tile_scene.long().repeat_interleave(128)[:n]
     inp = torch.cat([table[row_scene], xyz], 1).to(DEV)
+    mod.fused_eval = False                                      # the independent fp32 CUDA-core path as the on-device reference
     with torch.no_grad():
         ref = mod.eval()(inp).squeeze(1)
+    mod.fused_eval = True
+    with torch.no_grad():
+        rows = mod(inp).squeeze(1)                              # the same 743 tiles with PER-ROW codes (dense L = 256 row mode)
+    err_r = (rows - ref).abs()
+    print(f"row mode vs generic over {n_tiles} tiles: max {float(err_r.max()):.2e} mean {float(err_r.mean()):.2e}")
+    assert float(err_r.max()) <= 2.5e-3 and float(err_r.mean()) <= 5e-4
     err = (a - ref).abs()
     print(f"fused vs generic over {n_tiles} tiles: max {float(err.max()):.2e} mean {float(err.mean()):.2e}")
     assert float(err.max()) <= 2.5e-3 and float(err.mean()) <= 5e-4
