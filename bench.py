@@ -605,7 +605,31 @@ def run_extras(trainer, dev, rank, world, barrier, max_over_ranks):
         ms = a.elapsed_time(b) / 3
         comp["fp32_generic_train_L256"] = {"rows": n_c, "ms_fwd_bwd": ms, "samples_per_s": n_c / (ms / 1e3),
                                            "what": "Decoder.forward + backward (parameter gradients), fp32 CUDA-core kernels: the exact (1e-5) mode"}
-        del d4, x4
+        del x4
+        d4.eval()
+        n_b = 1 << 19
+        x6 = torch.cat([torch.randn(n_b, 256, device=dev) / 16, torch.rand(n_b, 3, device=dev) * 2 - 1], 1)
+        with torch.no_grad():
+            d4(x6)
+            torch.cuda.synchronize()
+            a.record()
+            for _ in range(5):
+                d4(x6)
+            b.record()
+            torch.cuda.synchronize()
+        ms_b = a.elapsed_time(b) / 5
+        xg = x6.clone().requires_grad_(True)
+        (g6,) = torch.autograd.grad(d4(xg).sum(), xg)
+        torch.cuda.synchronize()
+        a.record()
+        (g6,) = torch.autograd.grad(d4(xg).sum(), xg)
+        b.record()
+        torch.cuda.synchronize()
+        comp["eval_L256"] = {"rows": n_b, "ms_forward": ms_b, "queries_per_s": n_b / (ms_b / 1e3),
+                             "ms_forward_and_input_grad": a.elapsed_time(b),
+                             "what": "decoder(input[N, 259]) in eval mode: per-row codes as bf16 K chunks of the tcgen05 chain; "
+                                     "input.grad from the fused dgrad chain + input-gradient GEMM"}
+        del d4, x6, xg, g6
         d5 = _Dec2(16, **SPECS["NetworkSpecs"]).to(dev).eval()
         n_e = 1 << 20
         x5 = torch.cat([torch.randn(n_e, 16, device=dev) / 4, torch.rand(n_e, 3, device=dev) * 2 - 1], 1)
