@@ -293,38 +293,57 @@ def run_gpu(args):
         trainer.step(dev_batches[i % N_HOST_BATCHES], dev_ids[i % N_HOST_BATCHES], epoch=1, global_rows=global_rows, row0=row0)
     barrier()
 
-    # ---- timed region 1: inputs resident in HBM
+    # ---- region 0 (eager launches, a few steps): per-kernel CUDA events on the launching stream + the eager ms/step
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
+    n_eager = min(args.steps, 10)
     trainer.engine.kernel_events = []
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    launches0 = int(lib.dsdf_launch_count())
+    a0.record()
+    for i in range(n_eager):
+        loss = trainer.step(dev_batches[i % N_HOST_BATCHES], dev_ids[i % N_HOST_BATCHES], epoch=1, global_rows=global_rows,
+                            row0=row0)
+    a1.record()
+    barrier()
+    launches_eager = (int(lib.dsdf_launch_count()) - launches0) // n_eager
+    ms_eager = max_over_ranks(a0.elapsed_time(a1)) / n_eager
+    kev = trainer.engine.kernel_events
+    trainer.engine.kernel_events = None
+
+    # ---- timed region 1: inputs resident in HBM; the step is ONE CUDA-graph replay (SceneTrainer.step_graphed: the same
+    #      kernels, bit-identical results - tests/test_train_features_gpu.py) unless --no-graph
+    graphed = not args.no_graph
+    step_fn = trainer.step_graphed if graphed else trainer.step
+    for i in range(2):
+        step_fn(dev_batches[i % N_HOST_BATCHES], dev_ids[i % N_HOST_BATCHES], epoch=1, global_rows=global_rows, row0=row0)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     launches0 = int(lib.dsdf_launch_count())
     e0.record()
     for i in range(args.steps):
-        loss = trainer.step(dev_batches[i % N_HOST_BATCHES], dev_ids[i % N_HOST_BATCHES], epoch=1, global_rows=global_rows,
-                            row0=row0)
+        loss = step_fn(dev_batches[i % N_HOST_BATCHES], dev_ids[i % N_HOST_BATCHES], epoch=1, global_rows=global_rows, row0=row0)
     e1.record()
     barrier()
-    gpu_launches = int(lib.dsdf_launch_count()) - launches0        # counted by the library at its launch statements
+    # this repo's kernels inside timed region 1: counted by the library at its launch statements (eager) / at capture (graph)
+    gpu_launches = trainer.graph_launches * args.steps if graphed else int(lib.dsdf_launch_count()) - launches0
     ms_total = max_over_ranks(e0.elapsed_time(e1))
-    kev = trainer.engine.kernel_events
-    trainer.engine.kernel_events = None
     ms_step = ms_total / args.steps
     value = global_rows / (ms_step / 1e3)
     loss_dev = [float(x) for x in loss.cpu()]
 
     # ---- timed region 2: end to end from pinned host memory, loss read back every step
     for i in range(2):
-        trainer.step_from_host(host_batches[i], host_ids[i], 1, staging, global_rows=global_rows, row0=row0).cpu()
+        trainer.step_from_host(host_batches[i], host_ids[i], 1, staging, global_rows=global_rows, row0=row0, graphed=graphed).cpu()
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     last = None
     for i in range(args.steps):
         l = trainer.step_from_host(host_batches[i % N_HOST_BATCHES], host_ids[i % N_HOST_BATCHES], 1, staging,
-                                   global_rows=global_rows, row0=row0)
+                                   global_rows=global_rows, row0=row0, graphed=graphed)
         last = l.cpu()                    # device -> host read of the step's loss (synchronises, like .item() at :535)
     e3.record()
     barrier()
@@ -371,12 +390,12 @@ def run_gpu(args):
         n_rows = scenes * SAMPLES_PER_SCENE
         sl = [(b[:n_rows], i[:scenes].contiguous()) for b, i in zip(dev_batches, dev_ids)]
         for k in range(3):
-            trainer.step(sl[k % N_HOST_BATCHES][0], sl[k % N_HOST_BATCHES][1], epoch=1, global_rows=g_rows, row0=r0)
+            step_fn(sl[k % N_HOST_BATCHES][0], sl[k % N_HOST_BATCHES][1], epoch=1, global_rows=g_rows, row0=r0)
         barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         for k in range(steps):
-            trainer.step(sl[k % N_HOST_BATCHES][0], sl[k % N_HOST_BATCHES][1], epoch=1, global_rows=g_rows, row0=r0)
+            step_fn(sl[k % N_HOST_BATCHES][0], sl[k % N_HOST_BATCHES][1], epoch=1, global_rows=g_rows, row0=r0)
         b.record()
         barrier()
         return max_over_ranks(a.elapsed_time(b)) / steps
@@ -436,6 +455,9 @@ def run_gpu(args):
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e},
         "gpu_launches": gpu_launches,         # this repo's kernels inside timed region 1 (dsdf_launch_count; NCCL's are not ours)
+        "launch_mode": {"timed_region": "cuda_graph" if graphed else "eager", "kernels_per_step": gpu_launches // args.steps,
+                        "eager_ms_per_step": ms_eager, "eager_kernels_per_step": launches_eager,
+                        "what": "eager = the same step launched kernel by kernel (region 0, also the source of kernels_ms)"},
         "roofline": roofline,
         "cpu_baseline": cpu,
         "clocks": clk,
@@ -779,6 +801,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch the timed steps kernel by kernel instead of replaying the captured CUDA graph")
     ap.add_argument("--no-extras", action="store_true", help="skip the grid / latent-optimisation secondary metrics")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: 64 scenes per GPU per step (default, the driver's SCALE runs); strong: the fixed 64-scene batch split "

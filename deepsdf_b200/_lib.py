@@ -40,7 +40,7 @@ class TrainIO(C.Structure):
         ("b_last", C.c_void_p), ("training", C.c_int32), ("seed", C.c_uint64), ("row0", C.c_uint64),
         ("gt", C.c_void_p), ("gt_stride", C.c_int32), ("clamp", C.c_float), ("inv_n", C.c_float), ("dy_out", C.c_void_p),
         ("tile_loss", C.c_void_p), ("bitmask", C.c_void_p), ("acts", C.c_void_p), ("n_rows_pad", C.c_int64),
-        ("dropout_off", C.c_int32), ("dy_unit", C.c_int32), ("tile_rows", C.c_void_p),
+        ("dropout_off", C.c_int32), ("dy_unit", C.c_int32), ("tile_rows", C.c_void_p), ("step_state", C.c_void_p),
     ]
 
 
@@ -90,6 +90,9 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_iso_emit": (C.c_int, [vp, i32, i32, i32, f32, P(f32), P(f32), vp, vp, vp]),
         "dsdf_adam": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp, vp]),
         "dsdf_clip_coef": (C.c_int, [vp, i64, f32, vp, vp, vp]),
+        "dsdf_adam_state": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, vp, f32, vp, vp]),
+        "dsdf_step_advance": (C.c_int, [vp, f32, f32, vp]),
+        "dsdf_step_set": (C.c_int, [vp, u32, vp]),
         "dsdf_selftest_umma_pair": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp]),
         "dsdf_selftest_umma_aux": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, vp]),
         "dsdf_selftest_umma": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint,

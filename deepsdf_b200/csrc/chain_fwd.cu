@@ -351,6 +351,8 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
     const uint32_t one0 = leader ? one : 0u, one1 = leader ? 0u : one;
 
     const int dense_chunks = args.dense_chunks;
+    // per-step dropout streams without per-step kernel parameters: the optimiser step counter lives in device memory
+    const uint64_t step_key = (kTrain && args.step_dev != nullptr) ? (uint64_t(__ldg(args.step_dev)) << 40) : 0ull;
     for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
       const int tile = 2 * tp + int(rank);
       const bool tile_ok = tile < args.n_tiles;
@@ -439,7 +441,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         const bool produce_a = !last;
         const bool drop = kTrain && L.dropout != 0 && args.dropout_on != 0;
         // ---- before the accumulators are ready: draw the first keep words
-        const uint64_t grow = args.row0 + uint64_t(int64_t(tile_c) * TILE_M + rt);
+        const uint64_t grow = args.row0 + step_key + uint64_t(int64_t(tile_c) * TILE_M + rt);
         // all four keep words of the layer now: the warps idle here anyway (the tensor cores are still on half 0), and later
         // every cycle between tmem_full[1] and the last a_ready arrive is on the critical path of the next layer
         uint32_t kwa = 0xFFFFFFFFu, kwb = 0xFFFFFFFFu, kwc = 0xFFFFFFFFu, kwd = 0xFFFFFFFFu;

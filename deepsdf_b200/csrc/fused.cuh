@@ -72,6 +72,7 @@ struct FwdArgs {
   uint32_t drop_thr;
   uint64_t seed;
   uint64_t row0;                            // global row id of local row 0 (dropout stream is keyed by global rows)
+  const uint32_t* step_dev;                 // device step counter or null: rows are keyed row0 + (step << 40) + r
   const float* gt;                          // [N] or null
   float clamp;                              // ClampingDistance (<=0: no clamp)
   float inv_n;                              // 1 / N_total (global batch)

@@ -451,6 +451,7 @@ static int fused_forward_impl(const dsdf_net_desc* desc, const void* pack, const
   a.seed = tr->seed;
   philox_round_keys(tr->seed, a.philox_rk);
   a.row0 = tr->row0;
+  a.step_dev = tr->step_state ? &tr->step_state->step : nullptr;
   a.gt = tr->gt;
   a.clamp = tr->clamp;
   a.inv_n = tr->inv_n;

@@ -252,6 +252,36 @@ extern "C" int dsdf_adam(float* p, const float* g, float* m, float* v, int64_t n
   return 0;
 }
 
+extern "C" int dsdf_adam_state(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
+                               const dsdf_step_state* state, float grad_scale, const float* grad_scale_dev, void* stream) {
+  if (int e = require_sm100()) return e;
+  if (n <= 0) return 0;
+  DSDF_REQUIRE(state != nullptr, "dsdf_adam_state needs the device step state");
+  DSDF_LAUNCHED;
+  adam_state_kernel<<<unsigned((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, g, m, v, n, lr, beta1, beta2, eps, state,
+                                                                                             grad_scale, grad_scale_dev);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dsdf_step_advance(dsdf_step_state* state, float beta1, float beta2, void* stream) {
+  if (int e = require_sm100()) return e;
+  DSDF_REQUIRE(state != nullptr, "dsdf_step_advance: null state");
+  DSDF_LAUNCHED;
+  step_advance_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state, double(beta1), double(beta2), 0, 0u);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dsdf_step_set(dsdf_step_state* state, uint32_t step, void* stream) {
+  if (int e = require_sm100()) return e;
+  DSDF_REQUIRE(state != nullptr, "dsdf_step_set: null state");
+  DSDF_LAUNCHED;
+  step_advance_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(state, 0.9, 0.999, 1, step);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int dsdf_clip_coef(const float* g, int64_t n, float max_norm, float* scratch, float* out, void* stream) {
   if (int e = require_sm100()) return e;
   DSDF_REQUIRE(n > 0 && g && scratch && out, "dsdf_clip_coef: bad arguments");

@@ -225,6 +225,30 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
   p[i] -= (lr / bc1) * (mi / denom);
 }
 
+// the same update with the bias corrections taken from the device-resident step state (CUDA-graph replayable)
+__global__ void adam_state_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n,
+                                  float lr, float beta1, float beta2, float eps, const dsdf_step_state* __restrict__ state, float grad_scale,
+                                  const float* __restrict__ grad_scale_dev) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float bc1 = state->bc1, bc2_sqrt = state->bc2_sqrt;
+  if (grad_scale_dev != nullptr) grad_scale *= __ldg(grad_scale_dev);
+  const float gi = g[i] * grad_scale;
+  const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+  const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+  m[i] = mi;
+  v[i] = vi;
+  const float denom = sqrtf(vi) / bc2_sqrt + eps;
+  p[i] -= (lr / bc1) * (mi / denom);
+}
+
+__global__ void step_advance_kernel(dsdf_step_state* state, double beta1, double beta2, int set, uint32_t value) {
+  const uint32_t s = set ? value : state->step + 1u;
+  state->step = s;
+  state->bc1 = float(1.0 - pow(beta1, double(s)));
+  state->bc2_sqrt = sqrtf(float(1.0 - pow(beta2, double(s))));
+}
+
 // ||g||^2 in two deterministic stages: 1024 blocks of fixed element ranges, then one block.
 __global__ void __launch_bounds__(256) sumsq_partial_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ part) {
   __shared__ float red[256];

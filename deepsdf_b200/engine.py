@@ -341,7 +341,8 @@ class FusedEngine:
                        gt: torch.Tensor, *, clamp: float, reg_lambda_eff: float, n_total: int, code_bound: Optional[float],
                        seed: int, row0: int, PG: L.ParamGrads, lat_grad: torch.Tensor, training: bool = True,
                        point_stride: int = 3, gt_stride: int = 1, n_rows: Optional[int] = None, accumulate: bool = False,
-                       scene_capacity: int = 0, side_stream: Optional[torch.cuda.Stream] = None, after_scene=None) -> torch.Tensor:
+                       scene_capacity: int = 0, side_stream: Optional[torch.cuda.Stream] = None, after_scene=None,
+                       step_state: Optional[torch.Tensor] = None) -> torch.Tensor:
         """train_deep_sdf.py:483-533 for one (local) batch: returns the 2-element loss tensor (total, data term); fills
         the decoder gradients behind ``PG`` and the dense latent gradient ``lat_grad`` [S_total, L] (``accumulate``: adds to
         them and to the loss instead - one chunk of ``--batch_split``).
@@ -362,6 +363,7 @@ class FusedEngine:
         io.dropout_off = int(not training)           # training=False: the same step with dropout disabled
         io.seed = seed
         io.row0 = row0
+        io.step_state = step_state.data_ptr() if step_state is not None else None     # dropout keyed by the device step counter
         io.gt = gt.data_ptr()
         io.gt_stride = gt_stride
         io.clamp = float(clamp or 0.0)
@@ -421,8 +423,16 @@ class FusedEngine:
         return b["loss"]
 
     def adam(self, p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int, lr: float,
-             grad_scale: float = 1.0, betas=(0.9, 0.999), eps: float = 1e-8, scale_dev: Optional[torch.Tensor] = None) -> None:
-        """torch.optim.Adam update (train_deep_sdf.py:400-411,545) of one flat fp32 tensor."""
+             grad_scale: float = 1.0, betas=(0.9, 0.999), eps: float = 1e-8, scale_dev: Optional[torch.Tensor] = None,
+             step_state: Optional[torch.Tensor] = None) -> None:
+        """torch.optim.Adam update (train_deep_sdf.py:400-411,545) of one flat fp32 tensor.  With ``step_state`` the bias
+        corrections come from the device-resident step counter (``dsdf_step_advance``): replayable inside a CUDA graph."""
+        if step_state is not None:
+            with torch.cuda.device(self.device):
+                L.check(self.lib.dsdf_adam_state(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), float(lr), betas[0],
+                                                 betas[1], eps, step_state.data_ptr(), float(grad_scale),
+                                                 scale_dev.data_ptr() if scale_dev is not None else None, self._st()))
+            return
         with torch.cuda.device(self.device):
             L.check(self.lib.dsdf_adam(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), float(lr), betas[0], betas[1],
                                        eps, int(step), float(grad_scale), scale_dev.data_ptr() if scale_dev is not None else None,

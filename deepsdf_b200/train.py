@@ -116,7 +116,7 @@ def load_adam_state_dict(trainer: SceneTrainer, sd: dict, lat_rows: range) -> No
         trainer.lat_exp_avg.copy_(st[ids1[0]]["exp_avg"][lat_rows.start:lat_rows.stop])
         trainer.lat_exp_avg_sq.copy_(st[ids1[0]]["exp_avg_sq"][lat_rows.start:lat_rows.stop])
         steps.append(int(float(st[ids1[0]]["step"])))
-    trainer.step_count = max(steps) if steps else 0
+    trainer.set_step(max(steps) if steps else 0)
 
 
 def save_checkpoint(exp: str, name: str, trainer: SceneTrainer, all_latents: torch.Tensor, all_lat_m: torch.Tensor,
@@ -154,7 +154,8 @@ def load_checkpoint(exp: str, name: str, trainer: SceneTrainer, lat_rows: range)
 
 
 def main_function(experiment_directory: str, data_source: str = None, max_epochs: int = None,
-                  strict_shuffle: bool = None, backend: str = "nccl", continue_from: str = None, batch_split: int = 1) -> dict:
+                  strict_shuffle: bool = None, backend: str = "nccl", continue_from: str = None, batch_split: int = 1,
+                  cuda_graph: bool = False) -> dict:
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -205,6 +206,7 @@ def main_function(experiment_directory: str, data_source: str = None, max_epochs
         start_epoch = saved + 1
     logging.info("starting from epoch {}".format(start_epoch))
     trainer.batch_split = int(batch_split)
+    trainer.use_graph = bool(cuda_graph)          # partition mode, batch_split 1: every iteration is one CUDA-graph replay
     gen = torch.Generator()
     shuffle_seed = 1234 + (0 if strict_shuffle else rank)
     its = num_scenes // spb if strict_shuffle else len(dataset) // spb_local
@@ -267,5 +269,9 @@ if __name__ == "__main__":
     ap.add_argument("--batch_split", dest="batch_split", type=int, default=1,
                     help="split each batch into this many chunks whose gradients are accumulated (train_deep_sdf.py:602-609): "
                          "the activation stash shrinks accordingly")
+    ap.add_argument("--cuda-graph", action="store_true",
+                    help="capture the optimiser step once per epoch-dependent setting and replay it (SceneTrainer.step_graphed): "
+                         "same results bit for bit, no per-kernel launch gaps")
     a = ap.parse_args()
-    main_function(a.experiment_directory, a.data_source, a.max_epochs, a.strict_shuffle, a.backend, a.continue_from, a.batch_split)
+    main_function(a.experiment_directory, a.data_source, a.max_epochs, a.strict_shuffle, a.backend, a.continue_from, a.batch_split,
+                  a.cuda_graph)

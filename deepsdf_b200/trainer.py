@@ -128,6 +128,11 @@ class SceneTrainer:
         self.code_reg_lambda = get_spec_with_default(specs, "CodeRegularizationLambda", 1e-4)
         self.grad_clip = get_spec_with_default(specs, "GradientClipNorm", None)
         self.step_count = 0
+        # device-resident step state (include/dsdf.h dsdf_step_state): optimiser step counter + Adam bias corrections.  The
+        # dropout stream and both Adam updates read it from memory, so a step has no per-step kernel parameter and can be
+        # replayed as one CUDA graph (step_graphed)
+        self.step_state = torch.zeros(16, dtype=torch.int32, device=self.device)
+        self.use_graph = False        # train_epoch replays the captured step (step_graphed) instead of launching it kernel by kernel
         self.batch_split = 1          # --batch_split (train_deep_sdf.py:602-609): chunks per batch, gradients accumulated
         self.seed = seed
         self._clip_scratch = torch.zeros(1024, device=self.device)
@@ -150,6 +155,17 @@ class SceneTrainer:
             t = torch.arange(n_scenes, dtype=torch.int32, device=self.device).repeat_interleave(samples_per_scene // TILE)
             self._tile_scene_cache[key] = t.contiguous()
         return self._tile_scene_cache[key]
+
+    def dropout_key(self) -> int:
+        """Philox key of this trainer's dropout streams.  Row r of optimiser step s draws from counter row0 + (s << 40) + r
+        (``dsdf_dropout_mask(key, layer, row0 + (s << 40), ...)`` reproduces the masks of step s)."""
+        return (self.seed * 0x9E3779B1 + 0x51ED27) & 0x3FFFFFFFFFFFFFFF
+
+    def set_step(self, step: int) -> None:
+        """Resume: host and device step counters (checkpoint loading)."""
+        self.step_count = int(step)
+        with torch.cuda.device(self.device):
+            L.check(self.engine.lib.dsdf_step_set(self.step_state.data_ptr(), int(step), L.stream_ptr(self.device)))
 
     def learning_rates(self, epoch: int):
         return [s.get_learning_rate(epoch) for s in self.lr_schedules]                  # :315-318
@@ -177,7 +193,9 @@ class SceneTrainer:
         if self.do_code_reg:
             lam = self.code_reg_lambda * min(1.0, epoch / 100.0)                        # :523-529
         self.step_count += 1
-        seed = (self.seed * 0x9E3779B1 + self.step_count) & 0x3FFFFFFFFFFFFFFF
+        with torch.cuda.device(self.device):
+            L.check(eng.lib.dsdf_step_advance(self.step_state.data_ptr(), 0.9, 0.999, L.stream_ptr(self.device)))
+        seed = self.dropout_key()               # constant Philox key; the step enters through the row counter (step << 40)
         flat = samples.view(-1)
         code_bound = self.code_bound
         shared_lat = self.replicated and self.world_size > 1
@@ -198,7 +216,7 @@ class SceneTrainer:
             loss = eng.loss_and_grads(self.lat_vecs, scene_ids, tile_scene, flat, flat[3:], clamp=clamp,
                                       reg_lambda_eff=lam, n_total=n_total, code_bound=code_bound, seed=seed,
                                       row0=row0, PG=self.PG, lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
-                                      n_rows=N, side_stream=self.side_stream)
+                                      n_rows=N, side_stream=self.side_stream, step_state=self.step_state)
         else:
             # train_deep_sdf.py:495-535: the batch in `batch_split` row chunks (torch.chunk sizes: ceil(rows / k), here in whole
             # 128-row tiles), every chunk's loss divided by the WHOLE batch's row count (:519), gradients accumulated, one
@@ -220,7 +238,7 @@ class SceneTrainer:
                 loss = eng.loss_and_grads(self.lat_vecs, scene_ids[s0:s1], ts, part, part[3:], clamp=clamp, reg_lambda_eff=lam,
                                           n_total=n_total, code_bound=code_bound, seed=seed, row0=row0 + t0 * TILE, PG=self.PG,
                                           lat_grad=self.lat_grad, training=True, point_stride=4, gt_stride=4,
-                                          n_rows=(t1 - t0) * TILE, accumulate=c > 0, scene_capacity=S)
+                                          n_rows=(t1 - t0) * TILE, accumulate=c > 0, scene_capacity=S, step_state=self.step_state)
         # the one exchange of the step: all-reduce (sum) of the flat decoder gradient (strict mode: + the dense latent gradient
         # behind it in the same buffer).  Replaces nn.DataParallel's gradient reduction (train_deep_sdf.py:353).
         work = None
@@ -231,27 +249,95 @@ class SceneTrainer:
             if shared_lat:                               # the latent gradient is part of the exchange
                 work.wait()
                 work = None
-            eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat)
+            eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat, step_state=self.step_state)
         if work is not None:
             work.wait()
         scale_dev = None
         if self.grad_clip is not None:                                                  # :541-543 (decoder only)
             eng.clip_coef(self.flat_g, self.grad_clip, self._clip_scratch, self._clip_out)
             scale_dev = self._clip_out[1:2]
-        eng.adam(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.step_count, lr_dec, scale_dev=scale_dev)
+        eng.adam(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.step_count, lr_dec, scale_dev=scale_dev,
+                 step_state=self.step_state)
         # the kernel wrote the parameters behind torch's version counters: cached packs of other engines key on this
         object.__setattr__(self.decoder, "_param_epoch", getattr(self.decoder, "_param_epoch", 0) + 1)
         eng.repack(train_only=True)      # the training variants only; an eval-mode call on this engine rebuilds the others
         return loss
 
+    # ------------------------------------------------------------------ the same step as ONE CUDA graph
+    def step_graphed(self, samples: torch.Tensor, scene_ids: torch.Tensor, epoch: int, global_rows: Optional[int] = None,
+                     row0: int = 0) -> torch.Tensor:
+        """``step`` replayed from a captured CUDA graph (partition mode, batch_split 1): ~20 kernel launches, the side-stream
+        fork / join and the NCCL all-reduce become one graph launch, which removes the launch gaps that matter once a rank's
+        share of the batch is small (strong scaling).  Nothing in the step depends on a per-step kernel PARAMETER (dropout
+        stream and Adam bias corrections read the device step state), so a replay is a full optimiser step.  The graph is
+        re-captured when the shapes or an epoch-dependent scalar (learning rates, regulariser ramp) change.  ``samples`` /
+        ``scene_ids`` are copied into the graph's static input buffers (or ARE them: ``graph_inputs``).  Returns the static
+        loss tensor [2] (overwritten by the next replay)."""
+        if (self.replicated and self.world_size > 1) or self.batch_split != 1:
+            return self.step(samples, scene_ids, epoch, global_rows=global_rows, row0=row0)
+        S, N = scene_ids.numel(), samples.shape[0]
+        lam = self.code_reg_lambda * min(1.0, epoch / 100.0) if self.do_code_reg else 0.0
+        key = (N, S, global_rows, row0, lam, tuple(self.learning_rates(epoch)))
+        if getattr(self, "_graph_key", None) != key:
+            self._capture(key, samples, scene_ids, epoch, global_rows, row0)
+        g_s, g_i = self._graph_in
+        if samples.data_ptr() != g_s.data_ptr():
+            g_s.copy_(samples, non_blocking=True)
+        if scene_ids.data_ptr() != g_i.data_ptr():
+            g_i.copy_(scene_ids, non_blocking=True)
+        self._graph.replay()
+        self.step_count += 1
+        object.__setattr__(self.decoder, "_param_epoch", getattr(self.decoder, "_param_epoch", 0) + 1)
+        return self._graph_loss
+
+    def graph_inputs(self, n_rows: int, n_scenes: int):
+        """Static input buffers (samples [n_rows, 4], scene_ids [n_scenes]) a caller may fill directly (e.g. the H2D copy of
+        the next batch) before ``step_graphed`` - no device-to-device copy then."""
+        gi = getattr(self, "_graph_in", None)
+        if gi is None or gi[0].shape[0] != n_rows or gi[1].numel() != n_scenes:
+            self._graph_in = (torch.empty(n_rows, 4, device=self.device), torch.zeros(n_scenes, dtype=torch.int64, device=self.device))
+            self._graph_key = None
+        return self._graph_in
+
+    def _capture(self, key, samples, scene_ids, epoch, global_rows, row0) -> None:
+        g_s, g_i = self.graph_inputs(samples.shape[0], scene_ids.numel())
+        g_s.copy_(samples)
+        g_i.copy_(scene_ids)
+        # warm-up step on the real inputs (lazy allocations, kernel attributes, NCCL communicator), then put the state back
+        saved = [t.clone() for t in (self.flat_p, self.exp_avg, self.exp_avg_sq, self.lat_vecs, self.lat_exp_avg, self.lat_exp_avg_sq,
+                                     self.step_state)]
+        count = self.step_count
+        cap_stream = torch.cuda.Stream(device=self.device)
+        cap_stream.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(cap_stream):
+            self.step(g_s, g_i, epoch, global_rows=global_rows, row0=row0)
+        torch.cuda.current_stream(self.device).wait_stream(cap_stream)
+        torch.cuda.synchronize(self.device)
+        for t, s in zip((self.flat_p, self.exp_avg, self.exp_avg_sq, self.lat_vecs, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_state),
+                        saved):
+            t.copy_(s)
+        self.step_count = count
+        self.engine.repack(train_only=True)
+        n0 = int(self.engine.lib.dsdf_launch_count())
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._graph_loss = self.step(g_s, g_i, epoch, global_rows=global_rows, row0=row0)
+        self.graph_launches = int(self.engine.lib.dsdf_launch_count()) - n0      # this repo's kernels inside one replay
+        self.step_count = count                                                  # capture executes nothing
+        self._graph_key = key
+
     def step_from_host(self, samples_host: torch.Tensor, scene_ids_host: torch.Tensor, epoch: int, staging: Dict,
-                       global_rows: Optional[int] = None, row0: int = 0) -> torch.Tensor:
+                       global_rows: Optional[int] = None, row0: int = 0, graphed: bool = False) -> torch.Tensor:
         """The call a user of the reference's DataLoader makes: pinned host samples in, device loss out.  ``staging`` holds
-        the reusable device buffers ("samples", "scene_ids")."""
-        d_s, d_i = staging["samples"], staging["scene_ids"]
+        the reusable device buffers ("samples", "scene_ids"); ``graphed``: the H2D copies land in the captured step's static
+        input buffers and the step is one graph replay (``step_graphed``)."""
+        if graphed:
+            d_s, d_i = self.graph_inputs(samples_host.shape[0], scene_ids_host.numel())
+        else:
+            d_s, d_i = staging["samples"], staging["scene_ids"]
         d_s.copy_(samples_host, non_blocking=True)
         d_i.copy_(scene_ids_host, non_blocking=True)
-        return self.step(d_s, d_i, epoch, global_rows=global_rows, row0=row0)
+        return (self.step_graphed if graphed else self.step)(d_s, d_i, epoch, global_rows=global_rows, row0=row0)
 
     def train_epoch(self, dataset, epoch: int, scenes_per_batch: Optional[int] = None, generator=None,
                     max_iterations: Optional[int] = None, global_rows: Optional[int] = None, row0: int = 0) -> List[torch.Tensor]:
@@ -280,7 +366,7 @@ class SceneTrainer:
                 sps = buf.shape[0] // share
                 loss = self.step(buf, mine, epoch, global_rows=spb * sps, row0=self.rank * share * sps, batch_scene_ids=ids_d)
             else:
-                loss = self.step(buf, mine, epoch, global_rows=global_rows, row0=row0)
+                loss = (self.step_graphed if self.use_graph else self.step)(buf, mine, epoch, global_rows=global_rows, row0=row0)
             losses.append(loss.clone())
         return losses
 

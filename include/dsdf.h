@@ -69,6 +69,18 @@ typedef struct dsdf_param_grads {      /* same shapes as dsdf_params; written (n
   float* ln_b[DSDF_MAX_LAYERS];
 } dsdf_param_grads;
 
+/* Device-resident per-step scalars (64 bytes, caller-allocated device memory): what changes from one optimiser step to the next.
+ * Kernels read them from memory instead of from their parameters, which makes the whole training step replayable as one CUDA
+ * graph.  dsdf_step_advance: step += 1 and Adam's bias corrections bc1 = 1 - beta1^step, bc2_sqrt = sqrt(1 - beta2^step)
+ * (computed in double, like torch.optim.Adam's host arithmetic).  dsdf_step_set: set the counter (resume from a checkpoint). */
+typedef struct dsdf_step_state {
+  uint32_t step;
+  float bc1, bc2_sqrt;
+  uint32_t reserved[13];
+} dsdf_step_state;
+int dsdf_step_advance(dsdf_step_state* state, float beta1, float beta2, void* stream);
+int dsdf_step_set(dsdf_step_state* state, uint32_t step, void* stream);
+
 int dsdf_abi_version(void);
 const char* dsdf_last_error(void);
 /* 0 if the current CUDA device is sm_100; error otherwise (used by the Python side to fail loudly). */
@@ -157,6 +169,9 @@ typedef struct dsdf_train_io {
                               (what the input-gradient path and the frozen-decoder latent optimisation need) */
   int32_t dy_unit;         /* gt == NULL: dy_out = d sdf / d(pre-tanh output), the seed of the input gradient */
   const int32_t* tile_rows;/* [n_tiles] valid rows per 128-row tile (ragged scenes padded to tiles), or NULL = all */
+  const struct dsdf_step_state* step_state;   /* device-resident optimiser step counter, or NULL: the dropout stream of row r is then
+                              keyed by row0 + (step << 40) + r, so that a step captured in a CUDA graph draws fresh masks at
+                              every replay without a single changed kernel parameter */
 } dsdf_train_io;
 
 int dsdf_fused_supported(const dsdf_net_desc* desc);
@@ -313,6 +328,9 @@ int dsdf_iso_emit(const float* volume, int32_t nx, int32_t ny, int32_t nz, float
  * host round trip). */
 int dsdf_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
               int32_t step, float grad_scale, const float* grad_scale_dev, void* stream);
+/* the same update with the bias corrections read from the device-resident step state: replayable inside a CUDA graph */
+int dsdf_adam_state(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
+                    const dsdf_step_state* state, float grad_scale, const float* grad_scale_dev, void* stream);
 /* torch.nn.utils.clip_grad_norm_ (train_deep_sdf.py:541-543) over one flat fp32 gradient: out[0] = ||g||_2,
  * out[1] = min(1, max_norm / (||g||_2 + 1e-6)).  Deterministic two-stage reduction; `scratch` holds 1024 floats. */
 int dsdf_clip_coef(const float* g, int64_t n, float max_norm, float* scratch, float* out, void* stream);

@@ -53,11 +53,11 @@ def test_loss_curve_50_epochs_within_one_percent():
         n = batch.shape[0]
         loss = tr.step(batch.to(DEV), ids.to(DEV), epoch)
         got.append(float(loss[0].cpu()))
-        seed = (tr.seed * 0x9E3779B1 + tr.step_count) & 0x3FFFFFFFFFFFFFFF      # the stream the trainer just used
+        seed, r0 = tr.dropout_key(), tr.step_count << 40      # the stream the trainer just used: key + (step << 40) row offset
         masks = {}
         for l in range(ospec.num_linear - 1):
             buf = torch.empty(n, ospec.out_dims[l], dtype=torch.uint8, device=DEV)
-            L.check(tr.engine.lib.dsdf_dropout_mask(seed, l, 0, n, ospec.out_dims[l], drop_p, buf.data_ptr(), None))
+            L.check(tr.engine.lib.dsdf_dropout_mask(seed, l, r0, n, ospec.out_dims[l], drop_p, buf.data_ptr(), None))
             masks[l] = buf.cpu().float()
         row_scene = ids.repeat_interleave(sps)
         l_ref, grads, zgrad, pred_raw = O.train_loss_and_grads(ospec, P, Z, row_scene, batch[:, :3], batch[:, 3], 0.1, 1e-4, epoch,

@@ -19,17 +19,20 @@ ids = torch.arange(64) * 3
 batch = bench.make_batch(gen, dev, ids, bench.SCENES_TOTAL)
 ids_d = ids.to(dev)
 g_rows = 64 * bench.SAMPLES_PER_SCENE
-out = {}
-for s in (64, 32, 16, 8):
-    b, i = batch[:s * bench.SAMPLES_PER_SCENE], ids_d[:s].contiguous()
-    for _ in range(5):
-        tr.step(b, i, epoch=1, global_rows=g_rows)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        tr.step(b, i, epoch=1, global_rows=g_rows)
-    e1.record()
-    torch.cuda.synchronize()
-    out[s] = round(e0.elapsed_time(e1) / steps, 4)
-print("side_stream", tr.side_stream is not None, out, "bound@8", round(out[64] / (8 * out[8]), 3))
+for mode in ("eager", "graph"):
+    fn = tr.step if mode == "eager" else tr.step_graphed
+    out = {}
+    for s in (64, 32, 16, 8):
+        b, i = batch[:s * bench.SAMPLES_PER_SCENE], ids_d[:s].contiguous()
+        for _ in range(5):
+            fn(b, i, epoch=1, global_rows=g_rows)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn(b, i, epoch=1, global_rows=g_rows)
+        e1.record()
+        torch.cuda.synchronize()
+        out[s] = round(e0.elapsed_time(e1) / steps, 4)
+    print(mode, "side_stream", tr.side_stream is not None, out, "bound@8", round(out[64] / (8 * out[8]), 3),
+          "kernels/step", getattr(tr, "graph_launches", None) if mode == "graph" else "-")
