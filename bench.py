@@ -238,6 +238,19 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
+def _teardown(dist) -> None:
+    """destroy_process_group with a watchdog: the measurement is complete and printed; a communicator teardown that does not
+    return within a minute must not hold the launcher (exit code 0 either way)."""
+    import threading
+    t = threading.Timer(60.0, lambda: os._exit(0))
+    t.daemon = True
+    t.start()
+    torch.cuda.synchronize()
+    dist.barrier()
+    dist.destroy_process_group()
+    t.cancel()
+
+
 def run_gpu(args):
     import torch.distributed as dist
     from deepsdf_b200.trainer import SceneTrainer
@@ -428,9 +441,10 @@ def run_gpu(args):
         except Exception as exc:  # noqa: BLE001 - the headline line must still be printed
             extras = {"error": repr(exc)[:300]}
 
+    trainer.release_graph()           # a live graph holding NCCL kernels blocks the communicator's teardown
     if rank != 0:
         if world > 1:
-            dist.destroy_process_group()
+            _teardown(dist)
         return
 
     cpu = None
@@ -472,7 +486,7 @@ def run_gpu(args):
     }
     print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        _teardown(dist)
 
 
 def run_extras(trainer, dev, rank, world, barrier, max_over_ranks):

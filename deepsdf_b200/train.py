@@ -249,6 +249,7 @@ def main_function(experiment_directory: str, data_source: str = None, max_epochs
                            os.path.join(experiment_directory, logs_filename))
             logging.info("Finished {} ({}/{}) loss {:.6f} ({:.2f}s/epoch)".format(
                 epoch, epoch, num_epochs, loss_log[-1] if loss_log else float("nan"), timing_log[-1]))
+    trainer.release_graph()
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()

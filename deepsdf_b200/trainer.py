@@ -290,6 +290,17 @@ class SceneTrainer:
         object.__setattr__(self.decoder, "_param_epoch", getattr(self.decoder, "_param_epoch", 0) + 1)
         return self._graph_loss
 
+    def release_graph(self) -> None:
+        """Drop the captured graph.  MUST run before ``torch.distributed.destroy_process_group()`` when world_size > 1: a
+        live CUDA graph that holds NCCL kernels keeps the communicator busy and its teardown never returns."""
+        torch.cuda.synchronize(self.device)
+        self._graph = None
+        self._graph_loss = None
+        self._graph_key = None
+        import gc
+        gc.collect()
+        torch.cuda.synchronize(self.device)
+
     def graph_inputs(self, n_rows: int, n_scenes: int):
         """Static input buffers (samples [n_rows, 4], scene_ids [n_scenes]) a caller may fill directly (e.g. the H2D copy of
         the next batch) before ``step_graphed`` - no device-to-device copy then."""
