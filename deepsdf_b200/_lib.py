@@ -93,6 +93,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_adam_state": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, vp, f32, vp, vp]),
         "dsdf_step_advance": (C.c_int, [vp, f32, f32, vp]),
         "dsdf_step_set": (C.c_int, [vp, u32, vp]),
+        "dsdf_selftest_mma_rate": (C.c_int, [C.c_int, C.c_int, C.c_int, vp, vp]),
         "dsdf_selftest_umma_pair": (C.c_int, [C.c_int, vp, vp, vp, C.c_int, vp]),
         "dsdf_selftest_umma_aux": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, vp]),
         "dsdf_selftest_umma": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint,

@@ -47,6 +47,16 @@ constexpr int P_OFF_WLAST = P_OFF_AUX + 4 * AUX_CORE_BYTES;      // f32 [512]
 constexpr int P_OFF_YPART = P_OFF_WLAST + FH * 4;                // f32 [4][128]
 constexpr int P_SMEM = P_OFF_YPART + 4 * TILE_M * 4 + 1024;
 
+// Timeline instrumentation (build with -DDSDF_TRACE; never in the shipped library - tools/trace_fwd.py): SM clock at the
+// hand-over points of the 4th tile of CTA pair 0, read back with dsdf_debug_trace.  [role 0: epilogue warp 0, 1: MMA warp (2 per
+// step: a_ready seen, B stage full), 2: epilogue warp 15, 3: TMA warp (stage empty seen, per step), 4: epilogue warp 0 of CTA 1]
+#ifdef DSDF_TRACE
+__device__ unsigned long long g_trace[6][16][40];
+#define TR(role, l, e) do { if (trace_on) g_trace[role][l][e] = clock64(); } while (0)
+#else
+#define TR(role, l, e) do { } while (0)
+#endif
+
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(P_EPI_THREADS) : "memory"); }
 
 // Post-process 16 consecutive columns [c0, c0+16) of one row and write them (bf16) into the SW128 activation tile.
@@ -157,6 +167,9 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       uint32_t stage = 0, phase = 0;
       const uint64_t pol_w = l2_policy_evict_last();    // 3.4 MB of weights, re-read by every tile
       for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+#ifdef DSDF_TRACE
+        const bool trace_on = blockIdx.x == 0 && tp == pair0 + 3 * pair_stride && lane == 0;
+#endif
         // the two tiles of the pair may belong to different scenes: k-core 0 of a per-scene aux block is taken from
         // rank 0's scene, k-core 1 from rank 1's (fused.cuh)
         int scene0 = 0, scene1 = 0;
@@ -173,6 +186,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           for (int h = 0; h < n_halves; ++h) {
             // ---- aux stage: bias (+ xyz / latent) columns of these 256 output features
             mbar_wait_a(empty0 + stage * 8, phase ^ 1);
+            TR(3, l, h * 9);
             if (elect_one()) {
               if (leader) mbar_arrive_expect_tx_a(full0 + stage * 8, uint32_t(2 * aux_cores) * AUX_CORE_BYTES);
               const uint32_t dst = sB_u + stage * P_STAGE_BYTES, bar = full_leader + stage * 8;
@@ -189,6 +203,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
             if (++stage == P_STAGES) { stage = 0; phase ^= 1; }
             for (int kc = 0; kc < k_chunks; ++kc) {
               mbar_wait_a(empty0 + stage * 8, phase ^ 1);
+              TR(3, l, h * 9 + kc + 1);
               if (elect_one()) {
                 if (leader) mbar_arrive_expect_tx_a(full0 + stage * 8, 2 * P_STAGE_BYTES);
                 tma_load_2d_pair_hint_a(sB_u + stage * P_STAGE_BYTES, &tmW, full_leader + stage * 8, kc * 64, row_base + h * HALF_N, pol_w);
@@ -220,6 +235,9 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       const uint32_t ready0 = smem_u32(&bar_a_ready[0]);
       uint32_t stage = 0, phase = 0, a_cons = 0;
       for (int tp = pair0; tp < n_pairs; tp += pair_stride) {
+#ifdef DSDF_TRACE
+        const bool trace_on = blockIdx.x == 0 && tp == pair0 + 3 * pair_stride && lane == 0;
+#endif
         for (int l = 0; l < nh; ++l) {
           const int n_halves = args.prog[l].n_halves, k_chunks = args.prog[l].k_chunks;
           const int aux_steps = args.aux_steps[l];
@@ -242,8 +260,10 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
                 needm &= needm - 1;
                 waited |= 1u << qd;
               }
+              TR(1, l, 2 * (h * 9 + kc + 1));
               mbar_wait_a(full0 + stage * 8, phase);
               tc_fence_after();
+              TR(1, l, 2 * (h * 9 + kc + 1) + 1);
               const uint64_t ad = a_base + uint64_t(kc * (A_CHUNK_BYTES >> 4));
               const uint64_t bd = b_base + uint64_t(stage * (P_STAGE_BYTES >> 4));
               const uint64_t bx = b_aux + uint64_t(stage * (P_STAGE_BYTES >> 4));
@@ -359,6 +379,10 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
       const int tile_c = tile_ok ? tile : args.n_tiles - 1;
       const bool valid = tile_ok && (int64_t(tile_c) * TILE_M + rt) < args.n_rows &&
                          (args.tile_rows == nullptr || int(rt) < __ldg(args.tile_rows + tile_c));
+#ifdef DSDF_TRACE
+      const bool trace_on = blockIdx.x <= 1 && tp == pair0 + 3 * pair_stride && lane == 0 && (warp == 0 || (warp == 15 && blockIdx.x == 0));
+      const int trole = blockIdx.x == 1 ? 4 : (warp == 0 ? 0 : 2);
+#endif
       // dense per-row codes: this row's code as bf16 K chunks [chunk0, chunk0 + dense_chunks) of the activation tile
       // (thread j of the row writes chunks j, j + 4, ...; columns beyond L are zero)
       auto write_code_chunks = [&](int chunk0) {
@@ -445,6 +469,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         // all four keep words of the layer now: the warps idle here anyway (the tensor cores are still on half 0), and later
         // every cycle between tmem_full[1] and the last a_ready arrive is on the critical path of the next layer
         uint32_t kwa = 0xFFFFFFFFu, kwb = 0xFFFFFFFFu, kwc = 0xFFFFFFFFu, kwd = 0xFFFFFFFFu;
+        TR(trole, l, 0);
         if (drop) {
           kwa = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(j), args.drop_thr);
           kwb = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(4 + j), args.drop_thr);
@@ -453,6 +478,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
             kwd = dropout_keep_word_rk(args.philox_rk, uint32_t(l), grow, uint32_t(12 + j), args.drop_thr);
           }
         }
+        TR(trole, l, 1);      // keep words drawn
         const uint32_t par = mma_iter & 1;
         ++mma_iter;
         uint32_t* gdst = nullptr;
@@ -471,8 +497,10 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
           if (kTrain && gdst != nullptr) gdst[size_t(Q) * 4 * TILE_M] = g0 | (g1 << 16);
           // only the stores have to wait: for the tensor cores to be done with the old chunks, and for the previous layer's
           // stash of this quarter to have been read out of the tile
+          TR(trole, l, 3 + 3 * Q + (Q >= 2 ? 1 : 0));                         // quarter computed
           if (free_bar != nullptr) mbar_wait(free_bar, par);
           if (stash && ((wany >> Q) & 1u)) mbar_wait(&bar_q_stashed[Q], ((wpar >> Q) & 1u) ^ 1u);
+          TR(trole, l, 4 + 3 * Q + (Q >= 2 ? 1 : 0));                         // store slot free
           sts_u32x4(st_a0 + qoff, p0[0], p0[1], p0[2], p0[3]);
           sts_u32x4(st_a1 + qoff, p0[4], p0[5], p0[6], p0[7]);
           sts_u32x4(st_a2 + qoff, p1[0], p1[1], p1[2], p1[3]);
@@ -485,6 +513,7 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
             if (lane == 0) mbar_arrive(&bar_q_written[Q]);
             wpar ^= 1u << Q; wany |= 1u << Q;
           }
+          TR(trole, l, 5 + 3 * Q + (Q >= 2 ? 1 : 0));                         // stored + signalled
         };
         // one run-time dispatch per quarter instead of flag tests in every 16-column pass
         auto quarter = [&](int Q, uint32_t keep, uint64_t* free_bar) {
@@ -496,10 +525,12 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
         //      half 1's MMAs have passed K chunk 1 (free_q0), chunks 2,3 after K chunk 3 (free_lo); the previous layer's
         //      stash (TMA store) must have been read out of the tile.
         mbar_wait(&bar_tmem_full[0], par); tc_fence_after();
+        TR(trole, l, 2);
         quarter(0, kwa, &bar_free_q0);
         quarter(1, kwb, &bar_free_lo);
         // ---- half 1: after all of this layer's MMAs; the next layer starts on the K chunks that are already there
         mbar_wait(&bar_tmem_full[1], par); tc_fence_after();
+        TR(trole, l, 9);
         if (L.n_halves == 2) {
           quarter(2, kwc, nullptr);
           quarter(3, kwd, nullptr);
@@ -562,6 +593,12 @@ chain_forward_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_const
   cluster_sync_all();
   if (warp == P_EPI_WARPS + 1) tmem_dealloc_pair<512>(tmem_base);
 }
+
+#ifdef DSDF_TRACE
+extern "C" int dsdf_debug_trace(void* host_out) {
+  return cudaMemcpyFromSymbol(host_out, g_trace, sizeof(g_trace)) == cudaSuccess ? 0 : 1;
+}
+#endif
 
 // Number of CTA pairs that can be co-resident (one CTA per SM, both CTAs of a pair on one TPC); cached per kernel.
 template <typename K>

@@ -386,3 +386,77 @@ extern "C" int dsdf_selftest_umma_aux(const void* A, const void* B, const void* 
   DSDF_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Tensor-pipe rate probe: one CTA pair issues `iters` x 8 K-chunks of cta_group::2 MMAs (M = 256, N = n, K = 16 each,
+// SS mode: A [128 x 512] and B from shared memory - contents are whatever the launch finds there, only the rate is
+// measured) back to back and reports the SM clocks between the first issue and the completion of the last commit.
+// n = 256: 4 MMAs per chunk; n = 128: 8 MMAs per chunk (the same MACs).  With lsu_load != 0 the four other warps of each
+// CTA hammer the A tile with STS.128 meanwhile (an epilogue's share of the shared-memory port).
+namespace dsdf {
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(ST_THREADS, 1)
+mma_rate_kernel(int n, int iters, int lsu_load, unsigned long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar_done;
+  __shared__ uint32_t tmem_base_slot;
+  __shared__ volatile int stop_flag;
+  const int warp = threadIdx.x >> 5;
+  const bool leader = cluster_ctarank() == 0;
+  if (threadIdx.x == 0) { mbar_init(&bar_done, 1); fence_barrier_init(); stop_flag = 0; }
+  if (warp == 5) tmem_alloc_pair<512>(&tmem_base_slot);
+  for (int i = threadIdx.x; i < (131072 + 65536) / 16; i += ST_THREADS) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_all();
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+  if (warp == 5 && leader) {
+    if (elect_one()) {
+      const uint32_t idesc = umma_idesc_bf16(256, uint32_t(n), 0, 0);
+      const uint64_t hi = umma_desc_hi_sw128(16, 1024);
+      const uint32_t a0 = smem_u32(smem), b0 = smem_u32(smem) + 131072;
+      const long long t0 = clock64();
+      for (int it = 0; it < iters; ++it)
+        for (int kc = 0; kc < 8; ++kc)
+          for (int g = 0; g < 256 / n; ++g)
+            for (int ks = 0; ks < 4; ++ks)
+              umma_bf16_ss_pair(tmem_base + g * n, umma_desc(a0 + kc * 16384u + ks * 32u, hi),
+                                umma_desc(b0 + (kc & 3) * 16384u + g * 8192u + ks * 32u, hi), idesc, 1u);
+      umma_commit_pair(&bar_done, 0b11);
+      mbar_wait(&bar_done, 0);
+      out[0] = (unsigned long long)(clock64() - t0);
+      stop_flag = 1;
+    }
+    __syncwarp();
+  } else if (warp < 4 && lsu_load) {
+    // 128 threads: STS.128 into the A tile, row = thread, rotating 16-byte pieces (swizzle-free: contents do not matter)
+    uint32_t a = smem_u32(smem) + threadIdx.x * 128u, k = 0;
+    unsigned long long cnt = 0;
+    while (!stop_flag || !leader) {
+      sts_u32x4(a + ((k & 7u) << 4) + ((k >> 3) & 7u) * 16384u, k, k, k, k);
+      ++k; ++cnt;
+      if (!leader && cnt > (unsigned long long)iters * 8ull * 64ull) break;     // the peer CTA has no flag: bounded
+    }
+    if (leader && threadIdx.x == 0) out[1] = cnt;
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 5) tmem_dealloc_pair<512>(tmem_base);
+}
+
+}  // namespace dsdf
+
+extern "C" int dsdf_selftest_mma_rate(int n, int iters, int lsu_load, unsigned long long* out_dev, void* stream) {
+  using namespace dsdf;
+  if (int e = require_sm100()) return e;
+  DSDF_REQUIRE(n == 256 || n == 128, "mma rate probe: n must be 256 or 128");
+  const size_t smem = 131072 + 65536 + 1024;
+  DSDF_CHECK_CUDA(cudaFuncSetAttribute(mma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  mma_rate_kernel<<<2, ST_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(n, iters, lsu_load, out_dev);
+  DSDF_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -349,6 +349,10 @@ int dsdf_selftest_umma_pair(int mode, const void* A, const void* B, float* C, in
  * (A_aux, B_aux: [256][32] bf16); lbo / sbo = descriptor offsets under test (the kernels use 2048 / 128). */
 int dsdf_selftest_umma_aux(const void* A, const void* B, const void* A_aux, const void* B_aux, float* C, int K, int aux_k,
                            unsigned lbo, unsigned sbo, void* stream);
+/* Tensor-pipe rate probe (bring-up / DESIGN.md evidence): `iters` x 8 K-chunks of cta_group::2 MMAs, M = 256, N = n (256 or
+ * 128), issued back to back by one CTA pair from shared-memory operands; out_dev[0] = SM clocks from first issue to the last
+ * commit, out_dev[1] = STS.128 issued meanwhile per thread when lsu_load != 0 (an epilogue's share of the shared-memory port). */
+int dsdf_selftest_mma_rate(int n, int iters, int lsu_load, unsigned long long* out_dev, void* stream);
 
 #ifdef __cplusplus
 }
