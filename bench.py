@@ -285,7 +285,6 @@ def run_gpu(args):
         host_batches.append(db.cpu().pin_memory())
         dev_ids.append(ids.to(dev))
         host_ids.append(ids.pin_memory())
-    staging = {"samples": torch.empty_like(dev_batches[0]), "scene_ids": torch.empty_like(dev_ids[0])}
     global_rows = N * world
     row0 = rank * N
 
@@ -347,16 +346,23 @@ def run_gpu(args):
     value = global_rows / (ms_step / 1e3)
     loss_dev = [float(x) for x in loss.cpu()]
 
-    # ---- timed region 2: end to end from pinned host memory, loss read back every step
+    # ---- timed region 2: end to end from pinned host memory, loss read back every step.  The user-facing loop of a host-fed
+    #      run: HostFeeder.submit (H2D copy of the NEXT batch on a copy stream, what DataLoader workers + .cuda() do in the
+    #      reference) then HostFeeder.step on the current one; every timed step contains one 16.8 MB copy and one loss read.
+    from deepsdf_b200.trainer import HostFeeder
+    feeder = HostFeeder(trainer, N, S_step, graphed=graphed)
+    feeder.submit(host_batches[0], host_ids[0])
     for i in range(2):
-        trainer.step_from_host(host_batches[i], host_ids[i], 1, staging, global_rows=global_rows, row0=row0, graphed=graphed).cpu()
+        feeder.submit(host_batches[(i + 1) % N_HOST_BATCHES], host_ids[(i + 1) % N_HOST_BATCHES])
+        feeder.step(1, global_rows=global_rows, row0=row0).cpu()
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     last = None
     for i in range(args.steps):
-        l = trainer.step_from_host(host_batches[i % N_HOST_BATCHES], host_ids[i % N_HOST_BATCHES], 1, staging,
-                                   global_rows=global_rows, row0=row0, graphed=graphed)
+        nb = (i + 3) % N_HOST_BATCHES
+        feeder.submit(host_batches[nb], host_ids[nb])          # next batch's copy runs under this step
+        l = feeder.step(1, global_rows=global_rows, row0=row0)
         last = l.cpu()                    # device -> host read of the step's loss (synchronises, like .item() at :535)
     e3.record()
     barrier()

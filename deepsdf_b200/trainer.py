@@ -387,3 +387,46 @@ class SceneTrainer:
 
     def mean_latent_magnitude(self) -> float:
         return float(torch.mean(torch.norm(self.lat_vecs.detach(), dim=1)))             # :242-243
+
+
+class HostFeeder:
+    """Double-buffered host -> device input pipeline in front of ``SceneTrainer`` - the part the reference's DataLoader
+    workers + ``.cuda()`` play (train_deep_sdf.py:369-375, 483-509).  ``submit`` starts the copy of a pinned host batch on a
+    copy stream; ``step`` trains on the oldest submitted batch.  Submitting batch i+1 before stepping batch i puts its copy
+    under that step's kernels, so a host-fed loop runs at the device-resident step time instead of copy + step."""
+
+    def __init__(self, trainer: "SceneTrainer", n_rows: int, n_scenes: int, depth: int = 2, graphed: bool = True):
+        self.trainer, self.depth, self.graphed = trainer, depth, graphed
+        dev = trainer.device
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self._bufs = [(torch.empty(n_rows, 4, device=dev), torch.zeros(n_scenes, dtype=torch.int64, device=dev)) for _ in range(depth)]
+        self._ready = [torch.cuda.Event() for _ in range(depth)]
+        self._consumed = [torch.cuda.Event() for _ in range(depth)]
+        self._head = self._tail = 0
+
+    def submit(self, samples_host: torch.Tensor, scene_ids_host: torch.Tensor) -> None:
+        if self._head - self._tail >= self.depth:
+            raise L.DsdfError("HostFeeder: all staging buffers are in flight; call step() first")
+        k = self._head % self.depth
+        d_s, d_i = self._bufs[k]
+        if self._head >= self.depth:
+            self.copy_stream.wait_event(self._consumed[k])     # the step that read this buffer last has been enqueued and must finish
+        with torch.cuda.stream(self.copy_stream):
+            d_s.copy_(samples_host, non_blocking=True)
+            d_i.copy_(scene_ids_host, non_blocking=True)
+            self._ready[k].record(self.copy_stream)
+        self._head += 1
+
+    def step(self, epoch: int, global_rows: Optional[int] = None, row0: int = 0) -> torch.Tensor:
+        if self._tail >= self._head:
+            raise L.DsdfError("HostFeeder: nothing submitted")
+        k = self._tail % self.depth
+        d_s, d_i = self._bufs[k]
+        cur = torch.cuda.current_stream(self.trainer.device)
+        cur.wait_event(self._ready[k])
+        fn = self.trainer.step_graphed if self.graphed else self.trainer.step
+        loss = fn(d_s, d_i, epoch, global_rows=global_rows, row0=row0)
+        self._consumed[k].record(cur)
+        self._tail += 1
+        return loss
+

@@ -151,3 +151,37 @@ def test_graphed_step_replays_the_eager_step_bit_for_bit(clip):
         L.check(L.lib().dsdf_dropout_mask(tr.dropout_key(), 0, (s + 1) << 40, 128, 512, 0.2, buf.data_ptr(), None))
     torch.cuda.synchronize()
     assert not torch.equal(m[0], m[1])
+
+
+@pytest.mark.parametrize("graphed", [False, True])
+def test_host_feeder_overlaps_copies_without_changing_results(graphed):
+    """HostFeeder (copy of batch i+1 on a copy stream under the step of batch i) == copying and stepping one after the other."""
+    from deepsdf_b200.trainer import HostFeeder, SceneTrainer
+    S, sps = 4, 1024
+    rng = np.random.RandomState(5)
+    host = []
+    for b in range(5):
+        xyz = rng.uniform(-1, 1, (S * sps, 3)).astype(np.float32)
+        sdf = (0.2 * np.sin(3 * xyz).sum(1, keepdims=True)).astype(np.float32)
+        ids = np.sort(rng.choice(6, S, replace=False)).astype(np.int64)
+        host.append((torch.from_numpy(np.concatenate([xyz, sdf], 1)).pin_memory(), torch.from_numpy(ids).pin_memory()))
+    out = []
+    for piped in (False, True):
+        tr = SceneTrainer(_specs(), 6, DEV, seed=3)
+        losses = []
+        if piped:
+            fd = HostFeeder(tr, S * sps, S, graphed=graphed)
+            fd.submit(*host[0])
+            for b in range(5):
+                if b + 1 < 5:
+                    fd.submit(*host[b + 1])
+                losses.append(fd.step(epoch=7).cpu().clone())
+            with pytest.raises(Exception):
+                fd.step(epoch=7)                                     # nothing submitted
+        else:
+            staging = {"samples": torch.empty(S * sps, 4, device=DEV), "scene_ids": torch.zeros(S, dtype=torch.int64, device=DEV)}
+            for b in range(5):
+                losses.append(tr.step_from_host(host[b][0], host[b][1], 7, staging).cpu().clone())
+        torch.cuda.synchronize()
+        out.append((torch.stack(losses), tr.flat_p.cpu().clone(), tr.lat_vecs.cpu().clone()))
+    assert torch.equal(out[0][0], out[1][0]) and torch.equal(out[0][1], out[1][1]) and torch.equal(out[0][2], out[1][2])
