@@ -138,7 +138,14 @@ class Decoder(nn.Module):
             # eval-mode boundary call of an 8x512-class network with a short per-row code (CodeLength <= 16): the bf16
             # tcgen05 chain in row-latent mode instead of the fp32 CUDA-core path (set ``decoder.fused_eval = False`` for
             # the exact fp32 mode)
-            return _FusedRowsFn.apply(self, input, *self.flat_param_list())
+            y = _FusedRowsFn.apply(self, input)
+            params = self.flat_param_list()
+            if torch.is_grad_enabled() and any(p.requires_grad for p in params):
+                # parameter gradients (rare in eval mode) hang on a separate, zero-valued branch of the graph: autograd walks it
+                # only when a parameter's gradient is actually asked for, so autograd.grad(sdf, xyz) / the jvp loop of
+                # deep_sdf/mesh.py:405-422 on a loaded model (whose parameters still require grad) never pays for them
+                y = y + _ParamBranchFn.apply(self, input.detach(), *params)
+            return y
         seed = 0
         if self.training and (self.spec.uses_dropout() or self.spec.latent_dropout):
             # one Philox key per call, drawn from torch's CPU generator -> torch.manual_seed makes runs repeatable.  Only
@@ -166,50 +173,64 @@ class _SecondOrderGuard(torch.autograd.Function):
 
 
 class _FusedRowsFn(torch.autograd.Function):
-    """Eval-mode ``decoder(input[N, L+3])`` of an 8x512-class network with CodeLength <= 16 on the fused tcgen05 chain in
-    row-latent mode (bf16 operands, fp32 accumulate: SDF within 2e-3 of the fp32 arithmetic).  The input gradient comes from
-    the fused dgrad chain + input-gradient GEMM (one ``G`` per call, also under the double-backward trick of
-    ``torch.autograd.functional.jvp``); parameter gradients - rare in eval mode - are taken from the fp32 generic path."""
+    """Eval-mode ``decoder(input[N, L+3])`` of an 8x512-class network (CodeLength <= 16, or a long code such as 256) on the
+    fused tcgen05 chain in row-latent mode (bf16 operands, fp32 accumulate: SDF within 2e-3 of the fp32 arithmetic).  The
+    input gradient comes from the fused dgrad chain + input-gradient GEMM (one ``G`` per call, also under the
+    double-backward trick of ``torch.autograd.functional.jvp``).  Parameter gradients live on ``_ParamBranchFn``."""
 
     @staticmethod
-    def forward(ctx, module, inp, *params):
+    def forward(ctx, module, inp):
         from ..utils import fused_engine_for
         eng = fused_engine_for(module)
         x = inp.detach().to(torch.float32).contiguous()
         sdf, _ = eng.sdf_and_input_grad_rows(x, with_grad=False)
         ctx.module = module
-        ctx.save_for_backward(x, *params)
+        ctx.save_for_backward(x)
         ctx.inp_ref = inp if inp.requires_grad else None
         return sdf.unsqueeze(1)
 
     @staticmethod
     def backward(ctx, grad_out):
         from ..utils import fused_engine_for
-        x, *params = ctx.saved_tensors
+        (x,) = ctx.saved_tensors
         module = ctx.module
-        need_in = ctx.needs_input_grad[1]
-        need_p = any(ctx.needs_input_grad[2:])
+        if not ctx.needs_input_grad[1]:
+            return None, None
         N = x.shape[0]
-        gin = None
-        deps = [t for t in ([ctx.inp_ref] if ctx.inp_ref is not None else []) + [p for p in params if p.requires_grad]]
-        if need_in:
-            eng = fused_engine_for(module)
-            n_pad = (N + 127) // 128 * 128
-            q = x if n_pad == N else torch.cat([x, x.new_zeros(n_pad - N, x.shape[1])], 0)
-            _, G = eng.sdf_and_input_grad_rows(q)
-            G = G[:N].clone()
-            if torch.is_grad_enabled() and deps:
-                G = _SecondOrderGuard.apply(G, *deps)
-            gin = grad_out * G                      # differentiable w.r.t. grad_out: the jvp trick of deep_sdf/mesh.py:405-422
+        deps = ([ctx.inp_ref] if ctx.inp_ref is not None else []) + [p for p in module.flat_param_list() if p.requires_grad]
+        eng = fused_engine_for(module)
+        n_pad = (N + 127) // 128 * 128
+        q = x if n_pad == N else torch.cat([x, x.new_zeros(n_pad - N, x.shape[1])], 0)
+        _, G = eng.sdf_and_input_grad_rows(q)
+        G = G[:N].clone()
+        if torch.is_grad_enabled() and deps:
+            G = _SecondOrderGuard.apply(G, *deps)
+        return None, grad_out * G                   # differentiable w.r.t. grad_out: the jvp trick of deep_sdf/mesh.py:405-422
+
+
+class _ParamBranchFn(torch.autograd.Function):
+    """The parameter dependence of the fused eval-mode call as its own graph branch: forward contributes zeros, backward
+    yields the parameter gradients from the fp32 generic path (recomputed from the saved input)."""
+
+    @staticmethod
+    def forward(ctx, module, x, *params):
+        ctx.module = module
+        ctx.save_for_backward(x.to(torch.float32).contiguous(), *params)
+        return torch.zeros(x.shape[0], 1, device=x.device, dtype=torch.float32)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        x, *params = ctx.saved_tensors
+        need = ctx.needs_input_grad[2:]
         gp = tuple(None for _ in params)
-        if need_p:
+        if any(need):
             with torch.enable_grad():
-                ps = [p.detach().requires_grad_(n) for p, n in zip(params, ctx.needs_input_grad[2:])]
-                y = _DecoderFn.apply(module, x, False, 0, *ps)
+                ps = [p.detach().requires_grad_(n) for p, n in zip(params, need)]
+                y = _DecoderFn.apply(ctx.module, x, False, 0, *ps)
                 want = [p for p in ps if p.requires_grad]
                 got = iter(torch.autograd.grad(y, want, grad_out.detach()))
-            gp = tuple(next(got) if n else None for n in ctx.needs_input_grad[2:])
-        return (None, gin) + gp
+            gp = tuple(next(got) if n else None for n in need)
+        return (None, None) + gp
 
 
 class _DecoderFn(torch.autograd.Function):
