@@ -125,6 +125,13 @@ class Decoder(nn.Module):
             object.__setattr__(self, "_fused_rows_ok", ok)
         return ok
 
+    def _small_supported(self) -> bool:
+        ok = getattr(self, "_small_ok", None)
+        if ok is None:
+            ok = L.lib().dsdf_small_supported(C.byref(self._desc)) == 1
+            object.__setattr__(self, "_small_ok", ok)
+        return ok
+
     def forward(self, input):
         if input.dim() != 2 or input.shape[1] != self.spec.full_dims[0]:
             raise RuntimeError(
@@ -144,6 +151,15 @@ class Decoder(nn.Module):
                 # parameter gradients (rare in eval mode) hang on a separate, zero-valued branch of the graph: autograd walks it
                 # only when a parameter's gradient is actually asked for, so autograd.grad(sdf, xyz) / the jvp loop of
                 # deep_sdf/mesh.py:405-422 on a loaded model (whose parameters still require grad) never pays for them
+                y = y + _ParamBranchFn.apply(self, input.detach(), *params)
+            return y
+        if not self.training and self.fused_eval and input.shape[0] > 0 and self._small_supported():
+            # eval-mode boundary call of a small network (hidden widths <= 128: the 4x32 / 4x64 / 6x128 decoders of the reference's
+            # optimisation runs): ONE fp32 launch for the SDF - and for dSDF/dinput when the input requires grad - instead of
+            # the per-layer generic kernels; same fp32 arithmetic up to summation order (~1e-6)
+            y = _SmallRowsFn.apply(self, input)
+            params = self.flat_param_list()
+            if torch.is_grad_enabled() and any(p.requires_grad for p in params):
                 y = y + _ParamBranchFn.apply(self, input.detach(), *params)
             return y
         seed = 0
@@ -206,6 +222,41 @@ class _FusedRowsFn(torch.autograd.Function):
         if torch.is_grad_enabled() and deps:
             G = _SecondOrderGuard.apply(G, *deps)
         return None, grad_out * G                   # differentiable w.r.t. grad_out: the jvp trick of deep_sdf/mesh.py:405-422
+
+
+class _SmallRowsFn(torch.autograd.Function):
+    """Eval-mode ``decoder(input[N, L+D])`` of a small network on the fused fp32 small-network kernel (csrc/smallnet.cu): the
+    SDF and - when the input requires grad - ``G = dSDF/dinput`` come out of the same launch.  Parameter gradients live on
+    ``_ParamBranchFn``; the double-backward trick of ``torch.autograd.functional.jvp`` works as on the other paths."""
+
+    @staticmethod
+    def forward(ctx, module, inp):
+        from ..small import small_engine_for
+        eng = small_engine_for(module)
+        x = inp.detach().to(torch.float32).contiguous()
+        want_g = inp.requires_grad and torch.is_grad_enabled()
+        sdf, G = eng.sdf_and_input_grad(x, with_grad=want_g)
+        ctx.module = module
+        ctx.have_g = G is not None
+        ctx.save_for_backward(x, *([G] if G is not None else []))
+        ctx.inp_ref = inp if inp.requires_grad else None
+        return sdf.unsqueeze(1)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        from ..small import small_engine_for
+        module = ctx.module
+        if not ctx.needs_input_grad[1]:
+            return None, None
+        if ctx.have_g:
+            x, G = ctx.saved_tensors
+        else:
+            (x,) = ctx.saved_tensors
+            _, G = small_engine_for(module).sdf_and_input_grad(x)
+        deps = ([ctx.inp_ref] if ctx.inp_ref is not None else []) + [p for p in module.flat_param_list() if p.requires_grad]
+        if torch.is_grad_enabled() and deps:
+            G = _SecondOrderGuard.apply(G, *deps)
+        return None, grad_out * G
 
 
 class _ParamBranchFn(torch.autograd.Function):

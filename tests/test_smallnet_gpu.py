@@ -208,3 +208,42 @@ def test_latent_optimizer_on_small_networks_tracks_oracle_reconstruct(name):
         rel = ((got_loss[:, s] - ref_loss).abs() / ref_loss).max().item()
         print(f"{name} shape {s}: loss {ref_loss[0]:.5f} -> {ref_loss[-1]:.5f}; max rel loss diff {rel:.2e}")
         assert rel <= 5e-3 and abs(float(got_loss[0, s]) - float(ref_loss[0])) <= 1e-5 * float(ref_loss[0]) + 1e-7
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_boundary_call_routes_eval_mode_small_networks(name):
+    """decoder(input[N, L+3]) itself - what the reference's unchanged scripts call - in eval mode: one small-network launch for
+    the SDF (+ G when the input requires grad), the jvp double-backward trick of deep_sdf/mesh.py:405-422, and parameter
+    gradients (their own graph branch, fp32 generic path) equal to the ones with the routing switched off."""
+    m, pre, ospec, params, mod, inp = _case(name)
+    lib = L.lib()
+    x = inp.to(DEV)
+    with torch.no_grad():
+        n0 = int(lib.dsdf_launch_count())
+        y = mod(x)
+        n_launch = int(lib.dsdf_launch_count()) - n0
+    assert y.shape == (x.shape[0], 1) and n_launch <= 2, n_launch
+    assert np.abs(y.squeeze(1).cpu().numpy() - BLOB[pre + "eval_out"].reshape(-1)).max() <= 1e-5
+    xg = x.clone().requires_grad_(True)
+    n0 = int(lib.dsdf_launch_count())
+    yg = mod(xg)
+    (G,) = torch.autograd.grad(yg.sum(), xg)
+    assert int(lib.dsdf_launch_count()) - n0 <= 2                      # SDF and G from the same launch, no parameter-gradient pass
+    ref_G = BLOB[pre + "input_grad"]
+    assert np.abs(G.cpu().numpy() - ref_G).max() <= 1e-4 * max(1.0, np.abs(ref_G).max())
+    # forward-mode product through the double-backward trick
+    v = torch.randn_like(x)
+    _, jv = torch.autograd.functional.jvp(lambda t: mod(t), x, v)
+    want = (torch.from_numpy(ref_G).to(DEV) * v).sum(1, keepdim=True)
+    assert (jv - want).abs().max().item() <= 1e-4 * max(1.0, float(want.abs().max()))
+    # parameter gradients: same values as the generic path
+    mod.zero_grad()
+    mod(x).sum().backward()
+    g_small = [p.grad.clone() for p in mod.parameters()]
+    mod.fused_eval = False
+    mod.zero_grad()
+    y32 = mod(x)
+    y32.sum().backward()
+    mod.fused_eval = True
+    assert all(torch.equal(a, p.grad) for a, p in zip(g_small, mod.parameters()))
+    assert (y32.detach() - y).abs().max().item() <= 1e-5
