@@ -90,6 +90,7 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_iso_emit": (C.c_int, [vp, i32, i32, i32, f32, P(f32), P(f32), vp, vp, vp]),
         "dsdf_adam": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp, vp]),
         "dsdf_clip_coef": (C.c_int, [vp, i64, f32, vp, vp, vp]),
+        "dsdf_clip_coef_static": (C.c_int, [vp, i64, f32, vp, vp]),
         "dsdf_adam_state": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, vp, f32, vp, vp]),
         "dsdf_step_advance": (C.c_int, [vp, f32, f32, vp]),
         "dsdf_step_set": (C.c_int, [vp, u32, vp]),

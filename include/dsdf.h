@@ -334,6 +334,17 @@ int dsdf_adam_state(float* p, const float* g, float* m, float* v, int64_t n, flo
 /* torch.nn.utils.clip_grad_norm_ (train_deep_sdf.py:541-543) over one flat fp32 gradient: out[0] = ||g||_2,
  * out[1] = min(1, max_norm / (||g||_2 + 1e-6)).  Deterministic two-stage reduction; `scratch` holds 1024 floats. */
 int dsdf_clip_coef(const float* g, int64_t n, float max_norm, float* scratch, float* out, void* stream);
+/* The same coefficient without a caller workspace and without any allocation (csrc/noalloc.cu).  NO counterpart in the
+ * reference: added for callers that cannot call cudaMalloc or hand over scratch - code
+ * under CUDA-graph capture, tight serving loops, harnesses that forbid allocation.  The 1024 partial sums live in a file-scope
+ * `static __device__ __align__(256)` array of 4 KB that every GPU loading the library holds until exit; its device address is
+ * resolved once per device (cudaGetSymbolAddress with that device current) on the first call there.  n must be
+ * <= DSDF_CLIP_STATIC_MAX_N, larger sizes are rejected with an error.  Calls no cudaMalloc / cudaFree / allocating routine.
+ * Every call on a device shares the array: it keeps the last call's partials (each call overwrites all of them, nothing needs
+ * clearing), and two calls that OVERLAP on the GPU (different streams, parallel graph branches) race - serialise them.
+ * Bit-identical to dsdf_clip_coef (same block ranges, same summation order). */
+#define DSDF_CLIP_STATIC_MAX_N (1LL << 28)
+int dsdf_clip_coef_static(const float* g, int64_t n, float max_norm, float* out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * tcgen05 bring-up self test (see csrc/selftest.cu). */
