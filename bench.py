@@ -65,9 +65,9 @@ SPECS = {
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of each tensor kernel at this workload: a STATIC copy of the
-# committed ncu capture (profiles/r02_ncu_v2_summary.txt), not re-measured by this script; algorithmic stash traffic:
+# committed ncu capture (profiles/r02_ncu_v3_summary.txt), not re-measured by this script; algorithmic stash traffic:
 # forward 8.6 GB, dgrad 7.5 GB, wgrad 14.7 GB
-NCU_DRAM_BYTES = {"fused_forward": 8.561e9, "fused_dgrad": 7.675e9, "wgrad": 14.514e9}
+NCU_DRAM_BYTES = {"fused_forward": 8.562e9, "fused_dgrad": 7.708e9, "wgrad": 14.510e9}
 
 
 def load_peaks():
@@ -384,7 +384,7 @@ def run_gpu(args):
     peak = peaks["sustained"]
     roofline = {
         "bound": "tensor", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-        "traffic": NCU_DRAM_BYTES.get(dom), "traffic_unit": "bytes per launch (dram read + write, ncu --set full, profiles/r01_ncu_v9_summary.txt)",
+        "traffic": NCU_DRAM_BYTES.get(dom), "traffic_unit": "bytes per launch (dram read + write, ncu --set full, profiles/r02_ncu_v3_summary.txt)",
         "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
         "flops_per_launch": FLOP_FWD_PER_ROW * N,
         "kernels_ms": kern,
