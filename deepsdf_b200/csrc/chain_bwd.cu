@@ -30,10 +30,21 @@ constexpr int B_STAGES = 5;
 constexpr int B_STAGE_BYTES = 128 * 128;
 constexpr int B_OFF_B = A_BYTES;
 constexpr int B_OFF_WLAST = B_OFF_B + B_STAGES * B_STAGE_BYTES;   // f32 [512]
-constexpr int B_OFF_XYZ = B_OFF_WLAST + FH * 4;                   // f32 [3][128]
-constexpr int B_SMEM = B_OFF_XYZ + 3 * TILE_M * 4 + 1024;
+constexpr int B_OFF_XYZ = B_OFF_WLAST + FH * 4;                   // float4 (x, y, z, -) of row r at slot (r & 7) * 17 + (r >> 3):
+                                                                  //   the column sums walk rows r0 + 8 i with ONE LDS.128 per row,
+                                                                  //   and the eight row classes of a warp fall on distinct banks
+constexpr int B_SMEM = B_OFF_XYZ + 8 * 17 * 16 + 1024;
 
 __device__ __forceinline__ void bwd_bar() { asm volatile("bar.sync 1, %0;" ::"n"(B_EPI_THREADS) : "memory"); }
+
+// packed fp32 pairs (sm_100 FFMA2)
+__device__ __forceinline__ uint64_t pack_f32x2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ void fma_f32x2(uint64_t& d, uint64_t a, uint64_t b) { asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b)); }
 
 // 16 columns [c0, c0+16) of one row: v = accumulators (or dy * w_last), gated and scaled, packed to bf16 into the A tile
 __device__ __forceinline__ void bwd_pass16(uint32_t taddr, bool has_acc, float dyv, uint32_t swl, uint32_t gate16,
@@ -260,9 +271,8 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       const float dyv = valid ? __ldg(args.dy + lrow) : 0.0f;
       if (j == 0) {
         const float* pt = args.xyz + lrow * args.xyz_stride;
-        sts_f32(xyz_a + rt * 4u, valid ? __ldg(pt + 0) : 0.0f);
-        sts_f32(xyz_a + (TILE_M + rt) * 4u, valid ? __ldg(pt + 1) : 0.0f);
-        sts_f32(xyz_a + (2 * TILE_M + rt) * 4u, valid ? __ldg(pt + 2) : 0.0f);
+        sts_u32x4(xyz_a + ((rt & 7u) * 17u + (rt >> 3)) * 16u, __float_as_uint(valid ? __ldg(pt + 0) : 0.0f),
+                  __float_as_uint(valid ? __ldg(pt + 1) : 0.0f), __float_as_uint(valid ? __ldg(pt + 2) : 0.0f), 0u);
       }
       bwd_bar();      // s_xyz visible to the column-sum passes of this tile
 
@@ -342,7 +352,7 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           if (cols_valid && do_sums) {
             const uint32_t piece = uint32_t(warp & 1) * 4u + pl;
             const uint32_t a0 = smem_a + uint32_t(cw >> 6) * A_CHUNK_BYTES + r0 * 128u + ((piece ^ r0) << 4);
-            const uint32_t xb = xyz_a + r0 * 4u;
+            const uint32_t xb = xyz_a + r0 * (17u * 16u);
             if (!want_xyz) {
 #pragma unroll
               for (int i = 0; i < TILE_M / 8; ++i) {
@@ -352,20 +362,33 @@ chain_dgrad_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
                 s[4] += bf16_lo_to_f32(w2); s[5] += bf16_hi_to_f32(w2); s[6] += bf16_lo_to_f32(w3); s[7] += bf16_hi_to_f32(w3);
               }
             } else {
+              // packed fp32 pairs (FFMA2: one instruction per (lo, hi) column pair and sum - half the FP issue slots of the
+              // scalar form, same roundings: fma(v, 1, s) == s + v)
+              uint64_t s2[4], sx2[4], sy2[4], sz2[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) { s2[k] = 0ull; sx2[k] = 0ull; sy2[k] = 0ull; sz2[k] = 0ull; }
 #pragma unroll 4
               for (int i = 0; i < TILE_M / 8; ++i) {
                 uint32_t w[4];
                 asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(a0 + uint32_t(i) * 1024u));
-                const float x = lds_f32(xb + uint32_t(i) * 32u), y = lds_f32(xb + uint32_t(TILE_M + 8 * i) * 4u),
-                            z = lds_f32(xb + uint32_t(2 * TILE_M + 8 * i) * 4u);
+                const float4 p = lds_f32x4(xb + uint32_t(i) * 16u);
+                const float x = p.x, y = p.y, z = p.z;
+                const uint64_t one2 = pack_f32x2(1.0f, 1.0f), x2 = pack_f32x2(x, x), y2 = pack_f32x2(y, y), z2 = pack_f32x2(z, z);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                  const float lo = bf16_lo_to_f32(w[k]), hi = bf16_hi_to_f32(w[k]);
-                  s[2 * k] += lo; s[2 * k + 1] += hi;
-                  sx[2 * k] += x * lo; sx[2 * k + 1] += x * hi;
-                  sy[2 * k] += y * lo; sy[2 * k + 1] += y * hi;
-                  sz[2 * k] += z * lo; sz[2 * k + 1] += z * hi;
+                  const uint64_t v2 = pack_f32x2(bf16_lo_to_f32(w[k]), bf16_hi_to_f32(w[k]));
+                  fma_f32x2(s2[k], v2, one2);
+                  fma_f32x2(sx2[k], v2, x2);
+                  fma_f32x2(sy2[k], v2, y2);
+                  fma_f32x2(sz2[k], v2, z2);
                 }
+              }
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                unpack_f32x2(s2[k], s[2 * k], s[2 * k + 1]);
+                unpack_f32x2(sx2[k], sx[2 * k], sx[2 * k + 1]);
+                unpack_f32x2(sy2[k], sy[2 * k], sy[2 * k + 1]);
+                unpack_f32x2(sz2[k], sz[2 * k], sz[2 * k + 1]);
               }
             }
           }
