@@ -520,26 +520,31 @@ def run_extras(trainer, dev, rank, world, barrier, max_over_ranks):
     G = torch.empty(chunk, Lz + 3, device=dev)
     cb = eng.scene_bias(trainer.lat_vecs[:1].contiguous(), torch.zeros(1, dtype=torch.int64, device=dev))
 
-    def sweep(with_grad):
+    cbx = eng.scene_bias_exact(trainer.lat_vecs[:1].contiguous(), torch.zeros(1, dtype=torch.int64, device=dev))
+
+    def sweep(mode):
         head = 0
         while head < total:
             n = min(chunk, total - head)
             eng.grid_points(NG, first + head, n, out=xyz)
-            if with_grad:
+            if mode == "sdf_and_grad":
                 eng.sdf_and_input_grad(cb, ts, xyz, G=G, sdf=sdf)
+            elif mode == "sdf_exact":
+                eng.decode_scenes(cbx, ts, xyz, out=sdf, exact=True)      # split-fp16 mode: <= 1e-5 vs fp32 (csrc/chain_exact.cu)
             else:
                 eng.decode_scenes(cb, ts, xyz, out=sdf)
             head += n
 
     res = {}
-    for with_grad in (False, True):
-        sweep(with_grad)                                     # warm-up (allocations, attribute setup)
+    for mode in ("sdf_only", "sdf_and_grad", "sdf_exact"):
+        sweep(mode)                                          # warm-up (allocations, attribute setup)
         barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(); sweep(with_grad); b.record()
+        a.record(); sweep(mode); b.record()
         barrier()
         ms = max_over_ranks(a.elapsed_time(b))
-        res["sdf_and_grad" if with_grad else "sdf_only"] = {"ms": ms, "queries_per_s": NG ** 3 / (ms / 1e3)}
+        res[mode] = {"ms": ms, "queries_per_s": NG ** 3 / (ms / 1e3)}
+    res["sdf_exact"]["what"] = "high-precision tensor-core mode: (hi, lo) fp16 operand pairs, <= 1e-5 vs the fp32 arithmetic (tests/test_exact_gpu.py)"
     flop = 2 * FLOP_FWD_PER_ROW
     out["grid"] = {"N": NG, "queries": NG ** 3, "sharding": f"z-slab x{world}", "chunk_rows": chunk, **res,
                    "sdf_and_grad_tflops_algorithmic": flop * NG ** 3 / (res["sdf_and_grad"]["ms"] / 1e3) / 1e12,

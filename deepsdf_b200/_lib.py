@@ -88,6 +88,10 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_iso_num_blocks": (i64, [i32, i32, i32]),
         "dsdf_iso_count": (C.c_int, [vp, i32, i32, i32, f32, vp, vp]),
         "dsdf_iso_emit": (C.c_int, [vp, i32, i32, i32, f32, P(f32), P(f32), vp, vp, vp]),
+        "dsdf_exact_pack_bytes": (C.c_size_t, [vp]),
+        "dsdf_exact_pack": (C.c_int, [vp, vp, vp, vp]),
+        "dsdf_exact_scene_aux": (C.c_int, [vp, vp, vp, vp, i32, vp, vp]),
+        "dsdf_fused_forward_exact": (C.c_int, [vp, vp, vp, vp, vp, vp, i32, i64, vp, vp, vp]),
         "dsdf_adam": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp, vp]),
         "dsdf_clip_coef": (C.c_int, [vp, i64, f32, vp, vp, vp]),
         "dsdf_clip_coef_static": (C.c_int, [vp, i64, f32, vp, vp]),

@@ -128,15 +128,50 @@ class FusedEngine:
                                                 scene_ids.data_ptr(), S, float(max_norm or 0.0), cb.data_ptr(), self._st()))
         return cb
 
+    def _exact_pack(self) -> torch.Tensor:
+        """(hi, lo) bf16 split of the folded hidden weights for ``decode_scenes(exact=True)``; rebuilt when the parameters changed."""
+        from .small import param_key
+        key = param_key(self.decoder)
+        if getattr(self, "_xpack_key", None) != key:
+            if getattr(self, "_xpack", None) is None:
+                self._xpack = torch.empty(self.lib.dsdf_exact_pack_bytes(C.byref(self.desc)) // 2, dtype=torch.bfloat16, device=self.device)
+            P = self.decoder.c_params()
+            with torch.cuda.device(self.device):
+                L.check(self.lib.dsdf_exact_pack(C.byref(self.desc), C.byref(P), self._xpack.data_ptr(), self._st()))
+            self._xpack_key = key
+        return self._xpack
+
+    def scene_bias_exact(self, lat_table: torch.Tensor, scene_ids: torch.Tensor) -> torch.Tensor:
+        """Per-scene aux rows for ``decode_scenes(exact=True)``: the fp16 (hi, lo) counterpart of ``scene_bias`` (no renorm)."""
+        L.require_cuda(lat_table, scene_ids)
+        S = scene_ids.numel()
+        self._ensure_eval()
+        out = torch.empty(S, 2, 512, 16, dtype=torch.float16, device=self.device)
+        with torch.cuda.device(self.device):
+            L.check(self.lib.dsdf_exact_scene_aux(C.byref(self.desc), self.pack.data_ptr(), lat_table.data_ptr(), scene_ids.data_ptr(), S,
+                                                  out.data_ptr(), self._st()))
+        return out
+
     def decode_scenes(self, cbias: torch.Tensor, tile_scene: torch.Tensor, xyz: torch.Tensor,
-                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """Eval-mode SDF [N] of xyz [N,3]; rows [128*t, 128*t+128) use scene row ``tile_scene[t]`` of ``cbias``."""
+                      out: Optional[torch.Tensor] = None, exact: bool = False) -> torch.Tensor:
+        """Eval-mode SDF [N] of xyz [N,3]; rows [128*t, 128*t+128) use scene row ``tile_scene[t]`` of ``cbias``.
+        ``exact``: the split-fp16 tensor-core mode (csrc/chain_exact.cu; ``cbias`` from ``scene_bias_exact``): <= 1e-5 against
+        fp32 arithmetic instead of ~1e-3, at about 4x the time."""
         L.require_cuda(cbias, tile_scene, xyz)
         N = xyz.shape[0]
         assert xyz.dtype == torch.float32 and xyz.is_contiguous() and xyz.shape[1] == 3
         assert tile_scene.dtype == torch.int32 and tile_scene.numel() == (N + TILE - 1) // TILE
         sdf = out if out is not None else torch.empty(N, device=self.device)
         self._ensure_eval()
+        if exact:
+            if cbias.dtype != torch.float16:
+                raise L.DsdfError("decode_scenes(exact=True) needs the aux rows of scene_bias_exact (fp16)")
+            xp = self._exact_pack()
+            with torch.cuda.device(self.device):
+                L.check(self.lib.dsdf_fused_forward_exact(C.byref(self.desc), self.pack.data_ptr(), xp.data_ptr(), cbias.data_ptr(),
+                                                          tile_scene.data_ptr(), xyz.data_ptr(), 3, N, self._b_last().data_ptr(),
+                                                          sdf.data_ptr(), self._st()))
+            return sdf
         io = L.TrainIO()
         io.b_last = self._b_last().data_ptr()
         io.training = 0

@@ -21,8 +21,12 @@ TILE = 128
 
 
 def create_mesh_sdf(decoder, latent_vec: torch.Tensor, N: int = 256, max_batch: int = 1 << 21, with_grad: bool = False,
-                    slab: Optional[Tuple[int, int]] = None, out_device=None, latent_tangents: Optional[torch.Tensor] = None):
+                    slab: Optional[Tuple[int, int]] = None, out_device=None, latent_tangents: Optional[torch.Tensor] = None,
+                    exact: bool = False):
     """SDF values of create_mesh's grid, shape [n_slab, N, N] (``slab=None``: the whole [N, N, N] volume).
+
+    exact=True (8x512-class decoders, SDF only): the split-bf16 tensor-core mode, ~1e-6 against the reference's fp32
+    arithmetic instead of the bf16 chain's ~1e-3, at about 4x the time (small decoders are fp32 anyway).
 
     with_grad=True additionally returns (dxyz [n, N, N, 3], dlat [n, N, N, L]); with ``latent_tangents`` [L, T] the
     latent part is contracted on the fly to [n, N, N, T] (what ``jvp`` with T tangents would give) so that the
@@ -35,6 +39,8 @@ def create_mesh_sdf(decoder, latent_vec: torch.Tensor, N: int = 256, max_batch: 
             raise L.DsdfError("create_mesh_sdf needs a decoder of the fused 8x512 class or of the small-network class (hidden width "
                               "<= 128); evaluate other NetworkSpecs through Decoder.forward chunks")
         return _create_mesh_sdf_small(sm, latent_vec, N, max_batch, with_grad, slab, out_device, latent_tangents)
+    if exact and with_grad:
+        raise L.DsdfError("create_mesh_sdf(exact=True) evaluates the SDF only; take derivatives from the bf16 path (with_grad=True)")
     dev = eng.device
     Lz = eng.spec.latent_size
     i0, i1 = slab if slab is not None else (0, N)
@@ -49,7 +55,8 @@ def create_mesh_sdf(decoder, latent_vec: torch.Tensor, N: int = 256, max_batch: 
         if latent_tangents is not None:
             latent_tangents = latent_tangents.to(dev, torch.float32)
     table = latent_vec.detach().reshape(1, -1).to(dev, torch.float32).contiguous()
-    cb = eng.scene_bias(table, torch.zeros(1, dtype=torch.int64, device=dev))
+    zero_id = torch.zeros(1, dtype=torch.int64, device=dev)
+    cb = eng.scene_bias_exact(table, zero_id) if exact else eng.scene_bias(table, zero_id)
     chunk = max(TILE, (int(max_batch) // TILE) * TILE)
     chunk = min(chunk, (total + TILE - 1) // TILE * TILE)
     xyz = torch.zeros(chunk, 3, device=dev)
@@ -70,7 +77,7 @@ def create_mesh_sdf(decoder, latent_vec: torch.Tensor, N: int = 256, max_batch: 
                     dlat[head:head + n].copy_(G[:n, :Lz] @ latent_tangents)
         else:
             n_pad = (n + TILE - 1) // TILE * TILE
-            eng.decode_scenes(cb, ts[:n_pad // TILE], xyz[:n], out=sdf_c)
+            eng.decode_scenes(cb, ts[:n_pad // TILE], xyz[:n], out=sdf_c, exact=exact)
         sdf[head:head + n].copy_(sdf_c[:n])
         head += n
     shape = (i1 - i0, N, N)

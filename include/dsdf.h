@@ -200,6 +200,23 @@ int dsdf_scene_prepare(const dsdf_net_desc* desc, const void* pack, float* lat_t
 int dsdf_fused_forward(const dsdf_net_desc* desc, const void* pack, const void* scene_aux, const int32_t* tile_scene,
                        const float* xyz, int32_t xyz_stride, int64_t n_rows, float* sdf_out, const dsdf_train_io* io,
                        void* stream);
+/* High-precision eval forward on the tensor cores (csrc/chain_exact.cu): the "1e-5" mode of Decoder.forward
+ * (deep_sdf/networks/deep_sdf_decoder.py:76-111) for grid evaluation (deep_sdf/mesh.py:37-73) and decode_sdf with one code
+ * (deep_sdf/utils.py:54-65).  Activations, weights and aux operands are carried as (hi, lo) fp16 pairs (~22 mantissa bits), all
+ * partial products accumulate in fp32: <= 1e-5 against the fp32 arithmetic at natural output scale, at ~4x the tensor work of
+ * dsdf_fused_forward per point.  Scene mode, eval only.
+ *   exact_pack   dsdf_exact_pack_bytes() bytes, written by dsdf_exact_pack from the parameters (weight norm folded, hidden
+ *                columns and layer biases split hi / lo)
+ *   scene_aux    dsdf_scene_aux_bytes(n_scenes) bytes, written by dsdf_exact_scene_aux (the fp16 counterpart of the rows
+ *                dsdf_scene_prepare writes; no renorm - run dsdf_scene_prepare first if max_norm applies)
+ *   pack         the regular pack (fp32 side tables, last layer) */
+size_t dsdf_exact_pack_bytes(const dsdf_net_desc* desc);
+int dsdf_exact_pack(const dsdf_net_desc* desc, const dsdf_params* params, void* exact_pack, void* stream);
+int dsdf_exact_scene_aux(const dsdf_net_desc* desc, const void* pack, const float* lat_table, const int64_t* scene_ids,
+                         int32_t n_scenes, void* scene_aux, void* stream);
+int dsdf_fused_forward_exact(const dsdf_net_desc* desc, const void* pack, const void* exact_pack, const void* scene_aux,
+                             const int32_t* tile_scene, const float* xyz, int32_t xyz_stride, int64_t n_rows,
+                             const float* b_last, float* sdf_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Fused training step (scene mode).  All buffers are caller-owned device memory; dsdf_train_buf_sizes() fills
