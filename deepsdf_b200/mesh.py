@@ -39,6 +39,8 @@ def create_mesh_sdf(decoder, latent_vec: torch.Tensor, N: int = 256, max_batch: 
             raise L.DsdfError("create_mesh_sdf needs a decoder of the fused 8x512 class or of the small-network class (hidden width "
                               "<= 128); evaluate other NetworkSpecs through Decoder.forward chunks")
         return _create_mesh_sdf_small(sm, latent_vec, N, max_batch, with_grad, slab, out_device, latent_tangents)
+    dec_ = decoder.module if isinstance(decoder, torch.nn.DataParallel) else decoder
+    exact = bool(exact or (getattr(dec_, "fused_exact", False) and not with_grad))
     if exact and with_grad:
         raise L.DsdfError("create_mesh_sdf(exact=True) evaluates the SDF only; take derivatives from the bf16 path (with_grad=True)")
     dev = eng.device

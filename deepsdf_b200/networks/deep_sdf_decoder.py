@@ -117,6 +117,8 @@ class Decoder(nn.Module):
 
     # ------------------------------------------------------------------ forward
     fused_eval = True      # eval-mode forward of fused-class networks with CodeLength <= 16 on the tensor-core chain
+    fused_exact = False    # consumers with one code per call (decode_sdf, create_mesh): True selects the split-fp16 high-precision
+                           # tensor-core forward (<= 1e-5 vs fp32, ~4x the time of the bf16 chain; csrc/chain_exact.cu)
 
     def _fused_rows_supported(self) -> bool:
         ok = getattr(self, "_fused_rows_ok", None)

@@ -64,6 +64,11 @@ def decode_sdf(decoder, latent_vector, queries):
     dev = eng.device
     q = queries.detach().to(dev, torch.float32).contiguous()
     table = latent_vector.detach().reshape(1, -1).to(dev, torch.float32).contiguous()
-    cb = eng.scene_bias(table, torch.zeros(1, dtype=torch.int64, device=dev))
     ts = torch.zeros((num_samples + TILE - 1) // TILE, dtype=torch.int32, device=dev)
+    zero_id = torch.zeros(1, dtype=torch.int64, device=dev)
+    dec = decoder.module if isinstance(decoder, torch.nn.DataParallel) else decoder
+    if getattr(dec, "fused_exact", False):
+        # ``decoder.fused_exact = True``: the split-fp16 tensor-core mode, <= 1e-5 against the reference's fp32 arithmetic
+        return eng.decode_scenes(eng.scene_bias_exact(table, zero_id), ts, q, exact=True).unsqueeze(1)
+    cb = eng.scene_bias(table, zero_id)
     return eng.decode_scenes(cb, ts, q).unsqueeze(1)

@@ -81,3 +81,25 @@ def test_exact_pack_follows_parameter_updates_and_grid_path():
         with torch.no_grad():
             for p in mod.parameters():
                 p.mul_(1.01)
+
+
+def test_decode_sdf_honours_the_modules_precision_switch():
+    """``decoder.fused_exact = True`` routes decode_sdf(decoder, latent, queries) (deep_sdf/utils.py:54-65) and create_mesh's grid
+    to the high-precision mode without touching the reference's call signatures."""
+    from deepsdf_b200.utils import decode_sdf
+    name = "big_8x512_L256"
+    kw = dict(META[name]["spec"])
+    ospec = O.OracleSpec(**kw)
+    params = O.make_params(ospec, 7)
+    mod = build_module(kw, params, DEV).eval()
+    rng = np.random.RandomState(4)
+    lat = torch.from_numpy((rng.normal(0, 1, (ospec.latent_size,)) / 16).astype(np.float32))
+    pts = torch.from_numpy(rng.uniform(-1, 1, (1000, 3)).astype(np.float32))
+    ref = O.decoder_forward(ospec, _f64(params), torch.cat([lat.expand(1000, -1), pts], 1).double())
+    y_bf16 = decode_sdf(mod, lat.to(DEV), pts.to(DEV)).cpu()
+    mod.fused_exact = True
+    y_exact = decode_sdf(mod, lat.to(DEV), pts.to(DEV)).cpu()
+    mod.fused_exact = False
+    e_b, e_x = (y_bf16.double() - ref).abs().max().item(), (y_exact.double() - ref).abs().max().item()
+    print(f"decode_sdf: bf16 chain max err {e_b:.2e}, fused_exact max err {e_x:.2e}")
+    assert y_exact.shape == (1000, 1) and e_x <= TOL and e_x < 0.05 * e_b
