@@ -12,7 +12,7 @@ LIB = os.path.join(ROOT, "deepsdf_b200", "libdsdf_b200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
 WANT = {"chain_forward_train": "chain_forward_kernelILb1", "chain_forward_eval": "chain_forward_kernelILb0",
         "chain_dgrad": "chain_dgrad_kernel", "wgrad": "_ZN4dsdf12wgrad_kernel", "input_grad": "input_grad_kernel",
-        "small_forward_128": "small_forward_kernelILi128"}
+        "small_forward_128": "small_forward_kernelILi128", "chain_exact": "chain_exact_kernel"}
 SPECIAL = ("UTC", "UTMA", "LDTM", "SYNCS", "UBLKCP")
 
 
