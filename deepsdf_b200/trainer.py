@@ -430,3 +430,29 @@ class HostFeeder:
         self._tail += 1
         return loss
 
+    def step_async(self, epoch: int, global_rows: Optional[int] = None, row0: int = 0) -> "LossHandle":
+        """``step`` whose loss is read back asynchronously: the [2] loss tensor is copied into a pinned ring slot behind the
+        step, and the returned handle's ``wait()`` blocks until THAT step has finished.  Reading the previous step's handle
+        after queueing the next step keeps the GPU busy across the read (the reference's ``.item()`` per iteration,
+        train_deep_sdf.py:535, drains the queue every step).  A handle must be waited for before ``depth`` further steps reuse
+        its slot."""
+        if not hasattr(self, "_loss_host"):
+            self._loss_host = [torch.empty(2, dtype=torch.float32).pin_memory() for _ in range(self.depth)]
+            self._loss_done = [torch.cuda.Event() for _ in range(self.depth)]
+        k = self._tail % self.depth
+        loss = self.step(epoch, global_rows=global_rows, row0=row0)
+        self._loss_host[k].copy_(loss, non_blocking=True)
+        self._loss_done[k].record(torch.cuda.current_stream(self.trainer.device))
+        return LossHandle(self._loss_host[k], self._loss_done[k])
+
+
+class LossHandle:
+    """Result of ``HostFeeder.step_async``: ``wait()`` returns the step's (total, data-term) loss as a CPU tensor."""
+
+    def __init__(self, host: torch.Tensor, done: torch.cuda.Event):
+        self._host, self._done = host, done
+
+    def wait(self) -> torch.Tensor:
+        self._done.synchronize()
+        return self._host.clone()
+

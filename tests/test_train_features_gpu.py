@@ -172,10 +172,18 @@ def test_host_feeder_overlaps_copies_without_changing_results(graphed):
         if piped:
             fd = HostFeeder(tr, S * sps, S, graphed=graphed)
             fd.submit(*host[0])
+            pending = None
             for b in range(5):
                 if b + 1 < 5:
                     fd.submit(*host[b + 1])
-                losses.append(fd.step(epoch=7).cpu().clone())
+                if b < 2:
+                    losses.append(fd.step(epoch=7).cpu().clone())
+                else:                                            # asynchronous read-back, one step behind
+                    h = fd.step_async(epoch=7)
+                    if pending is not None:
+                        losses.append(pending.wait())
+                    pending = h
+            losses.append(pending.wait())
             with pytest.raises(Exception):
                 fd.step(epoch=7)                                     # nothing submitted
         else:
