@@ -242,6 +242,10 @@ class SceneTrainer:
         # the one exchange of the step: all-reduce (sum) of the flat decoder gradient (strict mode: + the dense latent gradient
         # behind it in the same buffer).  Replaces nn.DataParallel's gradient reduction (train_deep_sdf.py:353).
         work = None
+        ev = getattr(self, "comm_events", None)      # optional timing hooks (tools/allreduce_exposure.py): (issued, joined) pairs
+        if ev is not None:
+            e_issue = torch.cuda.Event(enable_timing=True)
+            e_issue.record()
         if self.world_size > 1:
             import torch.distributed as dist
             work = dist.all_reduce(self._gbuf, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
@@ -252,6 +256,10 @@ class SceneTrainer:
             eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat, step_state=self.step_state)
         if work is not None:
             work.wait()
+        if ev is not None:
+            e_join = torch.cuda.Event(enable_timing=True)
+            e_join.record()
+            ev.append((e_issue, e_join))
         scale_dev = None
         if self.grad_clip is not None:                                                  # :541-543 (decoder only)
             eng.clip_coef(self.flat_g, self.grad_clip, self._clip_scratch, self._clip_out)
