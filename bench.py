@@ -474,6 +474,9 @@ def run_gpu(args):
                                (f"64 scenes x 16384 samples per step split over {world} GPU(s)" if strong else
                                 "64 scenes x 16384 samples per GPU per step"),
                    "rows_per_gpu_step": N, "global_rows_per_step": global_rows, "parallelism": f"dp{world}",
+                   "exchange": ("none (one GPU)" if world == 1 else
+                                "own NVLS all-reduce kernel (multimem.ld_reduce/st over NVSwitch multicast, dsdf_nvls_allreduce_f32)"
+                                if trainer._nvls is not None else "ncclAllReduce"),
                    "cache": "per-step working set (bf16 activation + dY stashes, 17 GB) is far larger than the 126 MB L2; 4 rotating input batches"},
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e},

@@ -94,6 +94,8 @@ def _declare(lib: C.CDLL) -> None:
         "dsdf_fused_forward_exact": (C.c_int, [vp, vp, vp, vp, vp, vp, i32, i64, vp, vp, vp]),
         "dsdf_adam": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp, vp]),
         "dsdf_clip_coef": (C.c_int, [vp, i64, f32, vp, vp, vp]),
+        "dsdf_nvls_signal_words": (C.c_int32, [i32]),
+        "dsdf_nvls_allreduce_f32": (C.c_int, [vp, vp, i32, i32, i64, vp]),
         "dsdf_clip_coef_static": (C.c_int, [vp, i64, f32, vp, vp]),
         "dsdf_adam_state": (C.c_int, [vp, vp, vp, vp, i64, f32, f32, f32, f32, vp, f32, vp, vp]),
         "dsdf_step_advance": (C.c_int, [vp, f32, f32, vp]),

@@ -101,7 +101,8 @@ class SceneTrainer:
         self.replicated = bool(replicated)
         # strict mode: decoder and latent gradients share one buffer = one all-reduce
         n_lat = num_scenes * self.latent_size if (self.replicated and world_size > 1) else 0
-        self._gbuf = torch.zeros(self.flat_p.numel() + n_lat, dtype=torch.float32, device=self.flat_p.device)
+        self._nvls = None
+        self._gbuf = self._alloc_grad_buffer(self.flat_p.numel() + n_lat)
         self.flat_g = self._gbuf[:self.flat_p.numel()]
         self.exp_avg = torch.zeros_like(self.flat_p)
         self.exp_avg_sq = torch.zeros_like(self.flat_p)
@@ -144,6 +145,40 @@ class SceneTrainer:
         self.side_stream = None if os.environ.get("DSDF_NO_SIDE_STREAM") else torch.cuda.Stream(device=self.device)
 
     # ------------------------------------------------------------------ helpers
+    def _alloc_grad_buffer(self, numel: int) -> torch.Tensor:
+        """The flat gradient buffer.  With several ranks it is placed in symmetric memory mapped through an NVSwitch multicast
+        address, so that the exchange of the step can be this library's own all-reduce kernel (``dsdf_nvls_allreduce_f32``,
+        csrc/nvls_allreduce.cu) instead of ncclAllReduce.  torch.distributed._symmetric_memory is used for the allocation and the
+        rendezvous only.  All ranks must agree, so the outcome is MIN-reduced; any rank that cannot (no multicast support, backend
+        other than NCCL, ``DSDF_ALLREDUCE=nccl``) sends everybody to the NCCL path."""
+        import os
+        dev = self.flat_p.device
+        if self.world_size <= 1:
+            return torch.zeros(numel, dtype=torch.float32, device=dev)
+        import torch.distributed as dist
+        group = self.pg if self.pg is not None else dist.group.WORLD
+        buf, hdl, ok = None, None, 0
+        if os.environ.get("DSDF_ALLREDUCE", "nvls") == "nvls" and dist.get_backend(group) == "nccl" and numel % 4 == 0:
+            try:
+                import torch.distributed._symmetric_memory as symm
+                buf = symm.empty(numel, dtype=torch.float32, device=dev)
+                buf.zero_()
+                hdl = symm.rendezvous(buf, group.group_name)
+                words = int(self.engine_lib().dsdf_nvls_signal_words(self.world_size))
+                ok = int(hdl.multicast_ptr != 0 and hdl.signal_pad_size >= 4 * words and hdl.world_size == self.world_size)
+            except Exception:  # noqa: BLE001 - symmetric memory is an optimisation; NCCL is the fallback for the whole group
+                ok = 0
+        flag = torch.tensor([ok], device=dev, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 1:
+            self._nvls = hdl
+            return buf
+        return torch.zeros(numel, dtype=torch.float32, device=dev)
+
+    @staticmethod
+    def engine_lib():
+        return L.lib()
+
     def tile_scene_for(self, n_scenes: int, samples_per_scene: int) -> torch.Tensor:
         """Scene-major batches (train_deep_sdf.py:496-499: indices repeated SamplesPerScene times): tile t of 128 rows
         belongs to batch slot t // (SamplesPerScene/128)."""
@@ -246,11 +281,17 @@ class SceneTrainer:
         if ev is not None:
             e_issue = torch.cuda.Event(enable_timing=True)
             e_issue.record()
-        if self.world_size > 1:
+        if self._nvls is not None:
+            # this library's own exchange: multimem.ld_reduce / multimem.st over the NVSwitch multicast mapping of the buffer
+            # (stream-ordered behind finish; nothing to overlap it with but the latent Adam, which is 8 us)
+            with torch.cuda.device(self.device):
+                L.check(eng.lib.dsdf_nvls_allreduce_f32(self._nvls.multicast_ptr, self._nvls.signal_pad_ptrs_dev, self._nvls.rank,
+                                                        self.world_size, self._gbuf.numel(), L.stream_ptr(self.device)))
+        elif self.world_size > 1:
             import torch.distributed as dist
             work = dist.all_reduce(self._gbuf, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
         if not lat_adam_done:
-            if shared_lat:                               # the latent gradient is part of the exchange
+            if shared_lat and work is not None:          # the latent gradient is part of the exchange
                 work.wait()
                 work = None
             eng.adam(self.lat_vecs, self.lat_grad, self.lat_exp_avg, self.lat_exp_avg_sq, self.step_count, lr_lat, step_state=self.step_state)

@@ -348,6 +348,15 @@ int dsdf_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr,
 /* the same update with the bias corrections read from the device-resident step state: replayable inside a CUDA graph */
 int dsdf_adam_state(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
                     const dsdf_step_state* state, float grad_scale, const float* grad_scale_dev, void* stream);
+/* All-reduce (sum, in place) of a flat fp32 buffer that every rank holds in symmetric memory mapped through one NVSwitch
+ * multicast address (csrc/nvls_allreduce.cu): the gradient exchange of the multi-GPU training path (replaces nn.DataParallel's
+ * reduction, train_deep_sdf.py:353) as this library's own kernel - multimem.ld_reduce / multimem.st on rank-owned slices between
+ * two cross-GPU barriers on the symmetric signal pads.  multicast_ptr: multicast address of the buffer; signal_pad_ptrs_dev: device
+ * array [world] of the ranks' signal-pad addresses (zero-initialised, >= dsdf_nvls_signal_words(world) 32-bit words each, used by
+ * nothing else); n: floats, a multiple of 4.  Every rank of the group must make the call, stream-ordered behind its producers. */
+int32_t dsdf_nvls_signal_words(int32_t world);
+int dsdf_nvls_allreduce_f32(float* multicast_ptr, const void* signal_pad_ptrs_dev, int32_t rank, int32_t world, int64_t n,
+                            void* stream);
 /* torch.nn.utils.clip_grad_norm_ (train_deep_sdf.py:541-543) over one flat fp32 gradient: out[0] = ||g||_2,
  * out[1] = min(1, max_norm / (||g||_2 + 1e-6)).  Deterministic two-stage reduction; `scratch` holds 1024 floats. */
 int dsdf_clip_coef(const float* g, int64_t n, float max_norm, float* scratch, float* out, void* stream);
