@@ -348,9 +348,10 @@ def run_gpu(args):
 
     # ---- timed region 2: end to end from pinned host memory, loss read back every step.  The user-facing loop of a host-fed
     #      run: HostFeeder.submit (H2D copy of the NEXT batch on a copy stream, what DataLoader workers + .cuda() do in the
-    #      reference) then HostFeeder.step on the current one; every timed step contains one 16.8 MB copy and one loss read (asynchronous, one step behind: HostFeeder.step_async).
+    #      reference) then HostFeeder.step on the current one; every timed step contains one 16.8 MB copy and one loss read (asynchronous, two steps behind: HostFeeder.step_async).
     from deepsdf_b200.trainer import HostFeeder
-    feeder = HostFeeder(trainer, N, S_step, graphed=graphed)
+    LAG = 2                               # steps the host runs ahead of the loss it reads (absorbs host-side jitter between ranks)
+    feeder = HostFeeder(trainer, N, S_step, depth=LAG + 2, graphed=graphed)
     feeder.submit(host_batches[0], host_ids[0])
     for i in range(2):
         feeder.submit(host_batches[(i + 1) % N_HOST_BATCHES], host_ids[(i + 1) % N_HOST_BATCHES])
@@ -358,15 +359,15 @@ def run_gpu(args):
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
-    last = pending = None
+    last, pending = None, []
     for i in range(args.steps):
         nb = (i + 3) % N_HOST_BATCHES
         feeder.submit(host_batches[nb], host_ids[nb])          # next batch's copy runs under this step
-        h = feeder.step_async(1, global_rows=global_rows, row0=row0)
-        if pending is not None:
-            last = pending.wait()         # device -> host read of the PREVIOUS step's loss, while this step is already queued
-        pending = h
-    last = pending.wait()                 # every step's loss has been read back inside the timed region
+        pending.append(feeder.step_async(1, global_rows=global_rows, row0=row0))
+        if len(pending) > LAG:
+            last = pending.pop(0).wait()  # device -> host read of an EARLIER step's loss, while later steps are already queued
+    while pending:
+        last = pending.pop(0).wait()      # every step's loss has been read back inside the timed region
     e3.record()
     barrier()
     ms_e2e = max_over_ranks(e2.elapsed_time(e3)) / args.steps
