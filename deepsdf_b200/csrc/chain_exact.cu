@@ -1,15 +1,17 @@
 // High-precision eval forward of the 8x512-class decoder on the tensor cores ("split-fp16" mode): the north star's
 // "1e-5 (tf32 mode)" bound, met with 16-bit MMAs (kind::f16, fp32 accumulate) instead of the fp32 CUDA-core path.
 //
-// Every activation x and every weight w is carried as a PAIR of 16-bit numbers, x = x_hi + x_lo, w = w_hi + w_lo
-// (fp16, x_lo = fp16(x - x_hi): together ~22 mantissa bits; the first build used bf16 pairs, ~16 bits, and missed the 1e-5
-// bound by 4x at natural output scale - fp16's range is ample for weight-normed activations, which are clamped to +-6e4).  The activation tile of a CTA keeps the kernel's usual geometry,
-// [128 rows x 512] bf16 in shared memory, but its 128 MMA rows are 64 points TWICE: rows 0..63 hold x_hi of the CTA's 64
-// points, rows 64..127 hold x_lo of the same points.  Each layer streams its weights twice, W_hi then W_lo, into the same
-// accumulators, so that TMEM lane r ends up with x_hi . (W_hi + W_lo) and lane r + 64 with x_lo . (W_hi + W_lo); the
-// epilogue adds the two lanes (exchanged through shared memory between the two warps that own them), which is
-// (x_hi + x_lo) . (W_hi + W_lo) with fp32 accumulation - all four partial products, nothing dropped.  Bias, per-scene
-// latent part and xyz columns enter through the aux step of chain_fwd.cu (bf16 operands, hi/lo-split already).
+// Every activation x, every weight w and every aux operand is carried as a PAIR of fp16 numbers, x = x_hi + x_lo
+// (x_lo = fp16(x - x_hi): together ~22 mantissa bits; a first build with bf16 pairs, ~16 bits, missed the 1e-5 bound by 4x at
+// natural output scale, and bf16-pair aux operands alone still left 1.4e-5.  fp16's range is ample for weight-normed
+// activations, which are clamped to 6e4).  The activation tile of a CTA keeps the chain kernel's geometry, [128 rows x 512]
+// 16-bit in shared memory, but its 128 MMA rows are 64 points TWICE: rows 0..63 hold x_hi of the CTA's 64 points, rows
+// 64..127 hold x_lo of the same points.  Each layer streams its weights twice, W_hi then W_lo, into the same accumulators,
+// so that TMEM lane r ends up with x_hi . (W_hi + W_lo) and lane r + 64 with x_lo . (W_hi + W_lo); the epilogue adds the two
+// lanes (exchanged through shared memory between the two warps that own them), which is (x_hi + x_lo) . (W_hi + W_lo) with
+// fp32 accumulation - all four partial products, nothing dropped.  Layer bias, per-scene latent part and xyz columns enter
+// through the aux step of chain_fwd.cu's design, here with fp16 (hi, lo) operands of their own (exact_scene_aux_kernel and the
+// constant aux rows behind the weights in the exact pack); the x_lo rows of the aux A block are zero, so they are added once.
 //
 // Cost: two weight passes for half as many points per tile = 4x the tensor work of the bf16 chain per point - still
 // ~20x the throughput of the fp32 CUDA-core path (csrc/generic.cu), which stays the bit-level reference.  Eval mode,
