@@ -27,6 +27,26 @@ def test_library_exports_every_declared_symbol():
     assert lib.dsdf_abi_version() == L.ABI_VERSION
 
 
+def test_ctypes_binding_matches_the_header_prototypes():
+    """Every function the Python side declares (deepsdf_b200/_lib.py) takes as many arguments as its prototype in
+    include/dsdf.h: a drifted binding would pass garbage through the C ABI without any error."""
+    hdr = open(os.path.join(ROOT, "include", "dsdf.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", " ", hdr, flags=re.S)                       # drop comments
+    protos = {}
+    for m in re.finditer(r"\b(dsdf_[a-z0-9_]+)\s*\(([^()]*)\)\s*;", hdr):
+        args = m.group(2).strip()
+        protos[m.group(1)] = 0 if args in ("", "void") else args.count(",") + 1
+    lib = L.lib()
+    checked = 0
+    for name, n_args in sorted(protos.items()):
+        fn = getattr(lib, name)
+        if fn.argtypes is None:
+            continue                                                       # not used from Python
+        assert len(fn.argtypes) == n_args, f"{name}: include/dsdf.h has {n_args} parameters, _lib.py declares {len(fn.argtypes)}"
+        checked += 1
+    assert checked >= 40, checked
+
+
 def test_no_gpu_means_loud_failure():
     if torch.cuda.is_available():
         pytest.skip("GPU present")
