@@ -95,10 +95,12 @@ def _unfiltered_batch(data, scenes, rows, seed):
     return ids, batch
 
 
-def test_unfiltered_gradients_vs_fp32_reference():
+@pytest.mark.parametrize("scenes,rows", [([0, 2, 3, 5, 8, 11, 13, 15], 1024), (list(range(16)), 2048)])
+def test_unfiltered_gradients_vs_fp32_reference(scenes, rows):
+    """8192 rows (the r01 verdict's minimum) and 32768 rows: the operand-rounding part of the error averages out with the
+    row count, the part that comes from ReLU gates within bf16 noise of zero does not."""
     ospec, params, mod, tr, table, data = trained()
     eng = tr.engine
-    scenes, rows = [0, 2, 3, 5, 8, 11, 13, 15], 1024
     ids, batch = _unfiltered_batch(data, scenes, rows, seed=21)
     N = batch.shape[0]
     tile_scene = torch.arange(len(scenes), dtype=torch.int32).repeat_interleave(rows // 128)
@@ -153,9 +155,11 @@ def test_unfiltered_gradients_vs_fp32_reference():
     lrelq = float((lat_grad.cpu() - zq).norm() / zq.norm())
     print(f"   latent gradient: vs fp32 {lrel32:.3e}, vs bf16-operand oracle {lrelq:.3e}")
     print(f"   WORST: vs fp32 {worst32:.3e} (min cos {mincos:.5f}); vs bf16-operand oracle without gate hand-over {worstq:.3e}")
-    # asserted at the level this arithmetic achieves on an unconditioned batch (numbers in DESIGN.md section 5)
-    assert worst32 <= 0.25 and mincos >= 0.97 and lrel32 <= 0.25
-    assert worstq <= 0.25 and lrelq <= 0.25
+    # asserted at the level this arithmetic achieves on an unconditioned batch (numbers in DESIGN.md section 5; the north star
+    # asks for 1e-2: met by most tensors, the worst sits at 1.4e-2 with 8192 rows)
+    bound = 2e-2 if N <= 8192 else 1.2e-2        # measured 1.09e-2 / 8.6e-3 (latent 8.8e-3 / 9.8e-3)
+    assert worst32 <= bound and mincos >= 0.9995 and lrel32 <= bound
+    assert worstq <= 2e-2 and lrelq <= 2e-2
 
 
 def test_gate_words_are_what_the_stash_and_philox_say():
